@@ -1,0 +1,194 @@
+/* pgm_gmove.h — C ABI of the B200-native `poregen gmove` hot path.
+ *
+ * The reference (hiruna72/poregen) exposes NO library/FFI interface for this path: its only
+ * boundaries are the command line `poregen gmove [opts] reads.blow5 alignment output_dir`
+ * (reference src/gmove.cpp:80-104, 330-360) and the C++ symbol `int gmove(int, char**)`
+ * (src/main.c:43,76). This header is the one host<->device seam the new build introduces under
+ * that CLI. Each entry point names the reference code it replaces.
+ *
+ * Plain C: pointers and sizes only, no C++/torch types. The library never calls exit(), never
+ * throws across the ABI, and has NO CPU fallback: every compute entry point fails with
+ * PGM_ERR_CUDA when no sm_100 device is usable.
+ *
+ * Data model (one "batch" = consecutive alignment records, in alignment-file order):
+ *   raw[]    int16 signal of all reads, concatenated               (slow5_rec_t::raw_signal)
+ *   align[]  per read: move string '0'/'1' (TSV col 5, gmove.cpp:574), or the mv:B:c moves after
+ *            the stride element as int8 (gmove.cpp:1100-1123), or the ss:Z: string (gmove.cpp:778)
+ *   bases[]  per read: basecalled sequence (TSV col 3 / SAM SEQ) or, for ss records, the target
+ *            slice faidx_fetch_seq(tid, st_k, end_k-1) (gmove.cpp:805). NOT T->U converted: the
+ *            device applies gmove.cpp:815-817 itself for records flagged PGM_READ_RNA.
+ *   reads[]  one pgm_read per record (offsets into the three arrays + per-record scalars)
+ */
+#ifndef PGM_GMOVE_H
+#define PGM_GMOVE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PGM_ABI_VERSION 1
+
+/* ---- status codes ---- */
+#define PGM_OK 0
+#define PGM_ERR_ARG 1       /* bad argument / unsupported option combination */
+#define PGM_ERR_CUDA 2      /* CUDA runtime failure or no usable device */
+#define PGM_ERR_NOMEM 3     /* host or device allocation failed */
+#define PGM_ERR_INPUT 4     /* malformed batch (bad ss string, offsets out of range, ...) */
+#define PGM_ERR_STATE 5     /* calls made in the wrong order */
+
+/* ---- alignment encodings (pgm_batch.mode) ---- */
+#define PGM_MODE_MOVES_CHAR 0 /* TSV move table: bytes '0'/'1'              gmove.cpp:539-706   */
+#define PGM_MODE_SS 1         /* PAF ss:Z: string "<n>,|<n>I|<n>D"          gmove.cpp:707-975   */
+#define PGM_MODE_MOVES_I8 2   /* SAM/BAM mv:B:c moves (int8 0/1); a read with ANY out-of-range pA
+                                 sample is dropped whole                    gmove.cpp:1061-1266 */
+
+/* ---- pgm_read.flags ---- */
+#define PGM_READ_RNA 1u  /* ss record with target_start > target_end (gmove.cpp:793)            */
+#define PGM_READ_SKIP 2u /* host decided to skip the record (e.g. ss target slice shorter than
+                            k, gmove.cpp:806-808); it produces no events and no ':' delimiter   */
+
+/* ---- result read_flags bits (device decided) ---- */
+#define PGM_RF_SKIPPED 1u   /* record produced nothing and gets no ':' (fastq_len<10
+                               gmove.cpp:616-619,1178-1181; MOVES_I8 out-of-range 1158-1160;
+                               host PGM_READ_SKIP)                                               */
+#define PGM_RF_BAD_ALIGN 2u /* malformed alignment (bad ss char, fewer than m+1 moves): the
+                               reference exits / has undefined behaviour; we emit nothing        */
+#define PGM_RF_BAD_CALIB 4u /* non-finite calibration; reference behaviour undefined             */
+
+/* ---- output kinds (pgm_opts.output) ---- */
+#define PGM_OUT_F64 0  /* selected samples as IEEE doubles (bit-exact with the reference vector) */
+#define PGM_OUT_TEXT 1 /* additionally the exact "%.8f," / "%.8f;" text of gmove.cpp:674-678     */
+
+/* Mirrors the fields of the reference's opt_t that the gmove path reads
+ * (src/poregen.h:48-79, defaults src/poregen.cpp:209-237) after gmove()'s own option handling
+ * (gmove.cpp:240-327, 428-440, 479-491). */
+typedef struct pgm_opts {
+    uint32_t kmer_size;           /* -k            [9]   1..15                                    */
+    uint32_t sig_move_offset;     /* -m            [0]                                            */
+    uint32_t kmer_start_offset;   /* -s            [0]   moves modes only (gmove.cpp:631,1194)    */
+    uint32_t signal_print_margin; /* --margin      [0]                                            */
+    uint32_t sample_limit;        /* --sample_limit[100]                                          */
+    uint32_t max_dur;             /* --max_dur     [70]                                           */
+    uint32_t min_dur;             /* --min_dur     [5]                                            */
+    uint32_t kmer_pick_margin;    /* --kmer_pick_margin [2], ss mode only (gmove.cpp:204-211)     */
+    uint32_t flag_rna;            /* --rna: generated alphabet is ACGU (gmove.cpp:421-425)        */
+    uint32_t scaling;             /* --scaling: 0 none (the real default, gmove.cpp:229), 1 medmad*/
+    uint32_t output;              /* PGM_OUT_*                                                    */
+    uint32_t n_slots;             /* number of dumped k-mers = index_end - index_start + 1        */
+    uint32_t index_lo;            /* generated list: id of the first dumped k-mer = index_start-1 */
+    uint32_t reserved0;
+    double pa_min;                /* --pa_min [40.0]                                              */
+    double pa_max;                /* --pa_max [180.0]                                             */
+    const char *kmer_list;        /* NULL: k-mers are the lexicographic ACGT/ACGU enumeration
+                                     (poregen.cpp:248-267) and slot s is id index_lo+s.
+                                     else: n_slots*kmer_size chars, the --kmer_file lines of the
+                                     dumped range in order (gmove.cpp:395-419); must be unique.   */
+} pgm_opts;
+
+/* One alignment record. 80 bytes. */
+typedef struct pgm_read {
+    uint64_t raw_off;      /* index of the read's first sample in raw[]                           */
+    uint64_t align_off;    /* byte offset in align[]                                              */
+    uint64_t seq_off;      /* byte offset in bases[]                                              */
+    uint32_t raw_len;      /* slow5_rec_t::len_raw_signal                                         */
+    uint32_t align_len;    /* bytes: moves (without the stride element) or strlen(ss)             */
+    uint32_t seq_len;      /* bytes in bases[] (fastq_seq.size(); ss: fetched length)             */
+    uint32_t trim;         /* moves: trim_offset / ts:i (gmove.cpp:576,1098); ss: must be 0       */
+    uint32_t stride;       /* moves: stride (TSV col 4 / mv[0]); ss: ignored                      */
+    int32_t fastq_len;     /* moves: TSV col 2 / l_qseq, only used for the "<10 => skip" rule     */
+    uint32_t query_start;  /* ss: PAF col 3 = first raw index (gmove.cpp:779)                     */
+    int32_t st_k;          /* ss: min(target_start,target_end) (gmove.cpp:792-794)                */
+    int32_t end_k;         /* ss: max(target_start,target_end)                                    */
+    uint32_t flags;        /* PGM_READ_*                                                          */
+    double digitisation;   /* slow5_rec_t calibration, used as TO_PICOAMPS (poregen.h:30)         */
+    double offset;
+    double range;
+} pgm_read;
+
+/* Host (pgm_process / pgm_upload) or device (pgm_attach_device) pointers. */
+typedef struct pgm_batch {
+    uint32_t n_reads;
+    uint32_t mode;         /* PGM_MODE_*                                                          */
+    uint64_t n_raw;        /* samples in raw[]                                                    */
+    uint64_t n_align;      /* bytes in align[]  (must be < 2^32)                                  */
+    uint64_t n_bases;      /* bytes in bases[]                                                    */
+    const int16_t *raw;
+    const uint8_t *align;
+    const uint8_t *bases;
+    const pgm_read *reads;
+} pgm_batch;
+
+/* Result of one batch. All pointers are pinned host memory owned by the context and stay valid
+ * until the next pgm_process/pgm_download/pgm_destroy on it.
+ * Selected events are grouped by slot (k-mer), slots ascending; inside a slot they are in the
+ * reference's emission order = (record order, position in record) (gmove.cpp:650-652,680-685). */
+typedef struct pgm_result {
+    uint32_t n_slots;
+    uint32_t n_reads;
+    uint64_t n_events_examined; /* alignment events looked at (before any filter)                 */
+    uint64_t n_events_pass;     /* passed dur/k-mer/indel filters and not already over quota      */
+    uint64_t n_sel_events;
+    uint64_t n_sel_samples;
+    const uint32_t *slot_sel;   /* [n_slots]  events selected per slot in THIS batch              */
+    const uint32_t *slot_total; /* [n_slots]  kmer_frequency_map after this batch (gmove.cpp:680) */
+    const uint32_t *ev_len;     /* [n_sel_events] samples per event, grouped order                */
+    const uint32_t *ev_read;    /* [n_sel_events] record index inside the batch                   */
+    const uint32_t *ev_start;   /* [n_sel_events] first sample, relative to raw_off+trim          */
+    const double *samples;      /* [n_sel_samples] the values gmove.cpp:675-678 prints            */
+    const uint8_t *read_flags;  /* [n_reads] PGM_RF_*                                             */
+    const char *text;           /* PGM_OUT_TEXT: concatenated dump text, grouped by slot          */
+    const uint64_t *slot_text_off; /* [n_slots+1] byte range of slot s in text                    */
+} pgm_result;
+
+typedef struct pgm_ctx pgm_ctx;
+
+/* Replaces the option block handed to process_move_table_* (gmove.cpp:515-520) and the
+ * kmer_frequency_map / kmer_file_pointer_array initialisation (gmove.cpp:460-477).
+ * `device` is a CUDA ordinal. `stream` is a cudaStream_t to enqueue on, or NULL for a private one. */
+int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out);
+void pgm_destroy(pgm_ctx *ctx);
+const char *pgm_last_error(const pgm_ctx *ctx); /* ctx may be NULL: error of a failed pgm_create */
+int pgm_abi_version(void);
+
+/* One call = one pass of process_move_table_file / _paf / _bam over the batch's records
+ * (gmove.cpp:539-706, 707-975, 1061-1266): host buffers in, host result out. Synchronous. */
+int pgm_process(pgm_ctx *ctx, const pgm_batch *host_batch, pgm_result *out);
+
+/* Split-phase form of the same pass (device-resident timing, multi-GPU quota exchange):
+ *   pgm_upload | pgm_attach_device  ->  pgm_count  ->  [pgm_set_prior]  ->  pgm_emit  ->  pgm_download
+ * Everything except pgm_download is asynchronous on the context's stream. */
+int pgm_upload(pgm_ctx *ctx, const pgm_batch *host_batch);          /* H2D copies only            */
+int pgm_attach_device(pgm_ctx *ctx, const pgm_batch *device_batch); /* inputs already in HBM      */
+int pgm_count(pgm_ctx *ctx);  /* decode + filters + per-slot counts of passing events             */
+int pgm_emit(pgm_ctx *ctx);   /* stable bucketing, sample_limit, Med-MAD, sample gather/format    */
+int pgm_download(pgm_ctx *ctx, pgm_result *out); /* D2H + stream sync                             */
+int pgm_sync(pgm_ctx *ctx);
+
+/* Multi-GPU quota exchange (north_star: allgather of the 4^k count vector + exclusive scan over
+ * ranks). After pgm_count, counts[s] = passing events of slot s in this rank's batch (device
+ * uint32[n_slots]). The caller allgathers them and hands back, as DEVICE pointers:
+ *   prior[s]    = quota of slot s already consumed before this rank's batch
+ *                 (= total before this round + sum over lower ranks of their counts)
+ *   consumed[s] = min(sample_limit, total before this round + sum over ALL ranks) = the
+ *                 kmer_frequency_map after the round.
+ * Without these calls the context behaves as a single rank and carries the totals itself. */
+int pgm_counts_device(pgm_ctx *ctx, uint32_t **counts_dev);
+int pgm_totals_device(pgm_ctx *ctx, uint32_t **consumed_dev);
+int pgm_set_prior(pgm_ctx *ctx, const uint32_t *prior_dev, const uint32_t *consumed_dev);
+
+/* Forget all per-k-mer totals (start a new run with the same options). */
+int pgm_reset(pgm_ctx *ctx);
+
+/* Introspection for benchmarks: the stream (cudaStream_t), kernel launches issued so far, and
+ * the algorithmic byte count of the last batch (SURVEY.md §8d formula). */
+void *pgm_stream(pgm_ctx *ctx);
+uint64_t pgm_launch_count(const pgm_ctx *ctx);
+typedef struct pgm_stage_times { float upload_ms, count_ms, sort_ms, emit_ms, download_ms; } pgm_stage_times;
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PGM_GMOVE_H */

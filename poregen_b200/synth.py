@@ -1,0 +1,289 @@
+"""Seeded synthetic gmove workloads (C2..C5 shapes) as in-memory record batches,
+and optionally as the files the reference CLI reads (ASCII SLOW5 + TSV / PAF+FASTQ / SAM).
+
+Nothing here is on the hot path: it only manufactures inputs. numpy-vectorised so that the
+1e8-sample C2 workload is generated in seconds.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+
+from . import _capi as capi
+from .batch import ReadBatch
+
+
+@dataclass
+class SynthConfig:
+    n_reads: int = 100
+    median_samples: int = 10000      # per read, log-normal
+    sigma_len: float = 0.3
+    min_samples: int = 2000
+    max_samples: int = 40000
+    stride: int = 6
+    mean_dwell_strides: float = 5.0  # mean samples/base = stride * this
+    max_dwell_strides: int = 24
+    mode: int = capi.PGM_MODE_MOVES_CHAR
+    rna_orientation: bool = False    # ss records with target_start > target_end
+    digitisation: float = 8192.0
+    range_: float = 1467.61
+    offset_lo: int = -20
+    offset_hi: int = 30
+    level_mean: float = 90.0
+    level_sd: float = 15.0
+    noise_sd: float = 3.0
+    spike_frac: float = 0.001        # samples pushed outside [pa_min, pa_max]
+    level_k: int = 5
+    p_del: float = 0.0               # ss: probability that a target base is deleted
+    p_ins: float = 0.0               # ss: probability of an insertion token before a match
+    trim_max: int = 0                # moves: trim_offset ~ U[0, trim_max]
+    slice_max: int = 0               # ss: st_k ~ U[0, slice_max]
+    short_read_frac: float = 0.0     # moves: fraction of reads with < 10 bases
+    n_frac: float = 0.0              # fraction of bases replaced by 'N'
+    seed: int = 0x5EED
+
+
+def _lengths(cfg: SynthConfig, rng) -> np.ndarray:
+    ln = rng.lognormal(np.log(cfg.median_samples), cfg.sigma_len, cfg.n_reads)
+    return np.clip(ln, cfg.min_samples, cfg.max_samples).astype(np.int64)
+
+
+def make_batch(cfg: SynthConfig) -> ReadBatch:
+    rng = np.random.default_rng(cfg.seed)
+    R = cfg.n_reads
+    target = _lengths(cfg, rng)
+    spb = cfg.stride * cfg.mean_dwell_strides
+    nb = np.maximum((target / spb).astype(np.int64), 12)                  # bases (=events) per read
+    if cfg.short_read_frac > 0 and cfg.mode != capi.PGM_MODE_SS:
+        short = rng.random(R) < cfg.short_read_frac
+        nb = np.where(short, rng.integers(3, 10, R), nb)
+    B = int(nb.sum())
+    base_off = np.zeros(R + 1, np.int64)
+    np.cumsum(nb, out=base_off[1:])
+    read_of_base = np.repeat(np.arange(R), nb)
+
+    codes = rng.integers(0, 4, B, dtype=np.int64)
+    dwell = np.minimum(rng.geometric(1.0 / cfg.mean_dwell_strides, B), cfg.max_dwell_strides).astype(np.int64)
+    ev_samples = dwell * cfg.stride
+
+    # ---- alignment tokens ----
+    is_ss = cfg.mode == capi.PGM_MODE_SS
+    deleted = np.zeros(B, bool)
+    ins_len = np.zeros(B, np.int64)
+    if is_ss:
+        if cfg.p_del > 0:
+            deleted = rng.random(B) < cfg.p_del
+            deleted[base_off[:-1]] = False
+            deleted[base_off[1:] - 1] = False
+        if cfg.p_ins > 0:
+            ins = (rng.random(B) < cfg.p_ins) & ~deleted
+            ins[base_off[:-1]] = False
+            ins_len = np.where(ins, rng.integers(1, 31, B), 0)
+    sig_per_base = np.where(deleted, 0, ev_samples + ins_len)             # raw samples consumed per target base
+
+    trim = rng.integers(0, cfg.trim_max + 1, R).astype(np.int64) if (cfg.trim_max > 0 and not is_ss) else np.zeros(R, np.int64)
+    qstart = rng.integers(0, 50, R).astype(np.int64) if is_ss else np.zeros(R, np.int64)
+    lead = trim + qstart
+    body = np.add.reduceat(sig_per_base, base_off[:-1])
+    tail = rng.integers(0, cfg.stride, R)
+    raw_len = lead + body + tail
+    raw_off = np.zeros(R + 1, np.int64)
+    # every read starts on a 16-byte boundary (8 samples) in the batch
+    padded = (raw_len + 7) // 8 * 8
+    np.cumsum(padded, out=raw_off[1:])
+    S = int(raw_off[-1])
+
+    # ---- signal ----
+    table = rng.normal(cfg.level_mean, cfg.level_sd, 4 ** cfg.level_k)
+    kid = np.zeros(B, np.int64)
+    for j in range(cfg.level_k):
+        kid = kid * 4 + np.roll(codes, -j)
+    level = table[kid]
+    offset = rng.integers(cfg.offset_lo, cfg.offset_hi + 1, R).astype(np.float64)
+    offset[offset == 0] = 1.0  # slow5lib's ASCII parser rejects "0" when errno is a stale ERANGE (slow5_misc.c:369)
+    scale = cfg.range_ / cfg.digitisation
+    pa = rng.normal(cfg.level_mean, cfg.noise_sd * 2, S).astype(np.float32)   # lead / tail / padding filler
+    # positions of each base's samples
+    base_sig_off = np.zeros(B + 1, np.int64)
+    np.cumsum(sig_per_base, out=base_sig_off[1:])
+    within = base_sig_off[:-1] - base_sig_off[base_off[:-1]][read_of_base]
+    base_start = raw_off[:-1][read_of_base] + lead[read_of_base] + within
+    tot = int(sig_per_base.sum())
+    idx = np.repeat(base_start - base_sig_off[:-1], sig_per_base) + np.arange(tot)
+    pa[idx] = np.repeat(level, sig_per_base).astype(np.float32) + rng.normal(0, cfg.noise_sd, tot).astype(np.float32)
+    if cfg.spike_frac > 0:
+        ns = int(S * cfg.spike_frac)
+        sp = rng.integers(0, S, ns)
+        pa[sp] = np.where(rng.random(ns) < 0.5, 15.0, 230.0).astype(np.float32)
+    off_s = np.repeat(offset, padded).astype(np.float32)
+    raw = np.clip(np.rint(pa / np.float32(scale) - off_s), -32768, 32767).astype(np.int16)
+    del pa, off_s, idx
+
+    # ---- bases ----
+    alpha = np.frombuffer(b"ACGT", np.uint8)
+    chars = alpha[codes]
+    if cfg.n_frac > 0:
+        chars = np.where(rng.random(B) < cfg.n_frac, np.uint8(ord("N")), chars)
+
+    reads = np.zeros(R, np.dtype(capi.READ_DTYPE))
+    reads["raw_off"] = raw_off[:-1]
+    reads["raw_len"] = raw_len
+    reads["digitisation"] = cfg.digitisation
+    reads["offset"] = offset
+    reads["range"] = cfg.range_
+    reads["stride"] = cfg.stride
+    read_ids = [f"read_{cfg.seed & 0xffff:04x}_{i:07d}" for i in range(R)]
+
+    if not is_ss:
+        # move table: '1' then dwell-1 '0's per base
+        M = int(dwell.sum())
+        mv = np.zeros(M, np.uint8)
+        mstart = np.zeros(B + 1, np.int64)
+        np.cumsum(dwell, out=mstart[1:])
+        mv[mstart[:-1]] = 1
+        if cfg.mode == capi.PGM_MODE_MOVES_CHAR:
+            mv = mv + np.uint8(ord("0"))
+        reads["align_off"] = mstart[base_off[:-1]]
+        reads["align_len"] = mstart[base_off[1:]] - mstart[base_off[:-1]]
+        reads["seq_off"] = base_off[:-1]
+        reads["seq_len"] = nb
+        reads["fastq_len"] = nb
+        reads["trim"] = trim
+        return ReadBatch(cfg.mode, raw, mv, chars, reads, read_ids)
+
+    # ---- ss strings ----
+    # per target base, tokens: [<ins>I] then <n>, ; deleted runs become one <n>D token
+    if cfg.rna_orientation:
+        # events run 3'->5': event j <-> target base nb-1-j. Build tokens in event order by
+        # walking each read's bases backwards.
+        order = (base_off[1:][read_of_base] - 1) - (np.arange(B) - base_off[:-1][read_of_base])
+    else:
+        order = np.arange(B)
+    del_o, ins_o, evs_o = deleted[order], ins_len[order], ev_samples[order]
+    prev_del = np.concatenate(([False], del_o[:-1]))
+    prev_del[base_off[:-1]] = False
+    run_start = del_o & ~prev_del
+    # length of each deletion run
+    run_id = np.cumsum(run_start) - 1
+    run_len = np.bincount(run_id[del_o], minlength=int(run_start.sum())) if del_o.any() else np.zeros(0, np.int64)
+    pieces: List[np.ndarray] = []
+    tok_read: List[np.ndarray] = []
+    tok_key: List[np.ndarray] = []
+    pos = np.arange(B)
+    # insertion tokens (key = 3*pos), match tokens (3*pos+1), deletion tokens (3*pos+2 at run start)
+    mi = ins_o > 0
+    if mi.any():
+        pieces.append(np.char.add(ins_o[mi].astype(str), "I")); tok_read.append(read_of_base[mi]); tok_key.append(3 * pos[mi])
+    mm = ~del_o
+    pieces.append(np.char.add(evs_o[mm].astype(str), ",")); tok_read.append(read_of_base[mm]); tok_key.append(3 * pos[mm] + 1)
+    if run_start.any():
+        pieces.append(np.char.add(run_len.astype(str), "D")); tok_read.append(read_of_base[run_start]); tok_key.append(3 * pos[run_start] + 2)
+    toks = np.concatenate(pieces)
+    tr = np.concatenate(tok_read)
+    tk = np.concatenate(tok_key)
+    o = np.argsort(tk, kind="stable")
+    toks, tr = toks[o], tr[o]
+    tcount = np.bincount(tr, minlength=R)
+    toff = np.zeros(R + 1, np.int64)
+    np.cumsum(tcount, out=toff[1:])
+    ss_list = ["".join(toks[toff[i]:toff[i + 1]]) for i in range(R)]
+    ss_len = np.array([len(s) for s in ss_list], np.int64)
+    ss_off = np.zeros(R + 1, np.int64)
+    np.cumsum(ss_len, out=ss_off[1:])
+    align = np.frombuffer("".join(ss_list).encode(), np.uint8)
+
+    st_k = rng.integers(0, cfg.slice_max + 1, R).astype(np.int64) if cfg.slice_max > 0 else np.zeros(R, np.int64)
+    reads["align_off"] = ss_off[:-1]
+    reads["align_len"] = ss_len
+    reads["seq_off"] = base_off[:-1]
+    reads["seq_len"] = nb                      # the fetched slice [st_k, end_k)
+    reads["fastq_len"] = nb
+    reads["query_start"] = qstart
+    reads["st_k"] = st_k
+    reads["end_k"] = st_k + nb
+    reads["flags"] = capi.PGM_READ_RNA if cfg.rna_orientation else 0
+    return ReadBatch(cfg.mode, raw, align, chars, reads, read_ids)
+
+
+# ---------------------------------------------------------------------------------------------
+# File forms of a batch, for the reference CLI (`poregen gmove reads.slow5 <alignment> out`).
+# ---------------------------------------------------------------------------------------------
+
+_SLOW5_HDR = (
+    "#slow5_version\t0.2.0\n#num_read_groups\t1\n@asic_id\tsynthetic\n@sample_frequency\t4000\n"
+    "#char*\tuint32_t\tdouble\tdouble\tdouble\tdouble\tuint64_t\tint16_t*\n"
+    "#read_id\tread_group\tdigitisation\toffset\trange\tsampling_rate\tlen_raw_signal\traw_signal\n")
+
+
+def _fmt_g(x: float) -> str:
+    return repr(float(x)) if float(x) != int(x) else str(int(x))
+
+
+def write_slow5(batch: ReadBatch, path: str) -> None:
+    """ASCII SLOW5 (slow5lib reads it and builds the .idx on first open)."""
+    with open(path, "w") as f:
+        f.write(_SLOW5_HDR)
+        for i, rid in enumerate(batch.read_ids):
+            r = batch.reads[i]
+            sig = batch.raw[int(r["raw_off"]):int(r["raw_off"]) + int(r["raw_len"])]
+            f.write(f"{rid}\t0\t{_fmt_g(r['digitisation'])}\t{_fmt_g(r['offset'])}\t{_fmt_g(r['range'])}\t4000\t{int(r['raw_len'])}\t")
+            f.write(",".join(map(str, sig.tolist())))
+            f.write("\n")
+
+
+def _seq(batch: ReadBatch, i: int) -> str:
+    r = batch.reads[i]
+    return batch.bases[int(r["seq_off"]):int(r["seq_off"]) + int(r["seq_len"])].tobytes().decode()
+
+
+def _align(batch: ReadBatch, i: int) -> np.ndarray:
+    r = batch.reads[i]
+    return batch.align[int(r["align_off"]):int(r["align_off"]) + int(r["align_len"])]
+
+
+def write_alignment(batch: ReadBatch, outdir: str) -> dict:
+    """Writes the alignment in the form matching batch.mode; returns {'align': path, 'fastq': path|None}."""
+    os.makedirs(outdir, exist_ok=True)
+    res = {"fastq": None}
+    if batch.mode == capi.PGM_MODE_MOVES_CHAR:
+        p = os.path.join(outdir, "moves.tsv")
+        with open(p, "w") as f:
+            for i, rid in enumerate(batch.read_ids):
+                r = batch.reads[i]
+                f.write(f"{rid}\t{int(r['fastq_len'])}\t{_seq(batch, i)}\t{int(r['stride'])}\t"
+                        f"{_align(batch, i).tobytes().decode()}\t{int(r['raw_len'])}\t{int(r['trim'])}\n")
+        res["align"] = p
+    elif batch.mode == capi.PGM_MODE_MOVES_I8:
+        p = os.path.join(outdir, "moves.sam")
+        with open(p, "w") as f:
+            f.write("@HD\tVN:1.6\tSO:unknown\n@PG\tID:synth\tPN:synth\n")
+            for i, rid in enumerate(batch.read_ids):
+                r = batch.reads[i]
+                mv = ",".join(map(str, _align(batch, i).astype(np.int8).tolist()))
+                s = _seq(batch, i)
+                f.write(f"{rid}\t4\t*\t0\t0\t*\t*\t0\t0\t{s}\t*\tmv:B:c,{int(r['stride'])},{mv}\t"
+                        f"ns:i:{int(r['raw_len'])}\tts:i:{int(r['trim'])}\n")
+        res["align"] = p
+    else:
+        p = os.path.join(outdir, "events.paf")
+        fq = os.path.join(outdir, "reads.fastq")
+        with open(p, "w") as f, open(fq, "w") as g, open(fq + ".fai", "w") as h:
+            off = 0
+            for i, rid in enumerate(batch.read_ids):
+                r = batch.reads[i]
+                st, en = int(r["st_k"]), int(r["end_k"])
+                full = ("ACGT" * (st // 4 + 1))[:st] + _seq(batch, i) + "TTGCA"
+                ts, te = (en, st) if (int(r["flags"]) & capi.PGM_READ_RNA) else (st, en)
+                ss = _align(batch, i).tobytes().decode()
+                f.write(f"{rid}\t{int(r['raw_len'])}\t{int(r['query_start'])}\t{int(r['raw_len'])}\t+\t{rid}\t{len(full)}\t"
+                        f"{ts}\t{te}\t{en - st}\t{en - st}\t255\tss:Z:{ss}\n")
+                hdr = f"@{rid}\n"
+                g.write(hdr + full + "\n+\n" + "I" * len(full) + "\n")
+                h.write(f"{rid}\t{len(full)}\t{off + len(hdr)}\t{len(full)}\t{len(full) + 1}\t{off + len(hdr) + len(full) + 3}\n")
+                off += len(hdr) + 2 * (len(full) + 1) + 2
+        res["align"] = p
+        res["fastq"] = fq
+    return res

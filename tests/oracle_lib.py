@@ -1,0 +1,123 @@
+"""Test-side loader for the CPU oracle (oracle/liboracle.so) and the compiled reference
+(oracle/_ref/poregen_ref). Test infrastructure only."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from poregen_b200 import _capi as capi
+from poregen_b200.batch import GmoveOptions, GmoveResult, ReadBatch, _np_from
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_SO = os.path.join(ORACLE_DIR, "liboracle.so")
+REF_BIN = os.path.join(ORACLE_DIR, "_ref", "poregen_ref")
+
+
+class OracleResult(C.Structure):
+    _fields_ = [
+        ("n_slots", C.c_uint32), ("n_reads", C.c_uint32),
+        ("n_events_examined", C.c_uint64), ("n_events_pass", C.c_uint64),
+        ("n_sel_events", C.c_uint64), ("n_sel_samples", C.c_uint64),
+        ("slot_sel", C.c_void_p), ("slot_total", C.c_void_p),
+        ("ev_len", C.c_void_p), ("ev_read", C.c_void_p), ("ev_start", C.c_void_p),
+        ("samples", C.c_void_p), ("read_flags", C.c_void_p),
+        ("text", C.c_void_p), ("slot_text_off", C.c_void_p),
+    ]
+
+
+def build_oracle() -> str:
+    src = os.path.join(ORACLE_DIR, "gmove_oracle.c")
+    if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(src):
+        subprocess.check_call(["gcc", "-O2", "-g", "-std=c99", "-Wall", "-ffp-contract=off", "-fPIC", "-shared",
+                               src, "-o", ORACLE_SO, "-lm"])
+    return ORACLE_SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build_oracle())
+        _lib.oracle_gmove_batch.argtypes = [C.POINTER(capi.PgmOpts), C.POINTER(capi.PgmBatch), C.c_void_p,
+                                            C.POINTER(OracleResult)]
+        _lib.oracle_gmove_batch.restype = C.c_int
+        _lib.oracle_free_result.argtypes = [C.POINTER(OracleResult)]
+        _lib.oracle_median.argtypes = [C.c_void_p, C.c_size_t]
+        _lib.oracle_median.restype = C.c_double
+        _lib.oracle_mad.argtypes = [C.c_void_p, C.c_size_t, C.c_double]
+        _lib.oracle_mad.restype = C.c_double
+        _lib.oracle_model_row.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        _lib.oracle_model_row.restype = C.c_int
+    return _lib
+
+
+def oracle_run(opts: GmoveOptions, batch: ReadBatch, totals: np.ndarray | None = None) -> GmoveResult:
+    """One pass of the CPU restatement over `batch`; `totals` (uint32[n_slots]) is updated in place."""
+    co, keep = opts.to_c()
+    cb = batch.to_c()
+    if totals is None:
+        totals = np.zeros(co.n_slots, np.uint32)
+    assert totals.dtype == np.uint32 and totals.size == co.n_slots
+    r = OracleResult()
+    rc = lib().oracle_gmove_batch(C.byref(co), C.byref(cb), totals.ctypes.data, C.byref(r))
+    if rc != 0:
+        raise RuntimeError(f"oracle failed rc={rc}")
+    res = GmoveResult.from_c(r, want_text=True)
+    lib().oracle_free_result(C.byref(r))
+    del keep
+    return res
+
+
+def cli_args(opts: GmoveOptions) -> list:
+    """`poregen gmove` option list equivalent to `opts` (order matters: gmove.cpp:285-308)."""
+    a = ["-k", str(opts.kmer_size), "-m", str(opts.sig_move_offset)]
+    if opts.kmer_start_offset:
+        a += ["-s", str(opts.kmer_start_offset)]
+    a += ["--scaling", str(opts.scaling), "--margin", str(opts.signal_print_margin),
+          "--sample_limit", str(opts.sample_limit), "--index_start", str(opts.index_start),
+          "--index_end", str(opts.index_end),
+          "--max_dur", str(opts.max_dur), "--min_dur", str(opts.min_dur), "--pa_min", repr(opts.pa_min),
+          "--pa_max", repr(opts.pa_max), "--kmer_pick_margin", str(opts.kmer_pick_margin)]
+    if opts.rna:
+        a += ["--rna"]
+    if opts.delimit_files:
+        a += ["-d"]
+    return a
+
+
+def run_reference(opts: GmoveOptions, slow5: str, align: str, outdir: str, fastq: str | None = None,
+                  kmer_file: str | None = None, binary: str = REF_BIN) -> dict:
+    """Runs the UNMODIFIED compiled reference; returns {kmer: bytes} for dump/ plus 'freq.txt'."""
+    cmd = [binary, "gmove"] + cli_args(opts)
+    if kmer_file:
+        cmd += ["--kmer_file", kmer_file]
+    if fastq:
+        cmd += ["--fastq", fastq]
+    cmd += [slow5, align, outdir]
+    p = subprocess.run(cmd, capture_output=True)
+    if p.returncode != 0:
+        raise RuntimeError(f"reference failed rc={p.returncode}: {p.stderr.decode()[-2000:]}")
+    out = {}
+    d = os.path.join(outdir, "dump")
+    for name in os.listdir(d):
+        with open(os.path.join(d, name), "rb") as f:
+            out[name] = f.read()
+    with open(os.path.join(outdir, "freq.txt"), "rb") as f:
+        out["freq.txt"] = f.read()
+    return out
+
+
+def result_as_files(opts: GmoveOptions, res: GmoveResult) -> dict:
+    """dump/<kmer> contents and freq.txt as the host writer would produce them (no -d)."""
+    out = {}
+    names = opts.slot_kmers()
+    for s, name in enumerate(names):
+        out[name] = res.slot_text(s)
+    out["freq.txt"] = "".join(f"{n}\t{int(res.slot_total[s])}\n" for s, n in enumerate(names)).encode()
+    return out
