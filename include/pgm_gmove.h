@@ -88,7 +88,7 @@ typedef struct pgm_opts {
                                      dumped range in order (gmove.cpp:395-419); must be unique.   */
 } pgm_opts;
 
-/* One alignment record. 80 bytes. */
+/* One alignment record. 88 bytes, no padding. */
 typedef struct pgm_read {
     uint64_t raw_off;      /* index of the read's first sample in raw[]                           */
     uint64_t align_off;    /* byte offset in align[]                                              */

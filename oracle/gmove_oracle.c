@@ -253,7 +253,7 @@ static void do_ss_record(run_t *R, uint32_t ri, uint8_t *flag) {
     for (uint32_t p = 0; p < ss_len && !bad; p++) {
         char c = ss[p];
         if (c == ',' || c == 'I' || c == 'D') {
-            if (ndig <= 0) { bad = 1; break; }                            /* 834 */
+            if (ndig <= 0 || ndig > 9) { bad = 1; break; }                /* 834, U7 */
             if (c == 'I') { i_raw += num; indel[n_indel++] = (int)(i_k - num_del); }        /* 841-843 */
             else if (c == 'D') { indel[n_indel++] = (int)(i_k - num_del); i_k += num; num_del += num; } /* 844-847 */
             else {                                                         /* 848-857 */
@@ -264,8 +264,7 @@ static void do_ss_record(run_t *R, uint32_t ri, uint8_t *flag) {
             }
             num = 0; ndig = 0;
         } else if (c >= '0' && c <= '9') {
-            if (ndig >= 9) { bad = 1; break; }                            /* U7 */
-            num = num * 10 + (uint64_t)(c - '0'); ndig++;
+            if (ndig < 10) { num = num * 10 + (uint64_t)(c - '0'); ndig++; } /* U7 is decided at the operator */
         } else { bad = 1; break; }                                        /* 867 */
     }
     if (bad) { *flag |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED; goto done; }

@@ -97,7 +97,7 @@ class PgmResult(C.Structure):
     ]
 
 
-# numpy dtype with the same layout as PgmRead (80 bytes, no padding surprises: checked in tests)
+# numpy dtype with the same layout as PgmRead (88 bytes, no padding surprises: checked in tests)
 READ_DTYPE = [
     ("raw_off", "<u8"), ("align_off", "<u8"), ("seq_off", "<u8"),
     ("raw_len", "<u4"), ("align_len", "<u4"), ("seq_len", "<u4"), ("trim", "<u4"),

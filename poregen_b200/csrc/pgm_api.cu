@@ -1,0 +1,543 @@
+// pgm_api.cu — C ABI of the gmove hot path (include/pgm_gmove.h): context, device memory,
+// kernel sequencing. No CPU fallback: every compute entry point needs a live CUDA device.
+//
+// Pipeline of one batch (all on one stream, no host synchronisation until pgm_download):
+//   count: k_read_prep -> [k_oor_check] -> k_decode<COUNT> -> scan(n_pass)
+//   emit : k_decode<EMIT> -> stable radix sort by slot -> k_select_prep -> scans -> k_select
+//          -> scan(sel_len) -> [k_stats] -> k_gather -> totals update -> scalars
+// Element counts that only the device knows (passing / selected events) stay on the device: grids
+// are sized by capacities derived from the batch and the kernels read the counts themselves.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "pgm_decode.cuh"
+#include "pgm_device.cuh"
+#include "pgm_emit.cuh"
+#include "pgm_scan.cuh"
+#include "pgm_sort.cuh"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct Scalars {  // device -> host summary of one batch
+    unsigned long long examined;
+    unsigned long long n_sel_samples;
+    uint32_t n_pass;
+    uint32_t n_sel;
+    uint32_t err_flag;
+    uint32_t pad;
+};
+
+enum State { ST_IDLE = 0, ST_LOADED, ST_COUNTED, ST_EMITTED };
+
+}  // namespace
+
+struct pgm_ctx {
+    pgm_opts opts;
+    std::string kmer_store;
+    DevOpts dopts;
+    int device = 0;
+    int n_sm = 148;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    State state = ST_IDLE;
+    uint64_t launches = 0;
+
+    // per-context persistent device state
+    DBuf lut, consumed, counts, keep, totals_next, bucket_base, sel_base, scalars, dev_misc, gscratch;
+    const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
+
+    // batch (device view) + owned copies
+    DevBatch db{};
+    bool attached = false;
+    DBuf raw, align, bases, reads;
+    uint32_t ev_cap = 0;
+    uint64_t samples_cap = 0;
+
+    // per-record
+    DBuf cal, rflags, n_pass, ev_base, read_has_sel, ss_L, ss_nindel;
+    // events / sort / selection
+    DBuf key, ev_start, ev_len, ev_read, key2, val, val2, hist, blk32, blk64;
+    DBuf sc_start, sc_end, sc_code, sc_indel;
+    DBuf sel_start, sel_len, sel_read, sel_off, samples;
+
+    // pinned host results
+    Scalars *h_scalars = nullptr;
+    DBuf h_slot_sel, h_slot_total, h_ev_len, h_ev_read, h_ev_start, h_samples, h_rflags;
+    // pinned staging for pageable inputs is left to the caller (pass pinned buffers for speed)
+};
+
+namespace {
+
+int fail(pgm_ctx *c, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+
+#define CU(c, call)                                                                                        \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) return fail((c), PGM_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+int ensure(pgm_ctx *c, DBuf &b, size_t bytes) {
+    if (bytes <= b.cap && b.p) return PGM_OK;
+    if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) { b.p = nullptr; return fail(c, PGM_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); }
+    b.cap = want;
+    return PGM_OK;
+}
+
+int ensure_host(pgm_ctx *c, DBuf &b, size_t bytes) {
+    if (bytes <= b.cap && b.p) return PGM_OK;
+    if (b.p) { cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaHostAlloc(&b.p, want, cudaHostAllocDefault);
+    if (e != cudaSuccess) { b.p = nullptr; return fail(c, PGM_ERR_NOMEM, "cudaHostAlloc(%zu) failed: %s", want, cudaGetErrorString(e)); }
+    b.cap = want;
+    return PGM_OK;
+}
+
+void release(DBuf &b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+void release_host(DBuf &b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
+
+template <typename T> T *P(DBuf &b) { return reinterpret_cast<T *>(b.p); }
+
+#define RET(x) do { int rc_ = (x); if (rc_ != PGM_OK) return rc_; } while (0)
+
+inline uint32_t cdiv(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
+
+// Device-wide exclusive scan. n_cap sizes the grid; n_ptr (nullable) holds the real count.
+template <typename TIn, typename TOut>
+int scan(pgm_ctx *c, const TIn *in, TOut *out, uint64_t n_cap, const uint32_t *n_ptr, bool write_total, DBuf &blk) {
+    if (n_cap == 0) {
+        if (write_total) CU(c, cudaMemsetAsync(out, 0, sizeof(TOut), c->stream));
+        return PGM_OK;
+    }
+    const uint32_t nb = cdiv(n_cap, SCAN_TILE);
+    RET(ensure(c, blk, (size_t)nb * sizeof(TOut)));
+    TOut *bs = reinterpret_cast<TOut *>(blk.p);
+    k_scan_reduce<TIn, TOut><<<nb, PGM_BLOCK, 0, c->stream>>>(in, n_cap, n_ptr, bs);
+    k_scan_top<TOut><<<1, PGM_BLOCK, 0, c->stream>>>(bs, nb, (TOut *)nullptr);
+    k_scan_down<TIn, TOut><<<nb, PGM_BLOCK, 0, c->stream>>>(in, n_cap, n_ptr, bs, out, write_total ? 1 : 0);
+    c->launches += 3;
+    CU(c, cudaGetLastError());
+    return PGM_OK;
+}
+
+uint32_t bit_length(uint32_t x) { uint32_t b = 0; while (x) { b++; x >>= 1; } return b; }
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+int pgm_abi_version(void) { return PGM_ABI_VERSION; }
+
+const char *pgm_last_error(const pgm_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+void pgm_destroy(pgm_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->totals_next, &c->bucket_base, &c->sel_base, &c->scalars,
+                   &c->dev_misc, &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
+                   &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
+                   &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
+                   &c->sc_indel, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples};
+    for (DBuf *b : dev) release(*b);
+    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags};
+    for (DBuf *b : host) release_host(*b);
+    if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
+    if (!opts || !out) return fail(nullptr, PGM_ERR_ARG, "pgm_create: null argument");
+    *out = nullptr;
+    if (opts->kmer_size < 1 || opts->kmer_size > 15) return fail(nullptr, PGM_ERR_ARG, "kmer_size %u outside 1..15", opts->kmer_size);
+    if (opts->n_slots < 1) return fail(nullptr, PGM_ERR_ARG, "n_slots must be >= 1");
+    if (opts->scaling > 1) return fail(nullptr, PGM_ERR_ARG, "scaling must be 0 or 1");
+    if (opts->output != PGM_OUT_F64) return fail(nullptr, PGM_ERR_ARG, "output kind %u not supported in this build", opts->output);
+    const uint64_t n_ids = 1ull << (2 * opts->kmer_size);
+    if (!opts->kmer_list && (uint64_t)opts->index_lo + opts->n_slots > n_ids)
+        return fail(nullptr, PGM_ERR_ARG, "k-mer window [%u,+%u) exceeds 4^k", opts->index_lo, opts->n_slots);
+    if (opts->kmer_list && opts->kmer_size > 12) return fail(nullptr, PGM_ERR_ARG, "--kmer_file lists need kmer_size <= 12");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, PGM_ERR_CUDA, "no CUDA device (%s); the gmove hot path has no CPU fallback", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(nullptr, PGM_ERR_ARG, "device %d out of range (have %d)", device, ndev);
+    cudaDeviceProp prop;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess)
+        return fail(nullptr, PGM_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    if (prop.major != 10) return fail(nullptr, PGM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+
+    pgm_ctx *c = new pgm_ctx();
+    c->opts = *opts;
+    c->device = device;
+    c->n_sm = prop.multiProcessorCount;
+    if (stream) { c->stream = (cudaStream_t)stream; c->own_stream = false; }
+    else {
+        if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+            delete c;
+            return fail(nullptr, PGM_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+        }
+        c->own_stream = true;
+    }
+    DevOpts &d = c->dopts;
+    memset(&d, 0, sizeof d);
+    d.k = opts->kmer_size; d.m = opts->sig_move_offset; d.s_off = opts->kmer_start_offset; d.margin = opts->signal_print_margin;
+    d.limit = opts->sample_limit; d.max_dur = opts->max_dur; d.min_dur = opts->min_dur; d.pick_margin = opts->kmer_pick_margin;
+    d.scaling = opts->scaling; d.n_slots = opts->n_slots; d.index_lo = opts->index_lo;
+    d.pa_min = opts->pa_min; d.pa_max = opts->pa_max;
+    d.fourth = opts->flag_rna ? 'U' : 'T';
+    int rc = PGM_OK;
+    auto bail = [&](int code) { std::string m = c->err; pgm_destroy(c); g_create_error = m; return code; };
+    if (opts->kmer_list) {
+        // --kmer_file: the list is verbatim text (gmove.cpp:406-414). Lines made of A,C,G and ONE of
+        // T/U get a LUT entry; any other line can never equal a substring of an ACGT/ACGU sequence
+        // and simply keeps count 0 (documented limitation: 'N' or mixed T/U lines do not match).
+        c->kmer_store.assign(opts->kmer_list, (size_t)opts->n_slots * opts->kmer_size);
+        c->opts.kmer_list = c->kmer_store.data();
+        bool has_u = c->kmer_store.find('U') != std::string::npos, has_t = c->kmer_store.find('T') != std::string::npos;
+        d.fourth = (has_u && !has_t) ? 'U' : (has_t ? 'T' : (opts->flag_rna ? 'U' : 'T'));
+        std::vector<uint32_t> lut(n_ids, PGM_INVALID);
+        for (uint32_t s = 0; s < opts->n_slots; s++) {
+            uint32_t id = 0; bool ok = true;
+            for (uint32_t j = 0; j < opts->kmer_size; j++) {
+                const char ch = c->kmer_store[(size_t)s * opts->kmer_size + j];
+                uint32_t code = ch == 'A' ? 0 : ch == 'C' ? 1 : ch == 'G' ? 2 : ((uint32_t)ch == d.fourth) ? 3 : 0xFF;
+                if (code == 0xFF) { ok = false; break; }
+                id = (id << 2) | code;
+            }
+            if (!ok) continue;
+            if (lut[id] != PGM_INVALID) { c->err = "duplicate k-mer in kmer_list"; return bail(PGM_ERR_ARG); }
+            lut[id] = s;
+        }
+        if ((rc = ensure(c, c->lut, n_ids * 4)) != PGM_OK) return bail(rc);
+        if (cudaMemcpy(c->lut.p, lut.data(), n_ids * 4, cudaMemcpyHostToDevice) != cudaSuccess) { c->err = "LUT upload failed"; return bail(PGM_ERR_CUDA); }
+        d.use_lut = 1; d.lut = P<uint32_t>(c->lut);
+    }
+    const size_t sb = (size_t)opts->n_slots * 4;
+    DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep, &c->totals_next};
+    for (DBuf *b : slotbufs) if ((rc = ensure(c, *b, sb)) != PGM_OK) return bail(rc);
+    if ((rc = ensure(c, c->bucket_base, sb + 4)) != PGM_OK || (rc = ensure(c, c->sel_base, sb + 4)) != PGM_OK) return bail(rc);
+    if ((rc = ensure(c, c->scalars, sizeof(Scalars))) != PGM_OK || (rc = ensure(c, c->dev_misc, 64)) != PGM_OK) return bail(rc);
+    if (cudaMemset(c->consumed.p, 0, sb) != cudaSuccess) { c->err = "memset failed"; return bail(PGM_ERR_CUDA); }
+    if (cudaHostAlloc((void **)&c->h_scalars, sizeof(Scalars), cudaHostAllocDefault) != cudaSuccess) { c->err = "cudaHostAlloc failed"; return bail(PGM_ERR_NOMEM); }
+    *out = c;
+    return PGM_OK;
+}
+
+int pgm_reset(pgm_ctx *c) {
+    if (!c) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemsetAsync(c->consumed.p, 0, (size_t)c->opts.n_slots * 4, c->stream));
+    c->user_prior = c->user_consumed = nullptr;
+    c->state = ST_IDLE;
+    return PGM_OK;
+}
+
+void *pgm_stream(pgm_ctx *c) { return c ? (void *)c->stream : nullptr; }
+uint64_t pgm_launch_count(const pgm_ctx *c) { return c ? c->launches : 0; }
+
+int pgm_sync(pgm_ctx *c) {
+    if (!c) return PGM_ERR_ARG;
+    CU(c, cudaStreamSynchronize(c->stream));
+    return PGM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
+    if (b->mode > PGM_MODE_MOVES_I8) return fail(c, PGM_ERR_ARG, "unknown batch mode %u", b->mode);
+    if (b->n_align >= (1ull << 32)) return fail(c, PGM_ERR_ARG, "n_align must be < 2^32 per batch");
+    if (b->n_reads && (!b->reads || (b->n_raw && !b->raw) || (b->n_align && !b->align) || (b->n_bases && !b->bases)))
+        return fail(c, PGM_ERR_ARG, "null array in batch");
+    const uint32_t R = b->n_reads;
+    // capacity of the passing-event list: every event consumes >= 1 alignment byte (ss: >= 2) and
+    // needs a k-mer that starts at its own base of the record's sequence.
+    uint64_t cap = (b->mode == PGM_MODE_SS) ? b->n_align / 2 + R : b->n_align;
+    if (b->n_bases < cap) cap = b->n_bases;
+    if (cap >= 0xFFFFFFF0ull) return fail(c, PGM_ERR_ARG, "batch too large: split it");
+    c->ev_cap = (uint32_t)cap;
+    // every selected sample is one raw sample of one event, widened by --margin on both sides
+    c->samples_cap = b->n_raw + 2ull * c->opts.signal_print_margin * cap;
+
+    RET(ensure(c, c->cal, (size_t)R * sizeof(ReadCal)));
+    RET(ensure(c, c->rflags, R));
+    RET(ensure(c, c->n_pass, (size_t)R * 4));
+    RET(ensure(c, c->ev_base, (size_t)(R + 1) * 4));
+    RET(ensure(c, c->read_has_sel, R));
+    const size_t e4 = (size_t)cap * 4;
+    DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read};
+    for (DBuf *x : evb) RET(ensure(c, *x, e4));
+    RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
+    const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
+    RET(ensure(c, c->hist, (size_t)SORT_MAX_BINS * ntiles * 4));
+    RET(ensure(c, c->samples, (size_t)c->samples_cap * 8));
+    if (b->mode == PGM_MODE_SS) {
+        RET(ensure(c, c->ss_L, (size_t)R * 4));
+        RET(ensure(c, c->ss_nindel, (size_t)R * 4));
+        RET(ensure(c, c->sc_start, (size_t)b->n_align * 4));
+        RET(ensure(c, c->sc_end, (size_t)b->n_align * 4));
+        RET(ensure(c, c->sc_code, (size_t)b->n_align));
+        RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4));
+    }
+    if (c->opts.scaling) RET(ensure(c, c->gscratch, (size_t)c->n_sm * 4 * 65536 * 4));
+    return PGM_OK;
+}
+
+int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
+    if (!c || !b) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    RET(prepare_batch(c, b));
+    RET(ensure(c, c->raw, (size_t)b->n_raw * 2 + 32));
+    RET(ensure(c, c->align, (size_t)b->n_align + 32));
+    RET(ensure(c, c->bases, (size_t)b->n_bases + 32));
+    RET(ensure(c, c->reads, (size_t)b->n_reads * sizeof(pgm_read)));
+    if (b->n_raw) CU(c, cudaMemcpyAsync(c->raw.p, b->raw, (size_t)b->n_raw * 2, cudaMemcpyHostToDevice, c->stream));
+    if (b->n_align) CU(c, cudaMemcpyAsync(c->align.p, b->align, (size_t)b->n_align, cudaMemcpyHostToDevice, c->stream));
+    if (b->n_bases) CU(c, cudaMemcpyAsync(c->bases.p, b->bases, (size_t)b->n_bases, cudaMemcpyHostToDevice, c->stream));
+    if (b->n_reads) CU(c, cudaMemcpyAsync(c->reads.p, b->reads, (size_t)b->n_reads * sizeof(pgm_read), cudaMemcpyHostToDevice, c->stream));
+    c->db.n_reads = b->n_reads; c->db.mode = b->mode; c->db.n_raw = b->n_raw; c->db.n_align = b->n_align; c->db.n_bases = b->n_bases;
+    c->db.raw = P<int16_t>(c->raw); c->db.align = P<uint8_t>(c->align); c->db.bases = P<uint8_t>(c->bases); c->db.reads = P<pgm_read>(c->reads);
+    c->attached = false;
+    c->state = ST_LOADED;
+    return PGM_OK;
+}
+
+int pgm_attach_device(pgm_ctx *c, const pgm_batch *b) {
+    if (!c || !b) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    if (((uintptr_t)b->raw & 15) != 0) return fail(c, PGM_ERR_ARG, "device raw[] must be 16-byte aligned");
+    RET(prepare_batch(c, b));
+    c->db.n_reads = b->n_reads; c->db.mode = b->mode; c->db.n_raw = b->n_raw; c->db.n_align = b->n_align; c->db.n_bases = b->n_bases;
+    c->db.raw = b->raw; c->db.align = b->align; c->db.bases = b->bases; c->db.reads = b->reads;
+    c->attached = true;
+    c->state = ST_LOADED;
+    return PGM_OK;
+}
+
+static DecodeIO make_io(pgm_ctx *c) {
+    DecodeIO io;
+    memset(&io, 0, sizeof io);
+    io.consumed = P<uint32_t>(c->consumed);
+    io.counts = P<uint32_t>(c->counts);
+    io.n_pass = P<uint32_t>(c->n_pass);
+    io.ev_base = P<uint32_t>(c->ev_base);
+    io.ev_cap = c->ev_cap;
+    io.key = P<uint32_t>(c->key); io.ev_start = P<uint32_t>(c->ev_start); io.ev_len = P<uint32_t>(c->ev_len); io.ev_read = P<uint32_t>(c->ev_read);
+    io.rflags = P<uint8_t>(c->rflags);
+    io.examined = &P<Scalars>(c->scalars)->examined;
+    io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end); io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
+    io.ss_L = P<uint32_t>(c->ss_L); io.ss_nindel = P<uint32_t>(c->ss_nindel);
+    return io;
+}
+
+int pgm_count(pgm_ctx *c) {
+    if (!c) return PGM_ERR_ARG;
+    if (c->state != ST_LOADED) return fail(c, PGM_ERR_STATE, "pgm_count needs pgm_upload/pgm_attach_device first");
+    CU(c, cudaSetDevice(c->device));
+    const uint32_t R = c->db.n_reads;
+    cudaStream_t st = c->stream;
+    CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
+    CU(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(Scalars), st));
+    CU(c, cudaMemsetAsync(c->dev_misc.p, 0, 64, st));
+    c->user_prior = c->user_consumed = nullptr;
+    DevOpts d = c->dopts;
+    d.mode = c->db.mode;
+    if (R) {
+        CU(c, cudaMemsetAsync(c->read_has_sel.p, 0, R, st));
+        k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &P<Scalars>(c->scalars)->err_flag);
+        c->launches++;
+        if (c->db.mode == PGM_MODE_MOVES_I8) { k_oor_check<<<R, PGM_BLOCK, 0, st>>>(c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags)); c->launches++; }
+        DecodeIO io = make_io(c);
+        if (c->db.mode == PGM_MODE_SS) k_decode_ss<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+        else k_decode_moves<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->n_pass), P<uint32_t>(c->ev_base), R, nullptr, true, c->blk32)));
+    c->state = ST_COUNTED;
+    return PGM_OK;
+}
+
+int pgm_counts_device(pgm_ctx *c, uint32_t **counts_dev) {
+    if (!c || !counts_dev) return PGM_ERR_ARG;
+    *counts_dev = P<uint32_t>(c->counts);
+    return PGM_OK;
+}
+int pgm_totals_device(pgm_ctx *c, uint32_t **consumed_dev) {
+    if (!c || !consumed_dev) return PGM_ERR_ARG;
+    *consumed_dev = P<uint32_t>(c->consumed);
+    return PGM_OK;
+}
+int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consumed_dev) {
+    if (!c || !prior_dev || !consumed_dev) return PGM_ERR_ARG;
+    if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_set_prior belongs between pgm_count and pgm_emit");
+    c->user_prior = prior_dev; c->user_consumed = consumed_dev;
+    return PGM_OK;
+}
+
+// gathers the device-side counts of one batch into the Scalars block
+__global__ void k_collect(const uint32_t *ev_base, uint32_t R, const uint32_t *sel_base, uint32_t n_slots, const uint64_t *sel_off, Scalars *s) {
+    const uint32_t ns = sel_base[n_slots];
+    s->n_pass = ev_base[R];
+    s->n_sel = ns;
+    s->n_sel_samples = sel_off[ns];
+}
+
+int pgm_emit(pgm_ctx *c) {
+    if (!c) return PGM_ERR_ARG;
+    if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_emit needs pgm_count first");
+    CU(c, cudaSetDevice(c->device));
+    const uint32_t R = c->db.n_reads, NS = c->opts.n_slots;
+    cudaStream_t st = c->stream;
+    DevOpts d = c->dopts;
+    d.mode = c->db.mode;
+    const uint32_t *n_ev = P<uint32_t>(c->ev_base) + R;  // device scalar: passing events
+    const uint32_t pgrid = (uint32_t)c->n_sm * 8;
+    uint32_t *skey = P<uint32_t>(c->key), *sval = nullptr;
+    if (R && c->ev_cap) {
+        DecodeIO io = make_io(c);
+        if (c->db.mode == PGM_MODE_SS) k_decode_ss<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+        else k_decode_moves<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+        c->launches++;
+        // stable LSD radix sort of (slot, event index)
+        const uint32_t bits = bit_length(NS - 1);
+        const uint32_t passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
+        const uint32_t per = bits ? (bits + passes - 1) / passes : 1;
+        const uint32_t ntiles = cdiv(c->ev_cap, SORT_TILE);
+        const uint32_t sgrid = ntiles < pgrid ? ntiles : pgrid;
+        uint32_t *kin = P<uint32_t>(c->key), *kout = P<uint32_t>(c->key2);
+        uint32_t *vin = nullptr, *vout = P<uint32_t>(c->val);
+        for (uint32_t p = 0; p < passes; p++) {
+            const uint32_t shift = p * per;
+            k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
+            c->launches++;
+            RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->hist), P<uint32_t>(c->hist), (uint64_t)(1u << per) * ntiles, nullptr, false, c->blk32)));
+            k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
+            c->launches++;
+            // ping-pong: keys key<->key2, values val<->val2
+            uint32_t *t = kin; kin = kout; kout = t;
+            vin = vout; vout = (vout == P<uint32_t>(c->val)) ? P<uint32_t>(c->val2) : P<uint32_t>(c->val);
+        }
+        skey = kin; sval = vin;
+        CU(c, cudaGetLastError());
+    }
+    // quota
+    const uint32_t *prior = c->user_prior ? c->user_prior : P<uint32_t>(c->consumed);
+    k_select_prep<<<cdiv(NS, PGM_BLOCK), PGM_BLOCK, 0, st>>>(NS, c->opts.sample_limit, prior, P<uint32_t>(c->counts), P<uint32_t>(c->keep),
+                                                            c->user_consumed ? nullptr : P<uint32_t>(c->totals_next));
+    c->launches++;
+    RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->counts), P<uint32_t>(c->bucket_base), NS, nullptr, true, c->blk32)));
+    RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->keep), P<uint32_t>(c->sel_base), NS, nullptr, true, c->blk32)));
+    const uint32_t *n_sel = P<uint32_t>(c->sel_base) + NS;
+    if (R && c->ev_cap) {
+        SelectIO sio;
+        sio.n_events = n_ev; sio.skey = skey; sio.sval = sval; sio.bucket_base = P<uint32_t>(c->bucket_base); sio.keep = P<uint32_t>(c->keep);
+        sio.sel_base = P<uint32_t>(c->sel_base); sio.ev_start = P<uint32_t>(c->ev_start); sio.ev_len = P<uint32_t>(c->ev_len); sio.ev_read = P<uint32_t>(c->ev_read);
+        sio.sel_start = P<uint32_t>(c->sel_start); sio.sel_len = P<uint32_t>(c->sel_len); sio.sel_read = P<uint32_t>(c->sel_read);
+        sio.read_has_sel = P<uint8_t>(c->read_has_sel);
+        k_select<<<pgrid, PGM_BLOCK, 0, st>>>(sio);
+        c->launches++;
+    }
+    RET((scan<uint32_t, uint64_t>(c, P<uint32_t>(c->sel_len), P<uint64_t>(c->sel_off), c->ev_cap, n_sel, true, c->blk64)));
+    if (c->ev_cap == 0) CU(c, cudaMemsetAsync(c->sel_off.p, 0, 8, st));
+    if (R && c->ev_cap) {
+        if (c->opts.scaling) {
+            uint32_t *queue = P<uint32_t>(c->dev_misc);
+            k_stats<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), P<uint8_t>(c->read_has_sel), P<ReadCal>(c->cal), queue,
+                                                       P<uint32_t>(c->gscratch));
+            c->launches++;
+        }
+        GatherIO g;
+        g.n_sel = n_sel; g.sel_start = P<uint32_t>(c->sel_start); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
+        g.sel_off = P<uint64_t>(c->sel_off); g.cal = P<ReadCal>(c->cal); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
+        k_gather<<<pgrid, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        c->launches++;
+    }
+    // kmer_frequency_map after this batch
+    CU(c, cudaMemcpyAsync(c->consumed.p, c->user_consumed ? (const void *)c->user_consumed : c->totals_next.p, (size_t)NS * 4, cudaMemcpyDeviceToDevice, st));
+    k_collect<<<1, 1, 0, st>>>(P<uint32_t>(c->ev_base), R, P<uint32_t>(c->sel_base), NS, P<uint64_t>(c->sel_off), P<Scalars>(c->scalars));
+    c->launches++;
+    CU(c, cudaGetLastError());
+    c->state = ST_EMITTED;
+    return PGM_OK;
+}
+
+int pgm_download(pgm_ctx *c, pgm_result *out) {
+    if (!c || !out) return PGM_ERR_ARG;
+    if (c->state != ST_EMITTED) return fail(c, PGM_ERR_STATE, "pgm_download needs pgm_emit first");
+    CU(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint32_t R = c->db.n_reads, NS = c->opts.n_slots;
+    CU(c, cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(Scalars), cudaMemcpyDeviceToHost, st));
+    RET(ensure_host(c, c->h_slot_sel, (size_t)NS * 4));
+    RET(ensure_host(c, c->h_slot_total, (size_t)NS * 4));
+    RET(ensure_host(c, c->h_rflags, R ? R : 1));
+    CU(c, cudaMemcpyAsync(c->h_slot_sel.p, c->keep.p, (size_t)NS * 4, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaMemcpyAsync(c->h_slot_total.p, c->consumed.p, (size_t)NS * 4, cudaMemcpyDeviceToHost, st));
+    if (R) CU(c, cudaMemcpyAsync(c->h_rflags.p, c->rflags.p, R, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+    const Scalars s = *c->h_scalars;
+    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays");
+    if (s.n_pass > c->ev_cap || s.n_sel_samples > c->samples_cap)
+        return fail(c, PGM_ERR_INPUT, "internal capacity exceeded (events %u/%u, samples %llu/%llu)", s.n_pass, c->ev_cap,
+                    s.n_sel_samples, (unsigned long long)c->samples_cap);
+    const size_t ne = s.n_sel, nsamp = (size_t)s.n_sel_samples;
+    RET(ensure_host(c, c->h_ev_len, ne * 4 + 4));
+    RET(ensure_host(c, c->h_ev_read, ne * 4 + 4));
+    RET(ensure_host(c, c->h_ev_start, ne * 4 + 4));
+    RET(ensure_host(c, c->h_samples, nsamp * 8 + 8));
+    if (ne) {
+        CU(c, cudaMemcpyAsync(c->h_ev_len.p, c->sel_len.p, ne * 4, cudaMemcpyDeviceToHost, st));
+        CU(c, cudaMemcpyAsync(c->h_ev_read.p, c->sel_read.p, ne * 4, cudaMemcpyDeviceToHost, st));
+        CU(c, cudaMemcpyAsync(c->h_ev_start.p, c->sel_start.p, ne * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (nsamp) CU(c, cudaMemcpyAsync(c->h_samples.p, c->samples.p, nsamp * 8, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+    memset(out, 0, sizeof *out);
+    out->n_slots = NS; out->n_reads = R;
+    out->n_events_examined = s.examined; out->n_events_pass = s.n_pass;
+    out->n_sel_events = ne; out->n_sel_samples = nsamp;
+    out->slot_sel = P<uint32_t>(c->h_slot_sel); out->slot_total = P<uint32_t>(c->h_slot_total);
+    out->ev_len = P<uint32_t>(c->h_ev_len); out->ev_read = P<uint32_t>(c->h_ev_read); out->ev_start = P<uint32_t>(c->h_ev_start);
+    out->samples = P<double>(c->h_samples); out->read_flags = P<uint8_t>(c->h_rflags);
+    out->text = nullptr; out->slot_text_off = nullptr;
+    c->state = ST_IDLE;
+    return PGM_OK;
+}
+
+int pgm_process(pgm_ctx *c, const pgm_batch *host_batch, pgm_result *out) {
+    if (!c || !host_batch || !out) return PGM_ERR_ARG;
+    RET(pgm_upload(c, host_batch));
+    RET(pgm_count(c));
+    RET(pgm_emit(c));
+    return pgm_download(c, out);
+}
+
+}  // extern "C"

@@ -1,0 +1,99 @@
+// pgm_sort.cuh — stable LSD radix sort of (slot key, event index) pairs.
+//
+// This is the "stable counting-sort bucketing of surviving events by k-mer id" of the north star:
+// the passing events are produced in (record, position) order, so a STABLE sort by slot leaves
+// every bucket in exactly the order the reference would have appended to dump/<kmer>
+// (reference gmove.cpp:650-652, 680-685), and rank-in-bucket < remaining quota == "emitted".
+//
+// Per digit pass: per-tile digit histogram -> device-wide exclusive scan (digit-major) -> stable
+// scatter. Inside a tile, stability comes from processing items in (warp, round, lane) order with
+// __match_any_sync peer ranks and per-warp digit counters.
+#pragma once
+#include "pgm_device.cuh"
+
+#define SORT_ITEMS 8
+#define SORT_TILE (PGM_BLOCK * SORT_ITEMS)
+#define SORT_MAX_BITS 8
+#define SORT_MAX_BINS (1 << SORT_MAX_BITS)
+
+__global__ void __launch_bounds__(PGM_BLOCK) k_sort_hist(const uint32_t *keys, const uint32_t *n_ptr, uint32_t shift, uint32_t bits,
+                                                         uint32_t *hist, uint32_t ntiles) {
+    __shared__ uint32_t sm[SORT_MAX_BINS];
+    const uint32_t n = *n_ptr;
+    const uint32_t bins = 1u << bits, mask = bins - 1;
+    for (uint32_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) sm[i] = 0;
+        __syncthreads();
+        const uint32_t base = tile * SORT_TILE;
+        if (base < n) {
+#pragma unroll
+            for (int i = 0; i < SORT_ITEMS; i++) {
+                const uint32_t idx = base + i * PGM_BLOCK + threadIdx.x;
+                if (idx < n) atomicAdd(&sm[(keys[idx] >> shift) & mask], 1u);
+            }
+        }
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) hist[(size_t)i * ntiles + tile] = sm[i];
+    }
+}
+
+// vals_in == nullptr: the value of item i is i (first pass).
+__global__ void __launch_bounds__(PGM_BLOCK) k_sort_scatter(const uint32_t *keys_in, const uint32_t *vals_in, uint32_t *keys_out,
+                                                            uint32_t *vals_out, const uint32_t *n_ptr, uint32_t shift, uint32_t bits,
+                                                            const uint32_t *hist_scanned, uint32_t ntiles) {
+    __shared__ uint32_t wcount[PGM_WARPS][SORT_MAX_BINS];
+    __shared__ uint32_t goff[SORT_MAX_BINS];
+    const uint32_t n = *n_ptr;
+    const uint32_t bins = 1u << bits, mask = bins - 1;
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t used_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < PGM_WARPS * SORT_MAX_BINS; i += PGM_BLOCK) (&wcount[0][0])[i] = 0;
+        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) goff[i] = hist_scanned[(size_t)i * ntiles + tile];
+        __syncthreads();
+        const uint32_t wbase = tile * SORT_TILE + w * (32 * SORT_ITEMS);
+        uint32_t key[SORT_ITEMS], val[SORT_ITEMS], lrank[SORT_ITEMS];
+#pragma unroll
+        for (int rd = 0; rd < SORT_ITEMS; rd++) {
+            const uint32_t idx = wbase + rd * 32 + lane;
+            const bool valid = idx < n;
+            key[rd] = valid ? keys_in[idx] : 0;
+            val[rd] = valid ? (vals_in ? vals_in[idx] : idx) : 0;
+            const uint32_t d = valid ? ((key[rd] >> shift) & mask) : bins;  // invalid lanes form their own group
+            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const uint32_t leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if (valid && lane == leader) {
+                old = wcount[w][d];
+                wcount[w][d] = old + __popc(peers);
+            }
+            old = __shfl_sync(0xffffffffu, old, leader);
+            lrank[rd] = old + __popc(peers & ((1u << lane) - 1));
+            __syncwarp();
+        }
+        __syncthreads();
+        // exclusive scan over warps, per digit
+        for (uint32_t b = threadIdx.x; b < bins; b += PGM_BLOCK) {
+            uint32_t run = 0;
+#pragma unroll
+            for (int ww = 0; ww < PGM_WARPS; ww++) {
+                const uint32_t t = wcount[ww][b];
+                wcount[ww][b] = run;
+                run += t;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int rd = 0; rd < SORT_ITEMS; rd++) {
+            const uint32_t idx = wbase + rd * 32 + lane;
+            if (idx < n) {
+                const uint32_t d = (key[rd] >> shift) & mask;
+                const uint32_t pos = goff[d] + wcount[w][d] + lrank[rd];
+                keys_out[pos] = key[rd];
+                vals_out[pos] = val[rd];
+            }
+        }
+    }
+}

@@ -1,0 +1,127 @@
+"""Python handle on the C ABI (include/pgm_gmove.h) — test/bench plumbing, not a second
+implementation. Every method is a direct call into libpgm_gmove.so; there is no CPU path.
+
+`GmoveEngine.process(batch)` is one pass of the reference's record loop
+(process_move_table_file / _paf / _bam, reference src/gmove.cpp:539-706, 707-975, 1061-1266) over
+`batch`, carrying the per-k-mer totals (kmer_frequency_map) from batch to batch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import _capi as capi
+from .batch import GmoveOptions, GmoveResult, ReadBatch
+
+
+class PgmError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"pgm error {code}: {msg}")
+        self.code = code
+
+
+class GmoveEngine:
+    def __init__(self, opts: GmoveOptions, device: int = 0, stream: Optional[int] = None):
+        self.lib = capi.load()
+        self.opts = opts
+        self._copts, self._keep = opts.to_c()
+        self._ctx = C.c_void_p()
+        rc = self.lib.pgm_create(C.byref(self._copts), device, C.c_void_p(stream or 0), C.byref(self._ctx))
+        if rc != capi.PGM_OK:
+            raise PgmError(rc, self.lib.pgm_last_error(None).decode())
+        self.n_slots = int(self._copts.n_slots)
+        self._batch_keep = None
+
+    # -- lifetime ---------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self.lib.pgm_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _chk(self, rc: int):
+        if rc != capi.PGM_OK:
+            raise PgmError(rc, self.lib.pgm_last_error(self._ctx).decode())
+
+    # -- one-call form (host buffers in, host result out) -------------------------------------
+    def process(self, batch: ReadBatch) -> GmoveResult:
+        cb = batch.to_c()
+        r = capi.PgmResult()
+        self._chk(self.lib.pgm_process(self._ctx, C.byref(cb), C.byref(r)))
+        return GmoveResult.from_c(r, want_text=False)
+
+    # -- split-phase form -----------------------------------------------------------------------
+    def upload(self, batch: ReadBatch):
+        self._batch_keep = batch
+        cb = batch.to_c()
+        self._chk(self.lib.pgm_upload(self._ctx, C.byref(cb)))
+
+    def attach_device(self, cbatch: capi.PgmBatch, keep=None):
+        self._batch_keep = keep
+        self._chk(self.lib.pgm_attach_device(self._ctx, C.byref(cbatch)))
+
+    def count(self):
+        self._chk(self.lib.pgm_count(self._ctx))
+
+    def emit(self):
+        self._chk(self.lib.pgm_emit(self._ctx))
+
+    def download(self) -> GmoveResult:
+        r = capi.PgmResult()
+        self._chk(self.lib.pgm_download(self._ctx, C.byref(r)))
+        return GmoveResult.from_c(r, want_text=False)
+
+    def sync(self):
+        self._chk(self.lib.pgm_sync(self._ctx))
+
+    def reset(self):
+        self._chk(self.lib.pgm_reset(self._ctx))
+
+    def counts_ptr(self) -> int:
+        p = C.c_void_p()
+        self._chk(self.lib.pgm_counts_device(self._ctx, C.byref(p)))
+        return int(p.value)
+
+    def totals_ptr(self) -> int:
+        p = C.c_void_p()
+        self._chk(self.lib.pgm_totals_device(self._ctx, C.byref(p)))
+        return int(p.value)
+
+    def set_prior(self, prior_dev_ptr: int, consumed_dev_ptr: int):
+        self._chk(self.lib.pgm_set_prior(self._ctx, C.c_void_p(prior_dev_ptr), C.c_void_p(consumed_dev_ptr)))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.pgm_stream(self._ctx) or 0)
+
+    @property
+    def launches(self) -> int:
+        return int(self.lib.pgm_launch_count(self._ctx))
+
+
+def quota_exchange(counts_all: np.ndarray, before: np.ndarray, limit: int):
+    """Host-side statement of the multi-GPU quota rule (north star).
+
+    counts_all: [n_ranks, n_slots] passing events per rank in this round (rank order = record order),
+    before:     [n_slots] totals before the round.
+    Returns (prior [n_ranks, n_slots], consumed [n_slots]): prior[g] = before + sum of lower ranks'
+    counts (what rank g must treat as already emitted), consumed = min(limit, before + all counts).
+    """
+    c = counts_all.astype(np.uint64)
+    excl = np.cumsum(c, axis=0) - c
+    prior = np.minimum(before.astype(np.uint64)[None, :] + excl, limit).astype(np.uint32)
+    consumed = np.minimum(before.astype(np.uint64) + c.sum(axis=0), limit).astype(np.uint32)
+    return prior, consumed
