@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py — gmove hot-path benchmark (BASELINE.json metric: signal samples/s and events/s).
+
+A "step" is one full pass of the gmove record loop over the whole C2 workload (configs[1]:
+10,000 synthetic RNA004 reads x ~10k samples, ss records, -k 5 --rna --scaling 1
+--sample_limit 5000 --min_dur 20 --max_dur 40), starting from empty per-k-mer totals.
+
+  value : samples/s, whole job, inputs resident in HBM, timed with CUDA events on the stream the
+          kernels run on, max over ranks.
+  e2e   : the same through the host-buffer C-ABI path (pinned host arrays in, host result out;
+          H2D and D2H inside the timed region).
+  N > 1 : weak scaling. Each rank owns a contiguous range of records (its own C2-sized shard);
+          the only exchange is the all-gather of the per-k-mer count vector + exclusive scan over
+          ranks that fixes every rank's share of sample_limit.
+
+`--impl reference` times the UNMODIFIED reference (oracle/_ref/poregen_ref, single thread: it has
+no other mode) on a bounded prefix of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "gmove signal samples/sec (events/sec alongside)"
+UNIT = "samples/s"
+
+
+def workload_desc(n_reads):
+    return {"workload": "C2 synthetic RNA004 ss records: gmove -k 5 --rna --scaling 1 --sample_limit 5000 --min_dur 20 --max_dur 40 --file_limit 5000",
+            "reads_per_gpu": n_reads, "median_samples_per_read": 10000,
+            "l2": "inputs (200 MB int16 per step) exceed the 126 MB L2; no explicit flush"}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference_arm(args):
+    """Times oracle/_ref/poregen_ref on a bounded prefix of C2 (file form). Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from poregen_b200 import synth, workloads
+    import oracle_lib as ol
+    kind = "reference"
+    binary = ol.REF_BIN
+    if not os.path.exists(binary):
+        kind = "port"
+    n_reads = args.ref_reads
+    cfg, opts = workloads.c2(n_reads=n_reads)
+    batch = synth.make_batch(cfg)
+    n_samples = int(batch.reads["raw_len"].astype("int64").sum())
+    d = tempfile.mkdtemp(prefix="pgm_ref_")
+    times = []
+    examined = None
+    try:
+        if kind == "reference":
+            synth.write_blow5(batch, os.path.join(d, "reads.blow5"))
+            fl = synth.write_alignment(batch, d)
+            for i in range(args.warmup + args.steps):
+                out = os.path.join(d, f"out{i}")
+                t0 = time.perf_counter()
+                ol.run_reference(opts, os.path.join(d, "reads.blow5"), fl["align"], out, fastq=fl["fastq"])
+                dt = time.perf_counter() - t0
+                shutil.rmtree(out, ignore_errors=True)
+                if i >= args.warmup:
+                    times.append(dt)
+        else:
+            for i in range(args.warmup + args.steps):
+                t0 = time.perf_counter()
+                ol.oracle_run(opts, batch)
+                dt = time.perf_counter() - t0
+                if i >= args.warmup:
+                    times.append(dt)
+        examined = int(ol.oracle_run(opts, batch).n_events_examined)
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+    t = sum(times) / len(times)
+    val = n_samples / t
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": workload_desc(n_reads),
+            "events_per_sec": examined / t,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind,
+                             "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples) per step; "
+                                       "reference binary built -O2, end to end incl. BLOW5 read and dump/ text output"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks line of /opt/skills/guides/B200_PROFILING.md, sampled during the timed region."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+class _DevArr:
+    def __init__(self, ptr, n, typestr="<i4"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(stage):
+    """dram bytes per launch of the stage's kernel from the committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(stage)
+        except Exception:
+            return None
+    return None
+
+
+def cpu_baseline_leg(n_reads):
+    """Reference (or oracle port) on a bounded prefix of C2, ~10-30 s of one host core."""
+    from poregen_b200 import synth, workloads
+    import oracle_lib as ol
+    cfg, opts = workloads.c2(n_reads=n_reads)
+    batch = synth.make_batch(cfg)
+    n_samples = int(batch.reads["raw_len"].astype("int64").sum())
+    if os.path.exists(ol.REF_BIN):
+        d = tempfile.mkdtemp(prefix="pgm_cpu_")
+        try:
+            synth.write_blow5(batch, os.path.join(d, "reads.blow5"))
+            fl = synth.write_alignment(batch, d)
+            t0 = time.perf_counter()
+            ol.run_reference(opts, os.path.join(d, "reads.blow5"), fl["align"], os.path.join(d, "out"), fastq=fl["fastq"])
+            dt = time.perf_counter() - t0
+        finally:
+            shutil.rmtree(d, ignore_errors=True)
+        kind = "reference"
+        what = "unmodified reference binary (-O2), end to end incl. BLOW5 read and dump/ text output"
+    else:
+        t0 = time.perf_counter()
+        ol.oracle_run(opts, batch)
+        dt = time.perf_counter() - t0
+        kind = "port"
+        what = "CPU oracle port (oracle/gmove_oracle.c), in memory, incl. text formatting"
+    return {"value": n_samples / dt, "unit": UNIT, "cores": 1, "kind": kind,
+            "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples, {dt:.1f} s): {what}"}
+
+
+def run_own_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as g
+    from poregen_b200 import _capi as capi, synth, workloads
+    from poregen_b200.batch import ReadBatch
+    from poregen_b200.gmove import GmoveEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the gmove hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        g.build()
+    if world > 1:
+        dist.barrier()
+    capi.load()
+
+    cfg, opts = workloads.c2(n_reads=args.reads, seed=0xC2 + rank)
+    hb = synth.make_batch(cfg)
+    # pinned host copies: the e2e path reads its inputs from pinned memory
+    pin = lambda a: torch.from_numpy(a.view(np.uint8).reshape(-1)).pin_memory()
+    p_raw, p_align, p_bases, p_reads = pin(hb.raw), pin(hb.align), pin(hb.bases), pin(hb.reads)
+    batch = ReadBatch(hb.mode, p_raw.numpy().view(np.int16), p_align.numpy(), p_bases.numpy(),
+                      p_reads.numpy().view(np.dtype(capi.READ_DTYPE)), hb.read_ids)
+    n_samples = int(batch.reads["raw_len"].astype(np.int64).sum())
+    stream = torch.cuda.current_stream()
+    eng = GmoveEngine(opts, device=local, stream=stream.cuda_stream)
+    NS = eng.n_slots
+    limit = opts.sample_limit
+
+    counts_t = None
+    if world > 1:
+        counts_t = torch.as_tensor(_DevArr(eng.counts_ptr(), NS), device=f"cuda:{local}")
+        all_counts = torch.empty((world, NS), dtype=torch.int32, device=f"cuda:{local}")
+
+    def step_resident():
+        eng.reset()
+        eng.count()
+        if world > 1:
+            dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
+            c64 = all_counts.to(torch.int64)
+            excl = torch.cumsum(c64, 0)[rank] - c64[rank]
+            prior = torch.clamp(excl, max=limit).to(torch.int32)
+            consumed = torch.clamp(c64.sum(0), max=limit).to(torch.int32)
+            step_resident.keep = (prior, consumed)
+            eng.set_prior(prior.data_ptr(), consumed.data_ptr())
+        eng.emit()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident (kernel-only) timing
+    eng.upload(batch)
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    res0 = eng.download()               # result of the last warm-up step: counts for the byte model
+    eng.upload(batch)
+    barrier()
+    eng.profile_enable(True)
+    eng.profile_read()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = eng.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    launches = eng.launches - l0
+    stages = eng.profile_read()
+    eng.profile_enable(False)
+    clocks = sampler.stop() if rank == 0 else None
+    t_res = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
+    ms_step = float(t_res.item()) / args.steps
+
+    # ---- end to end: pinned host buffers in, host result out, every step
+    def step_e2e():
+        eng.reset()
+        if world == 1:
+            r = capi.PgmResult()
+            import ctypes as C
+            cb = batch.to_c()
+            eng._chk(eng.lib.pgm_process(eng._ctx, C.byref(cb), C.byref(r)))
+            return r
+        eng.upload(batch)
+        step_resident_no_reset()
+        import ctypes as C
+        r = capi.PgmResult()
+        eng._chk(eng.lib.pgm_download(eng._ctx, C.byref(r)))
+        return r
+
+    def step_resident_no_reset():
+        eng.count()
+        dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
+        c64 = all_counts.to(torch.int64)
+        excl = torch.cumsum(c64, 0)[rank] - c64[rank]
+        prior = torch.clamp(excl, max=limit).to(torch.int32)
+        consumed = torch.clamp(c64.sum(0), max=limit).to(torch.int32)
+        step_resident.keep = (prior, consumed)
+        eng.set_prior(prior.data_ptr(), consumed.data_ptr())
+        eng.emit()
+
+    for _ in range(max(1, args.warmup // 2)):
+        r = step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r = step_e2e()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    t_e2e = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_s = float(t_e2e.item())
+    h2d = int(batch.raw.nbytes + batch.align.nbytes + batch.bases.nbytes + batch.reads.nbytes)
+    d2h = int(r.n_sel_samples * 8 + r.n_sel_events * 12 + NS * 8 + batch.n_reads + 32)
+    examined = int(r.n_events_examined)
+
+    tot = torch.tensor([n_samples, examined, int(r.n_sel_events), int(r.n_sel_samples)], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(tot)
+    tot_samples, tot_events, tot_sel_ev, tot_sel_samp = [float(x) for x in tot.tolist()]
+
+    if rank == 0:
+        # ---- byte model per stage (this rank), DESIGN.md "Kernels and their algorithmic bytes"
+        rd = batch.reads
+        T = int(rd["align_len"].astype(np.int64).sum()); NB = int(rd["seq_len"].astype(np.int64).sum()); R = batch.n_reads
+        E_pass, E_sel, S_sel = int(res0.n_events_pass), int(res0.ev_len.size), int(res0.samples.size)
+        act = np.unique(res0.ev_read)
+        S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
+        alg = {"prep": 120 * R, "decode_count": T + NB + 88 * R, "decode_emit": T + NB + 16 * E_pass,
+               "sort": 16 * E_pass, "select": 8 * E_pass + 12 * E_sel, "stats": 2 * S_act if opts.scaling else 0,
+               "gather": 10 * S_sel + 12 * E_sel, "scan": 4 * R + 12 * E_sel, "misc": 8 * NS}
+        alg_step = 2 * n_samples + T + NB + 24 * R + 8 * S_sel + 12 * E_sel + 4 * NS
+        peak, peak_src = measured_peak()
+        stage_rows = {}
+        for name, (ms, ln) in stages.items():
+            per = ms / args.steps
+            stage_rows[name] = {"ms_per_step": per, "launches_per_step": ln / args.steps,
+                                "algorithmic_bytes": alg.get(name, 0),
+                                "gbs": (alg.get(name, 0) / (per * 1e-3) / 1e9) if per > 0 else None}
+        dom = max(stage_rows, key=lambda k: stage_rows[k]["ms_per_step"])
+        dom_per_launch_ms = stage_rows[dom]["ms_per_step"] / max(1.0, stage_rows[dom]["launches_per_step"])
+        achieved = stage_rows[dom]["gbs"] or 0.0
+        line = {"metric": METRIC, "value": tot_samples / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic", "config": dict(workload_desc(args.reads), parallelism=f"read-range x{world}"),
+                "events_per_sec": tot_events / (ms_step * 1e-3),
+                "events_selected_per_step": tot_sel_ev, "samples_selected_per_step": tot_sel_samp,
+                "e2e": {"value": tot_samples / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "events_per_sec": tot_events / e2e_s,
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak, "traffic": ncu_traffic(dom), "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": stage_rows[dom]["algorithmic_bytes"] / max(1.0, stage_rows[dom]["launches_per_step"]),
+                             "ms_per_launch": dom_per_launch_ms},
+                "roofline_step": {"algorithmic_bytes": alg_step, "gbs": alg_step / (ms_step * 1e-3) / 1e9,
+                                  "frac": alg_step / (ms_step * 1e-3) / 1e9 / peak},
+                "stages": stage_rows, "clocks": clocks}
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline_leg(args.cpu_reads)
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--reads", type=int, default=10000, help="records per GPU (C2 = 10000)")
+    ap.add_argument("--ref-reads", type=int, default=1500, help="--impl reference: records per step")
+    ap.add_argument("--cpu-reads", type=int, default=3000, help="cpu_baseline leg: records in the sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "own":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_own_arm(args)
+
+
+if __name__ == "__main__":
+    main()

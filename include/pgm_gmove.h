@@ -182,11 +182,28 @@ int pgm_set_prior(pgm_ctx *ctx, const uint32_t *prior_dev, const uint32_t *consu
 /* Forget all per-k-mer totals (start a new run with the same options). */
 int pgm_reset(pgm_ctx *ctx);
 
-/* Introspection for benchmarks: the stream (cudaStream_t), kernel launches issued so far, and
- * the algorithmic byte count of the last batch (SURVEY.md §8d formula). */
+/* Introspection for benchmarks: the stream (cudaStream_t) and the number of kernel launches
+ * issued so far. */
 void *pgm_stream(pgm_ctx *ctx);
 uint64_t pgm_launch_count(const pgm_ctx *ctx);
-typedef struct pgm_stage_times { float upload_ms, count_ms, sort_ms, emit_ms, download_ms; } pgm_stage_times;
+
+/* Per-stage device timing with CUDA events on the context's stream (for roofline reporting).
+ * pgm_profile_enable(ctx, 1) starts bracketing every stage with an event pair;
+ * pgm_profile_read synchronises, adds up the elapsed time and launch count of every stage since
+ * the last read into ms[PGM_N_STAGES] / launches[PGM_N_STAGES], and clears the record. */
+#define PGM_STAGE_PREP 0         /* k_read_prep, k_oor_check                                       */
+#define PGM_STAGE_DECODE_COUNT 1 /* k_decode_* <COUNT>                                             */
+#define PGM_STAGE_SCAN 2         /* prefix sums outside the sort                                   */
+#define PGM_STAGE_DECODE_EMIT 3  /* k_decode_* <EMIT>                                              */
+#define PGM_STAGE_SORT 4         /* radix sort passes (histogram, scan, scatter)                   */
+#define PGM_STAGE_SELECT 5       /* k_select_prep, k_select                                        */
+#define PGM_STAGE_STATS 6        /* k_stats (Med-MAD)                                              */
+#define PGM_STAGE_GATHER 7       /* k_gather                                                       */
+#define PGM_STAGE_MISC 8         /* memsets, totals update, k_collect                              */
+#define PGM_N_STAGES 9
+int pgm_profile_enable(pgm_ctx *ctx, int on);
+int pgm_profile_read(pgm_ctx *ctx, float *ms, uint32_t *launches);
+const char *pgm_stage_name(int stage);
 
 #ifdef __cplusplus
 }

@@ -111,7 +111,9 @@ SYMBOLS = [
     "pgm_create", "pgm_destroy", "pgm_last_error", "pgm_abi_version", "pgm_process", "pgm_upload",
     "pgm_attach_device", "pgm_count", "pgm_emit", "pgm_download", "pgm_sync", "pgm_counts_device",
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
+    "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name",
 ]
+PGM_N_STAGES = 9
 
 _lib = None
 
@@ -156,5 +158,11 @@ def load() -> C.CDLL:
     lib.pgm_stream.restype = C.c_void_p
     lib.pgm_launch_count.argtypes = [C.c_void_p]
     lib.pgm_launch_count.restype = C.c_uint64
+    lib.pgm_profile_enable.argtypes = [C.c_void_p, C.c_int]
+    lib.pgm_profile_enable.restype = C.c_int
+    lib.pgm_profile_read.argtypes = [C.c_void_p, P(C.c_float), P(C.c_uint32)]
+    lib.pgm_profile_read.restype = C.c_int
+    lib.pgm_stage_name.argtypes = [C.c_int]
+    lib.pgm_stage_name.restype = C.c_char_p
     _lib = lib
     return lib

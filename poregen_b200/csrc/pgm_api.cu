@@ -79,6 +79,12 @@ struct pgm_ctx {
     Scalars *h_scalars = nullptr;
     DBuf h_slot_sel, h_slot_total, h_ev_len, h_ev_read, h_ev_start, h_samples, h_rflags;
     // pinned staging for pageable inputs is left to the caller (pass pinned buffers for speed)
+
+    // optional per-stage event timing
+    bool prof = false;
+    struct Span { int stage; cudaEvent_t a, b; uint32_t launches; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> ev_pool;
 };
 
 namespace {
@@ -148,6 +154,30 @@ int scan(pgm_ctx *c, const TIn *in, TOut *out, uint64_t n_cap, const uint32_t *n
 
 uint32_t bit_length(uint32_t x) { uint32_t b = 0; while (x) { b++; x >>= 1; } return b; }
 
+// Brackets a pipeline stage with a CUDA event pair on the context's stream when profiling is on.
+struct StageTimer {
+    pgm_ctx *c;
+    int stage;
+    cudaEvent_t a = nullptr, b = nullptr;
+    uint64_t l0;
+    static cudaEvent_t get(pgm_ctx *c) {
+        if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
+    StageTimer(pgm_ctx *c_, int stage_) : c(c_), stage(stage_), l0(c_->launches) {
+        if (!c->prof) return;
+        a = get(c); b = get(c);
+        cudaEventRecord(a, c->stream);
+    }
+    ~StageTimer() {
+        if (!a) return;
+        cudaEventRecord(b, c->stream);
+        c->spans.push_back({stage, a, b, (uint32_t)(c->launches - l0)});
+    }
+};
+
 }  // namespace
 
 // ================================================================================================
@@ -170,6 +200,8 @@ void pgm_destroy(pgm_ctx *c) {
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags};
     for (DBuf *b : host) release_host(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    for (auto &sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -257,7 +289,7 @@ int pgm_reset(pgm_ctx *c) {
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaMemsetAsync(c->consumed.p, 0, (size_t)c->opts.n_slots * 4, c->stream));
     c->user_prior = c->user_consumed = nullptr;
-    c->state = ST_IDLE;
+    if (c->state != ST_IDLE) c->state = ST_LOADED;  // the loaded batch stays usable: count/emit can be re-run
     return PGM_OK;
 }
 
@@ -363,24 +395,36 @@ int pgm_count(pgm_ctx *c) {
     CU(c, cudaSetDevice(c->device));
     const uint32_t R = c->db.n_reads;
     cudaStream_t st = c->stream;
-    CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
-    CU(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(Scalars), st));
-    CU(c, cudaMemsetAsync(c->dev_misc.p, 0, 64, st));
+    {
+        StageTimer t(c, PGM_STAGE_MISC);
+        CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
+        CU(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(Scalars), st));
+        CU(c, cudaMemsetAsync(c->dev_misc.p, 0, 64, st));
+        if (R) CU(c, cudaMemsetAsync(c->read_has_sel.p, 0, R, st));
+    }
     c->user_prior = c->user_consumed = nullptr;
     DevOpts d = c->dopts;
     d.mode = c->db.mode;
     if (R) {
-        CU(c, cudaMemsetAsync(c->read_has_sel.p, 0, R, st));
-        k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &P<Scalars>(c->scalars)->err_flag);
-        c->launches++;
-        if (c->db.mode == PGM_MODE_MOVES_I8) { k_oor_check<<<R, PGM_BLOCK, 0, st>>>(c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags)); c->launches++; }
-        DecodeIO io = make_io(c);
-        if (c->db.mode == PGM_MODE_SS) k_decode_ss<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-        else k_decode_moves<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-        c->launches++;
+        {
+            StageTimer t(c, PGM_STAGE_PREP);
+            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &P<Scalars>(c->scalars)->err_flag);
+            c->launches++;
+            if (c->db.mode == PGM_MODE_MOVES_I8) { k_oor_check<<<R, PGM_BLOCK, 0, st>>>(c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags)); c->launches++; }
+        }
+        {
+            StageTimer t(c, PGM_STAGE_DECODE_COUNT);
+            DecodeIO io = make_io(c);
+            if (c->db.mode == PGM_MODE_SS) k_decode_ss<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            else k_decode_moves<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            c->launches++;
+        }
         CU(c, cudaGetLastError());
     }
-    RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->n_pass), P<uint32_t>(c->ev_base), R, nullptr, true, c->blk32)));
+    {
+        StageTimer t(c, PGM_STAGE_SCAN);
+        RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->n_pass), P<uint32_t>(c->ev_base), R, nullptr, true, c->blk32)));
+    }
     c->state = ST_COUNTED;
     return PGM_OK;
 }
@@ -422,11 +466,15 @@ int pgm_emit(pgm_ctx *c) {
     const uint32_t pgrid = (uint32_t)c->n_sm * 8;
     uint32_t *skey = P<uint32_t>(c->key), *sval = nullptr;
     if (R && c->ev_cap) {
-        DecodeIO io = make_io(c);
-        if (c->db.mode == PGM_MODE_SS) k_decode_ss<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-        else k_decode_moves<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-        c->launches++;
+        {
+            StageTimer t(c, PGM_STAGE_DECODE_EMIT);
+            DecodeIO io = make_io(c);
+            if (c->db.mode == PGM_MODE_SS) k_decode_ss<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            else k_decode_moves<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            c->launches++;
+        }
         // stable LSD radix sort of (slot, event index)
+        StageTimer tsort(c, PGM_STAGE_SORT);
         const uint32_t bits = bit_length(NS - 1);
         const uint32_t passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
         const uint32_t per = bits ? (bits + passes - 1) / passes : 1;
@@ -450,13 +498,20 @@ int pgm_emit(pgm_ctx *c) {
     }
     // quota
     const uint32_t *prior = c->user_prior ? c->user_prior : P<uint32_t>(c->consumed);
-    k_select_prep<<<cdiv(NS, PGM_BLOCK), PGM_BLOCK, 0, st>>>(NS, c->opts.sample_limit, prior, P<uint32_t>(c->counts), P<uint32_t>(c->keep),
-                                                            c->user_consumed ? nullptr : P<uint32_t>(c->totals_next));
-    c->launches++;
-    RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->counts), P<uint32_t>(c->bucket_base), NS, nullptr, true, c->blk32)));
-    RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->keep), P<uint32_t>(c->sel_base), NS, nullptr, true, c->blk32)));
+    {
+        StageTimer t(c, PGM_STAGE_SELECT);
+        k_select_prep<<<cdiv(NS, PGM_BLOCK), PGM_BLOCK, 0, st>>>(NS, c->opts.sample_limit, prior, P<uint32_t>(c->counts), P<uint32_t>(c->keep),
+                                                                c->user_consumed ? nullptr : P<uint32_t>(c->totals_next));
+        c->launches++;
+    }
+    {
+        StageTimer t(c, PGM_STAGE_SCAN);
+        RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->counts), P<uint32_t>(c->bucket_base), NS, nullptr, true, c->blk32)));
+        RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->keep), P<uint32_t>(c->sel_base), NS, nullptr, true, c->blk32)));
+    }
     const uint32_t *n_sel = P<uint32_t>(c->sel_base) + NS;
     if (R && c->ev_cap) {
+        StageTimer t(c, PGM_STAGE_SELECT);
         SelectIO sio;
         sio.n_events = n_ev; sio.skey = skey; sio.sval = sval; sio.bucket_base = P<uint32_t>(c->bucket_base); sio.keep = P<uint32_t>(c->keep);
         sio.sel_base = P<uint32_t>(c->sel_base); sio.ev_start = P<uint32_t>(c->ev_start); sio.ev_len = P<uint32_t>(c->ev_len); sio.ev_read = P<uint32_t>(c->ev_read);
@@ -465,15 +520,19 @@ int pgm_emit(pgm_ctx *c) {
         k_select<<<pgrid, PGM_BLOCK, 0, st>>>(sio);
         c->launches++;
     }
-    RET((scan<uint32_t, uint64_t>(c, P<uint32_t>(c->sel_len), P<uint64_t>(c->sel_off), c->ev_cap, n_sel, true, c->blk64)));
-    if (c->ev_cap == 0) CU(c, cudaMemsetAsync(c->sel_off.p, 0, 8, st));
+    {
+        StageTimer t(c, PGM_STAGE_SCAN);
+        RET((scan<uint32_t, uint64_t>(c, P<uint32_t>(c->sel_len), P<uint64_t>(c->sel_off), c->ev_cap, n_sel, true, c->blk64)));
+    }
     if (R && c->ev_cap) {
         if (c->opts.scaling) {
+            StageTimer t(c, PGM_STAGE_STATS);
             uint32_t *queue = P<uint32_t>(c->dev_misc);
             k_stats<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), P<uint8_t>(c->read_has_sel), P<ReadCal>(c->cal), queue,
                                                        P<uint32_t>(c->gscratch));
             c->launches++;
         }
+        StageTimer t(c, PGM_STAGE_GATHER);
         GatherIO g;
         g.n_sel = n_sel; g.sel_start = P<uint32_t>(c->sel_start); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
         g.sel_off = P<uint64_t>(c->sel_off); g.cal = P<ReadCal>(c->cal); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
@@ -481,6 +540,7 @@ int pgm_emit(pgm_ctx *c) {
         c->launches++;
     }
     // kmer_frequency_map after this batch
+    StageTimer tmisc(c, PGM_STAGE_MISC);
     CU(c, cudaMemcpyAsync(c->consumed.p, c->user_consumed ? (const void *)c->user_consumed : c->totals_next.p, (size_t)NS * 4, cudaMemcpyDeviceToDevice, st));
     k_collect<<<1, 1, 0, st>>>(P<uint32_t>(c->ev_base), R, P<uint32_t>(c->sel_base), NS, P<uint64_t>(c->sel_off), P<Scalars>(c->scalars));
     c->launches++;
@@ -529,6 +589,31 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     out->samples = P<double>(c->h_samples); out->read_flags = P<uint8_t>(c->h_rflags);
     out->text = nullptr; out->slot_text_off = nullptr;
     c->state = ST_IDLE;
+    return PGM_OK;
+}
+
+static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats", "gather", "misc"};
+
+const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }
+
+int pgm_profile_enable(pgm_ctx *c, int on) {
+    if (!c) return PGM_ERR_ARG;
+    c->prof = on != 0;
+    return PGM_OK;
+}
+
+int pgm_profile_read(pgm_ctx *c, float *ms, uint32_t *launches) {
+    if (!c || !ms || !launches) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < PGM_N_STAGES; i++) { ms[i] = 0.f; launches[i] = 0; }
+    for (auto &sp : c->spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) { ms[sp.stage] += t; launches[sp.stage] += sp.launches; }
+        c->ev_pool.push_back(sp.a);
+        c->ev_pool.push_back(sp.b);
+    }
+    c->spans.clear();
     return PGM_OK;
 }
 

@@ -103,6 +103,16 @@ class GmoveEngine:
     def set_prior(self, prior_dev_ptr: int, consumed_dev_ptr: int):
         self._chk(self.lib.pgm_set_prior(self._ctx, C.c_void_p(prior_dev_ptr), C.c_void_p(consumed_dev_ptr)))
 
+    def profile_enable(self, on: bool = True):
+        self._chk(self.lib.pgm_profile_enable(self._ctx, 1 if on else 0))
+
+    def profile_read(self) -> dict:
+        """{stage name: (ms, launches)} accumulated since the last read (synchronises)."""
+        ms = (C.c_float * capi.PGM_N_STAGES)()
+        ln = (C.c_uint32 * capi.PGM_N_STAGES)()
+        self._chk(self.lib.pgm_profile_read(self._ctx, ms, ln))
+        return {self.lib.pgm_stage_name(i).decode(): (float(ms[i]), int(ln[i])) for i in range(capi.PGM_N_STAGES)}
+
     @property
     def stream(self) -> int:
         return int(self.lib.pgm_stream(self._ctx) or 0)

@@ -48,3 +48,58 @@ def test_streamed_batches(built, label, cfg, opts):
             ref = ol.oracle_run(opts, sl, totals)
             res = eng.process(sl)
             assert_same(res, ref, f"{label}[{lo}:{hi}]")
+
+
+def test_two_rank_quota_exchange_on_one_gpu(built):
+    """The multi-GPU rule (all-gather of per-k-mer counts, exclusive scan over ranks) emulated with
+    two contexts on one device: rank 0 owns the first half of the records, rank 1 the second. The
+    concatenation of the two slices must equal the serial oracle run."""
+    import torch
+    from cases import _o
+    from poregen_b200 import _capi as capi
+    from poregen_b200.gmove import quota_exchange
+    from poregen_b200.synth import SynthConfig
+    opts = _o(kmer_size=4, sample_limit=40, scaling=1)
+    batch = synth.make_batch(SynthConfig(n_reads=64, median_samples=4000, seed=77))
+    ref = ol.oracle_run(opts, batch)
+    halves = [batch.slice(0, 32), batch.slice(32, 64)]
+    ns = opts.index_end - opts.index_start + 1
+
+    class Dev:
+        def __init__(self, ptr, n):
+            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 3}
+
+    engs = [GmoveEngine(opts) for _ in halves]
+    try:
+        counts = []
+        for e, h in zip(engs, halves):
+            e.upload(h)
+            e.count()
+            e.sync()
+            counts.append(torch.as_tensor(Dev(e.counts_ptr(), ns), device="cuda").cpu().numpy().astype(np.uint32))
+        prior, consumed = quota_exchange(np.stack(counts), np.zeros(ns, np.uint32), opts.sample_limit)
+        outs = []
+        for g, e in enumerate(engs):
+            p = torch.from_numpy(prior[g].astype(np.int32)).cuda()
+            c = torch.from_numpy(consumed.astype(np.int32)).cuda()
+            e.set_prior(p.data_ptr(), c.data_ptr())
+            e.emit()
+            outs.append(e.download())
+    finally:
+        for e in engs:
+            e.close()
+    np.testing.assert_array_equal(outs[1].slot_total, ref.slot_total)
+    np.testing.assert_array_equal(outs[0].slot_sel + outs[1].slot_sel, ref.slot_sel)
+    # per slot: rank 0's events, then rank 1's
+    ev_len, ev_start, ev_read, samples = [], [], [], []
+    offs = [np.concatenate(([0], np.cumsum(o.slot_sel.astype(np.int64)))) for o in outs]
+    soffs = [np.concatenate(([0], np.cumsum(o.ev_len.astype(np.int64)))) for o in outs]
+    for s in range(ns):
+        for g, o in enumerate(outs):
+            a, b = offs[g][s], offs[g][s + 1]
+            ev_len.append(o.ev_len[a:b]); ev_start.append(o.ev_start[a:b]); ev_read.append(o.ev_read[a:b] + 32 * g)
+            samples.append(o.samples[soffs[g][a]:soffs[g][b]])
+    np.testing.assert_array_equal(np.concatenate(ev_len), ref.ev_len)
+    np.testing.assert_array_equal(np.concatenate(ev_start), ref.ev_start)
+    np.testing.assert_array_equal(np.concatenate(ev_read), ref.ev_read)
+    np.testing.assert_array_equal(np.concatenate(samples).view(np.uint64), ref.samples.view(np.uint64))
