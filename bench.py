@@ -223,12 +223,16 @@ def run_own_arm(args):
     cfg, opts = workloads.c2(n_reads=args.reads, seed=0xC2 + rank)
     hb = synth.make_batch(cfg)
     # pinned host copies: the e2e path reads its inputs from pinned memory
-    pin = lambda a: torch.from_numpy(a.view(np.uint8).reshape(-1)).pin_memory()
+    pin = lambda a: torch.from_numpy(np.array(a, copy=True).view(np.uint8).reshape(-1)).pin_memory()
     p_raw, p_align, p_bases, p_reads = pin(hb.raw), pin(hb.align), pin(hb.bases), pin(hb.reads)
     batch = ReadBatch(hb.mode, p_raw.numpy().view(np.int16), p_align.numpy(), p_bases.numpy(),
                       p_reads.numpy().view(np.dtype(capi.READ_DTYPE)), hb.read_ids)
     n_samples = int(batch.reads["raw_len"].astype(np.int64).sum())
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: handle 0 would make the library create a private stream that
+    # torch's events could not bracket
+    stream = torch.cuda.Stream(device=local)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     eng = GmoveEngine(opts, device=local, stream=stream.cuda_stream)
     NS = eng.n_slots
     limit = opts.sample_limit
