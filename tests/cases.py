@@ -19,7 +19,7 @@ def parity_cases():
             (f"tsv_k5_sc{sc}", SynthConfig(n_reads=60, median_samples=4000, trim_max=40, short_read_frac=0.05, n_frac=0.01, seed=11),
              _o(kmer_size=5, sample_limit=20, scaling=sc)),
             (f"tsv_k9_window_sc{sc}", SynthConfig(n_reads=40, median_samples=6000, stride=5, seed=12),
-             GmoveOptions(kmer_size=9, sample_limit=3, scaling=sc, index_start=1000, index_end=90000, file_limit=89001).resolve_range()),
+             GmoveOptions(kmer_size=9, sample_limit=3, scaling=sc, index_start=1000, index_end=19000, file_limit=18001).resolve_range()),
             (f"sam_k5_sc{sc}", SynthConfig(n_reads=60, median_samples=4000, mode=B, trim_max=40, spike_frac=0.00002, seed=13),
              _o(kmer_size=5, sample_limit=20, scaling=sc)),
             (f"ss_dna_k6_sc{sc}", SynthConfig(n_reads=60, median_samples=4000, mode=S, p_del=0.06, p_ins=0.06, slice_max=7, seed=14),
