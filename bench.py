@@ -347,8 +347,9 @@ def run_own_arm(args):
         act = np.unique(res0.ev_read)
         S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
         alg = {"prep": 120 * R, "decode_count": T + NB + 88 * R, "decode_emit": T + NB + 16 * E_pass,
-               "sort": 16 * E_pass, "select": 8 * E_pass + 12 * E_sel, "stats": 2 * S_act if opts.scaling else 0,
-               "gather": 10 * S_sel + 12 * E_sel, "scan": 4 * R + 12 * E_sel, "misc": 8 * NS}
+               "sort": 16 * E_pass, "select": 8 * E_pass + 12 * E_sel, "stats_wide": 0,
+               "signal": (2 * S_act if opts.scaling else 2 * S_sel) + 8 * S_sel + 12 * E_pass,
+               "scan": 4 * R + 12 * E_sel, "misc": 8 * NS}
         alg_step = 2 * n_samples + T + NB + 24 * R + 8 * S_sel + 12 * E_sel + 4 * NS
         peak, peak_src = measured_peak()
         stage_rows = {}

@@ -21,6 +21,7 @@
 #include "pgm_device.cuh"
 #include "pgm_emit.cuh"
 #include "pgm_scan.cuh"
+#include "pgm_signal.cuh"
 #include "pgm_sort.cuh"
 
 namespace {
@@ -73,7 +74,8 @@ struct pgm_ctx {
     // events / sort / selection
     DBuf key, ev_start, ev_len, ev_read, key2, val, val2, hist, blk32, blk64;
     DBuf sc_start, sc_end, sc_code, sc_indel;
-    DBuf sel_start, sel_len, sel_read, sel_off, samples;
+    DBuf sel_start, sel_len, sel_read, sel_off, samples, ev_out;
+    bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
 
     // pinned host results
     Scalars *h_scalars = nullptr;
@@ -195,7 +197,7 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->dev_misc, &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples};
+                   &c->sc_indel, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags};
     for (DBuf *b : host) release_host(*b);
@@ -324,7 +326,7 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->ev_base, (size_t)(R + 1) * 4));
     RET(ensure(c, c->read_has_sel, R));
     const size_t e4 = (size_t)cap * 4;
-    DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read};
+    DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read, &c->ev_out};
     for (DBuf *x : evb) RET(ensure(c, *x, e4));
     RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
@@ -357,6 +359,15 @@ int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
     c->db.n_reads = b->n_reads; c->db.mode = b->mode; c->db.n_raw = b->n_raw; c->db.n_align = b->n_align; c->db.n_bases = b->n_bases;
     c->db.raw = P<int16_t>(c->raw); c->db.align = P<uint8_t>(c->align); c->db.bases = P<uint8_t>(c->bases); c->db.reads = P<pgm_read>(c->reads);
     c->attached = false;
+    c->need_wide = false;
+    if (c->opts.scaling) {
+        // in-range code span ~ (pa_max - pa_min) / |scale|; anything close to the shared-memory budget goes the wide way
+        const double span = c->opts.pa_max - c->opts.pa_min;
+        for (uint32_t i = 0; i < b->n_reads && !c->need_wide; i++) {
+            const double sc = fabs(b->reads[i].range / b->reads[i].digitisation);
+            if (!(span / sc < (double)(SIG_SMEM_BINS - 8))) c->need_wide = true;
+        }
+    }
     c->state = ST_LOADED;
     return PGM_OK;
 }
@@ -369,6 +380,7 @@ int pgm_attach_device(pgm_ctx *c, const pgm_batch *b) {
     c->db.n_reads = b->n_reads; c->db.mode = b->mode; c->db.n_raw = b->n_raw; c->db.n_align = b->n_align; c->db.n_bases = b->n_bases;
     c->db.raw = b->raw; c->db.align = b->align; c->db.bases = b->bases; c->db.reads = b->reads;
     c->attached = true;
+    c->need_wide = true;
     c->state = ST_LOADED;
     return PGM_OK;
 }
@@ -516,6 +528,7 @@ int pgm_emit(pgm_ctx *c) {
         sio.n_events = n_ev; sio.skey = skey; sio.sval = sval; sio.bucket_base = P<uint32_t>(c->bucket_base); sio.keep = P<uint32_t>(c->keep);
         sio.sel_base = P<uint32_t>(c->sel_base); sio.ev_start = P<uint32_t>(c->ev_start); sio.ev_len = P<uint32_t>(c->ev_len); sio.ev_read = P<uint32_t>(c->ev_read);
         sio.sel_start = P<uint32_t>(c->sel_start); sio.sel_len = P<uint32_t>(c->sel_len); sio.sel_read = P<uint32_t>(c->sel_read);
+        sio.ev_out = P<uint32_t>(c->ev_out);
         sio.read_has_sel = P<uint8_t>(c->read_has_sel);
         k_select<<<pgrid, PGM_BLOCK, 0, st>>>(sio);
         c->launches++;
@@ -525,18 +538,19 @@ int pgm_emit(pgm_ctx *c) {
         RET((scan<uint32_t, uint64_t>(c, P<uint32_t>(c->sel_len), P<uint64_t>(c->sel_off), c->ev_cap, n_sel, true, c->blk64)));
     }
     if (R && c->ev_cap) {
-        if (c->opts.scaling) {
+        if (c->opts.scaling && c->need_wide) {
             StageTimer t(c, PGM_STAGE_STATS);
             uint32_t *queue = P<uint32_t>(c->dev_misc);
-            k_stats<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), P<uint8_t>(c->read_has_sel), P<ReadCal>(c->cal), queue,
-                                                       P<uint32_t>(c->gscratch));
+            k_stats_wide<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), P<uint8_t>(c->read_has_sel), P<ReadCal>(c->cal), queue,
+                                                            P<uint32_t>(c->gscratch));
             c->launches++;
         }
         StageTimer t(c, PGM_STAGE_GATHER);
-        GatherIO g;
-        g.n_sel = n_sel; g.sel_start = P<uint32_t>(c->sel_start); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
-        g.sel_off = P<uint64_t>(c->sel_off); g.cal = P<ReadCal>(c->cal); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
-        k_gather<<<pgrid, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        SignalIO g;
+        g.rflags = P<uint8_t>(c->rflags); g.read_has_sel = P<uint8_t>(c->read_has_sel); g.cal = P<ReadCal>(c->cal);
+        g.ev_base = P<uint32_t>(c->ev_base); g.ev_start = P<uint32_t>(c->ev_start); g.ev_len = P<uint32_t>(c->ev_len); g.ev_out = P<uint32_t>(c->ev_out);
+        g.sel_off = P<uint64_t>(c->sel_off); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
+        k_signal<<<R, PGM_BLOCK, 0, st>>>(d, c->db, g);
         c->launches++;
     }
     // kmer_frequency_map after this batch
@@ -592,7 +606,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     return PGM_OK;
 }
 
-static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats", "gather", "misc"};
+static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats_wide", "signal", "misc"};
 
 const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }
 
