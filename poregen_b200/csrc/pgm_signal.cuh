@@ -62,10 +62,26 @@ __device__ __forceinline__ void stats_histogram(const int16_t *raw, uint64_t fir
     (void)SMEM;
 }
 
+// Shared scratch of stats_medmad.
+struct StatsShared {
+    uint32_t scan[PGM_WARPS + 1];
+    uint32_t idx;      // result of a parallel index search
+    uint32_t found;    // MAD candidate verified
+    double res;        // MAD value
+};
+
+// cumulative count of in-range samples with value index <= x (x may be negative or >= nb)
+__device__ __forceinline__ uint32_t st_cumAt(const StatsCtx &c, int64_t x, uint32_t n_in) {
+    if (x < 0) return 0u;
+    if (x >= (int64_t)c.nb) return n_in;
+    return c.H[st_bin(c, (uint32_t)x)];
+}
+
 // From the histogram in c.H (all threads of the block call this together): turns it into cumulative
-// counts, then computes med and the clamped mad exactly as the reference does. sm_u: PGM_WARPS+1
-// words, sm_res: one double, both shared. Returns the values to every thread.
-__device__ __forceinline__ void stats_medmad(const StatsCtx &c, uint32_t n, uint32_t *sm_u, double *sm_res, double *med_out, double *mad_out) {
+// counts, then computes med and the clamped mad exactly as the reference does. Index searches are
+// done in parallel over the bins with integer compares; the reference's double expression is only
+// evaluated for the handful of bins that can hold the answer.
+__device__ __forceinline__ void stats_medmad(const StatsCtx &c, uint32_t n, StatsShared *sh, double *med_out, double *mad_out) {
     const uint32_t tid = threadIdx.x;
     // ---- histogram -> inclusive cumulative counts, in value order, in place
     uint32_t carry = 0;
@@ -75,31 +91,44 @@ __device__ __forceinline__ void stats_medmad(const StatsCtx &c, uint32_t n, uint
 #pragma unroll
         for (int j = 0; j < 4; j++) { h[j] = (v0 + j < c.nb) ? c.H[st_bin(c, v0 + j)] : 0u; s += h[j]; }
         uint32_t tot;
-        uint32_t ex = carry + block_excl_scan_add(s, sm_u, &tot);
+        uint32_t ex = carry + block_excl_scan_add(s, sh->scan, &tot);
 #pragma unroll
         for (int j = 0; j < 4; j++) { ex += h[j]; if (v0 + j < c.nb) c.H[st_bin(c, v0 + j)] = ex; }
         carry += tot;
     }
-    __syncthreads();
     const uint32_t n_in = carry;
     const uint32_t nz = n - n_in;          // samples replaced by 0.0
     const uint32_t k = n / 2;              // ksmall(n, n/2)
-    // ---- upper median (every thread computes it redundantly: uniform control flow)
-    double med;
-    {
-        const uint32_t v0 = st_first(0u, c.nb, [&](uint32_t v) { return st_val(c, v) >= 0.0; });
-        const uint32_t a = st_cumE(c, v0);  // in-range samples with value < 0.0
-        if (k >= a && k < a + nz) med = 0.0;
-        else {
-            const uint32_t kk = (k < a) ? k : k - nz;
-            const uint32_t v = st_first(0u, c.nb, [&](uint32_t vv) { return st_cumI(c, vv) > kk; });
-            med = st_val(c, v);
+    // ---- where 0.0 sorts among the in-range values: vz = first v with value >= 0.0
+    if (tid == 0) {
+        uint32_t vz;
+        if (c.nb == 0 || st_val(c, 0) >= 0.0) vz = 0;                       // the usual case: pa_min > 0
+        else if (st_val(c, c.nb - 1) < 0.0) vz = c.nb;
+        else vz = st_first(0u, c.nb, [&](uint32_t v) { return st_val(c, v) >= 0.0; });
+        sh->idx = vz;
+        sh->found = 0;
+    }
+    __syncthreads();
+    const uint32_t vz = sh->idx;
+    const uint32_t a = st_cumE(c, vz);     // in-range samples with value < 0.0
+    const bool med_is_zero = (k >= a && k < a + nz);
+    const uint32_t kk = (k < a) ? k : k - nz;
+    __syncthreads();
+    // ---- upper median: the bin whose cumulative range holds rank kk
+    if (!med_is_zero) {
+        for (uint32_t v = tid; v < c.nb; v += PGM_BLOCK) {
+            const uint32_t ci = st_cumI(c, v);
+            if (kk < ci && st_cumE(c, v) <= kk) sh->idx = v;
         }
     }
-    // ---- n/2-th smallest |x - med|: rank every distinct value in the order (dev, zero-mass < left < right)
+    __syncthreads();
+    const uint32_t vmed = sh->idx;
+    const double med = med_is_zero ? 0.0 : st_val(c, vmed);
     double mad_raw = 0.0;
     if (n > 1) {
-        const uint32_t vm = st_first(0u, c.nb, [&](uint32_t v) { return st_val(c, v) >= med; });
+        // vm = first v with value >= med
+        uint32_t vm = vmed;               // med_is_zero: vmed == vz, which is that index by definition
+        if (!med_is_zero) while (vm > 0 && st_val(c, vm - 1) >= med) vm--;   // only moves for equal-valued neighbours
         const uint32_t cm = st_cumE(c, vm);
         const double d0 = fabs(__dsub_rn(0.0, med));
         auto dev = [&](uint32_t v) { return fabs(__dsub_rn(st_val(c, v), med)); };
@@ -107,31 +136,52 @@ __device__ __forceinline__ void stats_medmad(const StatsCtx &c, uint32_t n, uint
         auto cntR_lt = [&](double t) { return st_cumE(c, st_first(vm, c.nb, [&](uint32_t v) { return dev(v) >= t; })) - cm; };
         auto cntL_lt = [&](double t) { return cm - st_cumE(c, st_first(0u, vm, [&](uint32_t v) { return dev(v) < t; })); };
         auto cntL_le = [&](double t) { return cm - st_cumE(c, st_first(0u, vm, [&](uint32_t v) { return dev(v) <= t; })); };
-        if (tid == 0) {
-            *sm_res = 0.0;
-            if (nz) {
-                const uint32_t rs = cntL_lt(d0) + cntR_lt(d0);
-                if (rs <= k && k < rs + nz) *sm_res = d0;
-            }
-        }
-        __syncthreads();
-        for (uint32_t v = tid; v < c.nb; v += PGM_BLOCK) {
+        // exact test: is the n/2-th smallest deviation the one of bin v? order on ties: zero mass < left < right
+        auto try_bin = [&](uint32_t v) {
             const uint32_t ci = st_cumI(c, v), ce = st_cumE(c, v);
             const uint32_t w = ci - ce;
-            if (!w) continue;
+            if (!w) return;
             const double d = dev(v);
             uint32_t rs = (d0 <= d) ? nz : 0u;
             if (v < vm) rs += (cm - ci) + cntR_lt(d);
             else rs += (ce - cm) + cntL_le(d);
-            if (rs <= k && k < rs + w) *sm_res = d;
+            if (rs <= k && k < rs + w) { sh->res = d; sh->found = 1; }
+        };
+        auto try_zero = [&]() {
+            if (!nz) return;
+            const uint32_t rs = cntL_lt(d0) + cntR_lt(d0);
+            if (rs <= k && k < rs + nz) { sh->res = d0; sh->found = 1; }
+        };
+        __syncthreads();   // everyone has read vmed out of sh->idx
+        // integer pre-search: smallest radius rho with #{samples within rho bins of vm} >= k+1
+        // (deviation grows with the bin distance; which side wins at equal distance is settled exactly below)
+        for (uint32_t rho = tid; rho <= c.nb; rho += PGM_BLOCK) {
+            const uint32_t cur = st_cumAt(c, (int64_t)vm + rho, n_in) - st_cumAt(c, (int64_t)vm - rho - 1, n_in);
+            const uint32_t prev = rho ? st_cumAt(c, (int64_t)vm + rho - 1, n_in) - st_cumAt(c, (int64_t)vm - rho, n_in) : 0u;
+            if (prev < k + 1 && k + 1 <= cur) sh->idx = rho;
         }
+        if (tid == 0 && n_in < k + 1) sh->idx = c.nb;   // only the zero mass can complete the rank
         __syncthreads();
-        mad_raw = *sm_res;
+        const int64_t rho = sh->idx;
+        // candidates: bins at distance rho-2..rho+2 on both sides (11 lanes) + the zero mass
+        if (tid < 10) {
+            const int64_t dd = rho + (int64_t)(tid % 5) - 2;
+            const int64_t v = (tid < 5) ? (int64_t)vm + dd : (int64_t)vm - dd;
+            if (dd >= 0 && v >= 0 && v < (int64_t)c.nb) try_bin((uint32_t)v);
+        } else if (tid == 31) try_zero();
+        __syncthreads();
+        if (!sh->found) {   // unusual calibration or a heavy zero mass: rank every bin
+            if (tid == 0) try_zero();
+            for (uint32_t v = tid; v < c.nb; v += PGM_BLOCK) try_bin(v);
+            __syncthreads();
+        }
+        mad_raw = sh->res;
     }
     double mad = __dmul_rn(mad_raw, 1.4826);       // gmove.cpp:162,183
     mad = (mad > 1.0) ? mad : 1.0;                 // gmove.cpp:609
     *med_out = med;
     *mad_out = mad;
+    __syncthreads();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -141,9 +191,8 @@ __device__ __forceinline__ void stats_medmad(const StatsCtx &c, uint32_t n, uint
 __global__ void __launch_bounds__(PGM_BLOCK) k_stats_wide(DevOpts o, DevBatch b, const uint8_t *rflags, const uint8_t *read_has_sel,
                                                           ReadCal *cal, uint32_t *queue, uint32_t *gscratch) {
     __shared__ uint32_t sm_hist[STATS_SMEM_BINS];
-    __shared__ uint32_t sm_u[PGM_WARPS + 1];
+    __shared__ StatsShared sh;
     __shared__ uint32_t sm_r;
-    __shared__ double sm_res;
     const uint32_t tid = threadIdx.x;
     for (;;) {
         __syncthreads();
@@ -168,7 +217,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_stats_wide(DevOpts o, DevBatch b,
         else stats_histogram<false>(b.raw, first, n, c.clo, c.nb, c.H);
         __syncthreads();
         double med, mad;
-        stats_medmad(c, n, sm_u, &sm_res, &med, &mad);
+        stats_medmad(c, n, &sh, &med, &mad);
         if (tid == 0) { cal[r].med = med; cal[r].mad = mad; }
     }
 }
@@ -193,8 +242,7 @@ struct SignalIO {
 
 __global__ void __launch_bounds__(PGM_BLOCK) k_signal(DevOpts o, DevBatch b, SignalIO io) {
     __shared__ uint32_t sm_hist[SIG_SMEM_BINS];
-    __shared__ uint32_t sm_u[PGM_WARPS + 1];
-    __shared__ double sm_res;
+    __shared__ StatsShared sh;
     const uint32_t r = blockIdx.x;
     const uint32_t tid = threadIdx.x;
     if (io.rflags[r] != 0 || !io.read_has_sel[r]) return;
@@ -213,7 +261,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_signal(DevOpts o, DevBatch b, Sig
             __syncthreads();
             stats_histogram<true>(b.raw, first, n, c.clo, c.nb, sm_hist);
             __syncthreads();
-            stats_medmad(c, n, sm_u, &sm_res, &med, &mad);
+            stats_medmad(c, n, &sh, &med, &mad);
         }
     }
     // ---- gather: lanes over 32 events' metadata, then the warp walks each selected event
