@@ -62,6 +62,35 @@ __device__ __forceinline__ void stats_histogram(const int16_t *raw, uint64_t fir
     (void)SMEM;
 }
 
+// Shared-memory variant for k_signal: branch-free. Out-of-range codes are clamped into one extra bin
+// H[nb] (never read by the order statistics; the zero mass is n - sum of the others), and the
+// increment is a `red.shared` on a 32-bit shared address computed once.
+__device__ __forceinline__ void red_shared_inc(uint32_t saddr) { asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(saddr) : "memory"); }
+
+__device__ __forceinline__ void stats_histogram_shared(const int16_t *raw, uint64_t first, uint32_t n, int clo, uint32_t nb, uint32_t *H) {
+    const uint32_t tid = threadIdx.x;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(H);
+    const uint64_t end = first + n;
+    const uint64_t body0 = (first + 7) & ~(uint64_t)7, body1 = end & ~(uint64_t)7;
+    auto add = [&](int code) { red_shared_inc(sbase + 4u * min((uint32_t)(code - clo), nb)); };
+    if (body0 < body1) {
+        const uint32_t head = (uint32_t)(body0 - first), tail = (uint32_t)(end - body1);
+        if (tid < head) add(raw[first + tid]);
+        if (tid < tail) add(raw[body1 + tid]);
+        const int4 *v4 = reinterpret_cast<const int4 *>(raw + body0);
+        const uint32_t ng = (uint32_t)((body1 - body0) >> 3);
+        for (uint32_t g = tid; g < ng; g += PGM_BLOCK) {
+            const int4 q = __ldg(v4 + g);
+            add((int)(int16_t)(q.x & 0xffff)); add(q.x >> 16);
+            add((int)(int16_t)(q.y & 0xffff)); add(q.y >> 16);
+            add((int)(int16_t)(q.z & 0xffff)); add(q.z >> 16);
+            add((int)(int16_t)(q.w & 0xffff)); add(q.w >> 16);
+        }
+    } else {
+        for (uint32_t i = tid; i < n; i += PGM_BLOCK) add(raw[first + i]);
+    }
+}
+
 // Shared scratch of stats_medmad.
 struct StatsShared {
     uint32_t scan[PGM_WARPS + 1];
@@ -241,7 +270,7 @@ struct SignalIO {
 };
 
 __global__ void __launch_bounds__(PGM_BLOCK) k_signal(DevOpts o, DevBatch b, SignalIO io) {
-    __shared__ uint32_t sm_hist[SIG_SMEM_BINS];
+    __shared__ uint32_t sm_hist[SIG_SMEM_BINS + 1];
     __shared__ StatsShared sh;
     const uint32_t r = blockIdx.x;
     const uint32_t tid = threadIdx.x;
@@ -257,13 +286,19 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_signal(DevOpts o, DevBatch b, Sig
         if (c.nb <= SIG_SMEM_BINS) {
             c.clo = rc.clo; c.off = rd.offset; c.scale = rc.scale; c.inc = !(rc.scale < 0.0);
             c.H = sm_hist;
-            for (uint32_t i = tid; i < c.nb; i += PGM_BLOCK) sm_hist[i] = 0;
+            for (uint32_t i = tid; i <= c.nb; i += PGM_BLOCK) sm_hist[i] = 0;
             __syncthreads();
-            stats_histogram<true>(b.raw, first, n, c.clo, c.nb, sm_hist);
+            stats_histogram_shared(b.raw, first, n, c.clo, c.nb, sm_hist);
             __syncthreads();
             stats_medmad(c, n, &sh, &med, &mad);
         }
     }
+    // (x - med) / mad with one reciprocal per record: y = RN(1/mad); q0 = RN(a*y); two residual
+    // corrections r = fma(-mad, q, a), q = fma(r, y, q). After the first the quotient is faithful,
+    // and Markstein's theorem makes the second one the correctly rounded a/mad (= the reference's
+    // IEEE division) unless mad's significand is all ones; that case takes the plain division.
+    const double rcp = __drcp_rn(mad);
+    const bool fast_div = ((__double_as_longlong(mad) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll);
     // ---- gather: lanes over 32 events' metadata, then the warp walks each selected event
     const uint32_t lane = tid & 31, w = tid >> 5;
     const uint32_t e0 = io.ev_base[r], e1 = io.ev_base[r + 1];
@@ -290,7 +325,14 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_signal(DevOpts o, DevBatch b, Sig
             for (uint32_t t = lane; t < l0; t += 32) {
                 const int cval = x[s0 + t];
                 double v = (cval >= clo && cval <= chi) ? pgm_pa(cval, offset, scale) : 0.0;
-                if (o.scaling) v = __ddiv_rn(__dsub_rn(v, med), mad);
+                if (o.scaling) {
+                    const double a = __dsub_rn(v, med);
+                    if (fast_div) {
+                        double q = __dmul_rn(a, rcp);
+                        q = __fma_rn(__fma_rn(-mad, q, a), rcp, q);
+                        v = __fma_rn(__fma_rn(-mad, q, a), rcp, q);
+                    } else v = __ddiv_rn(a, mad);
+                }
                 out[t] = v;
             }
         }
