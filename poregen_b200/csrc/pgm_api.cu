@@ -248,6 +248,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     d.scaling = opts->scaling; d.n_slots = opts->n_slots; d.index_lo = opts->index_lo;
     d.pa_min = opts->pa_min; d.pa_max = opts->pa_max;
     d.fourth = opts->flag_rna ? 'U' : 'T';
+    if (const char *dbg = getenv("PGM_DEBUG_SLOW_STATS")) d.debug |= (dbg[0] && dbg[0] != '0') ? 1u : 0u;
     int rc = PGM_OK;
     auto bail = [&](int code) { std::string m = c->err; pgm_destroy(c); g_create_error = m; return code; };
     if (opts->kmer_list) {
@@ -550,7 +551,7 @@ int pgm_emit(pgm_ctx *c) {
         g.rflags = P<uint8_t>(c->rflags); g.read_has_sel = P<uint8_t>(c->read_has_sel); g.cal = P<ReadCal>(c->cal);
         g.ev_base = P<uint32_t>(c->ev_base); g.ev_start = P<uint32_t>(c->ev_start); g.ev_len = P<uint32_t>(c->ev_len); g.ev_out = P<uint32_t>(c->ev_out);
         g.sel_off = P<uint64_t>(c->sel_off); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
-        k_signal<<<R, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        k_signal<<<R, SIG_THREADS, 0, st>>>(d, c->db, g);
         c->launches++;
     }
     // kmer_frequency_map after this batch

@@ -5,6 +5,7 @@
 // plain x86-64 SSE2 code (no FMA), see SURVEY.md F2.
 #pragma once
 #include <cuda_runtime.h>
+#include <math_constants.h>
 #include <stdint.h>
 #include "../../include/pgm_gmove.h"
 
@@ -18,6 +19,8 @@ struct DevOpts {
     uint32_t scaling, n_slots, index_lo, mode;
     uint32_t use_lut;       // 1: slot = lut[id] (kmer_list), 0: slot = id - index_lo
     uint32_t fourth;        // 'T' or 'U': the 4th letter of the k-mer table's alphabet
+    uint32_t debug;         // bit 0: Med-MAD always takes the rank-every-bin path (env PGM_DEBUG_SLOW_STATS, tests)
+    uint32_t reserved;
     double pa_min, pa_max;
     const uint32_t *lut;    // [4^k] when use_lut
 };

@@ -103,3 +103,18 @@ def test_two_rank_quota_exchange_on_one_gpu(built):
     np.testing.assert_array_equal(np.concatenate(ev_start), ref.ev_start)
     np.testing.assert_array_equal(np.concatenate(ev_read), ref.ev_read)
     np.testing.assert_array_equal(np.concatenate(samples).view(np.uint64), ref.samples.view(np.uint64))
+
+
+_SCALED = [c for c in parity_cases() if c[2].scaling == 1]
+
+
+@pytest.mark.parametrize("label,cfg,opts", _SCALED, ids=[c[0] for c in _SCALED])
+def test_medmad_rank_every_bin_path(built, label, cfg, opts, monkeypatch):
+    """The Med-MAD fast path (window around the integer radius) is skipped: every record goes
+    through the generic rank-every-bin selection, which must give the same bits."""
+    monkeypatch.setenv("PGM_DEBUG_SLOW_STATS", "1")
+    batch = synth.make_batch(cfg)
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        res = eng.process(batch)
+    assert_same(res, ref, label)
