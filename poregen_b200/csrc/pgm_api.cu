@@ -17,10 +17,10 @@
 #include <string>
 #include <vector>
 
-#include "pgm_decode.cuh"
 #include "pgm_device.cuh"
-#include "pgm_emit.cuh"
 #include "pgm_scan.cuh"
+#include "pgm_decode.cuh"
+#include "pgm_emit.cuh"
 #include "pgm_signal.cuh"
 #include "pgm_sort.cuh"
 
@@ -33,14 +33,8 @@ struct DBuf {
     size_t cap = 0;
 };
 
-struct Scalars {  // device -> host summary of one batch
-    unsigned long long examined;
-    unsigned long long n_sel_samples;
-    uint32_t n_pass;
-    uint32_t n_sel;
-    uint32_t err_flag;
-    uint32_t pad;
-};
+typedef BatchScalars Scalars;  // device -> host summary of one batch (pgm_emit.cuh)
+#define MISC_WORDS 64   // dev_misc: word 0 = k_stats_wide queue, words 8.. = look-back scan tickets
 
 enum State { ST_IDLE = 0, ST_LOADED, ST_COUNTED, ST_EMITTED };
 
@@ -60,6 +54,8 @@ struct pgm_ctx {
 
     // per-context persistent device state
     DBuf lut, consumed, counts, keep, totals_next, bucket_base, sel_base, scalars, dev_misc, gscratch;
+    DBuf lb_flag, lb_agg, lb_pre;   // look-back scan status (shared by the scans of one stream, told apart by generation)
+    uint32_t lb_gen = 0, lb_ticket = 0;
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
 
     // batch (device view) + owned copies
@@ -194,7 +190,7 @@ void pgm_destroy(pgm_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->totals_next, &c->bucket_base, &c->sel_base, &c->scalars,
-                   &c->dev_misc, &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
+                   &c->dev_misc, &c->gscratch, &c->lb_flag, &c->lb_agg, &c->lb_pre, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
                    &c->sc_indel, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out};
@@ -280,7 +276,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep, &c->totals_next};
     for (DBuf *b : slotbufs) if ((rc = ensure(c, *b, sb)) != PGM_OK) return bail(rc);
     if ((rc = ensure(c, c->bucket_base, sb + 4)) != PGM_OK || (rc = ensure(c, c->sel_base, sb + 4)) != PGM_OK) return bail(rc);
-    if ((rc = ensure(c, c->scalars, sizeof(Scalars))) != PGM_OK || (rc = ensure(c, c->dev_misc, 64)) != PGM_OK) return bail(rc);
+    if ((rc = ensure(c, c->scalars, sizeof(Scalars))) != PGM_OK || (rc = ensure(c, c->dev_misc, MISC_WORDS * 4)) != PGM_OK) return bail(rc);
     if (cudaMemset(c->consumed.p, 0, sb) != cudaSuccess) { c->err = "memset failed"; return bail(PGM_ERR_CUDA); }
     if (cudaHostAlloc((void **)&c->h_scalars, sizeof(Scalars), cudaHostAllocDefault) != cudaSuccess) { c->err = "cudaHostAlloc failed"; return bail(PGM_ERR_NOMEM); }
     *out = c;
@@ -342,6 +338,17 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
         RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4));
     }
     if (c->opts.scaling) RET(ensure(c, c->gscratch, (size_t)c->n_sm * 4 * 65536 * 4));
+    {
+        uint64_t m = (uint64_t)SORT_MAX_BINS * ntiles;
+        if (m < c->opts.n_slots) m = c->opts.n_slots;
+        if (m < cap + 1) m = cap + 1;
+        const size_t tiles = (size_t)(m / LB_TILE) + 2;
+        const bool fresh = !c->lb_flag.p || c->lb_flag.cap < tiles * 4;
+        RET(ensure(c, c->lb_flag, tiles * 4));
+        RET(ensure(c, c->lb_agg, tiles * 8));
+        RET(ensure(c, c->lb_pre, tiles * 8));
+        if (fresh) CU(c, cudaMemsetAsync(c->lb_flag.p, 0, c->lb_flag.cap, c->stream));   // generation 0 = never valid
+    }
     return PGM_OK;
 }
 
@@ -412,7 +419,8 @@ int pgm_count(pgm_ctx *c) {
         StageTimer t(c, PGM_STAGE_MISC);
         CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
         CU(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(Scalars), st));
-        CU(c, cudaMemsetAsync(c->dev_misc.p, 0, 64, st));
+        CU(c, cudaMemsetAsync(c->dev_misc.p, 0, MISC_WORDS * 4, st));
+        c->lb_ticket = 0;
         if (R) CU(c, cudaMemsetAsync(c->read_has_sel.p, 0, R, st));
     }
     c->user_prior = c->user_consumed = nullptr;
@@ -459,13 +467,20 @@ int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consume
     return PGM_OK;
 }
 
-// gathers the device-side counts of one batch into the Scalars block
-__global__ void k_collect(const uint32_t *ev_base, uint32_t R, const uint32_t *sel_base, uint32_t n_slots, const uint64_t *sel_off, Scalars *s) {
-    const uint32_t ns = sel_base[n_slots];
-    s->n_pass = ev_base[R];
-    s->n_sel = ns;
-    s->n_sel_samples = sel_off[ns];
+extern "C++" {
+template <typename T>
+static LbBuf<T> next_lb(pgm_ctx *c) {
+    LbBuf<T> st;
+    st.flag = P<uint32_t>(c->lb_flag);
+    st.agg = P<T>(c->lb_agg);
+    st.pre = P<T>(c->lb_pre);
+    st.ticket = P<uint32_t>(c->dev_misc) + 8 + (c->lb_ticket++ % (MISC_WORDS - 8));
+    c->lb_gen = (c->lb_gen + 1) & 0x3fffffffu;
+    if (c->lb_gen == 0) c->lb_gen = 1;
+    st.gen = c->lb_gen;
+    return st;
 }
+}  // extern "C++"
 
 int pgm_emit(pgm_ctx *c) {
     if (!c) return PGM_ERR_ARG;
@@ -476,8 +491,7 @@ int pgm_emit(pgm_ctx *c) {
     DevOpts d = c->dopts;
     d.mode = c->db.mode;
     const uint32_t *n_ev = P<uint32_t>(c->ev_base) + R;  // device scalar: passing events
-    const uint32_t pgrid = (uint32_t)c->n_sm * 8;
-    uint32_t *skey = P<uint32_t>(c->key), *sval = nullptr;
+    const uint32_t pgrid = (uint32_t)c->n_sm * 4;
     if (R && c->ev_cap) {
         {
             StageTimer t(c, PGM_STAGE_DECODE_EMIT);
@@ -486,7 +500,21 @@ int pgm_emit(pgm_ctx *c) {
             else k_decode_moves<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
             c->launches++;
         }
-        // stable LSD radix sort of (slot, event index)
+    }
+    // quota: keep / bucket_base / sel_base / totals after the batch, one launch
+    {
+        StageTimer t(c, PGM_STAGE_SELECT);
+        QuotaIO q;
+        q.n_slots = NS; q.limit = c->opts.sample_limit;
+        q.prior = c->user_prior ? c->user_prior : P<uint32_t>(c->consumed);
+        q.user_consumed = c->user_consumed;
+        q.counts = P<uint32_t>(c->counts); q.keep = P<uint32_t>(c->keep); q.consumed = P<uint32_t>(c->consumed);
+        q.bucket_base = P<uint32_t>(c->bucket_base); q.sel_base = P<uint32_t>(c->sel_base);
+        k_quota<<<cdiv(NS, LB_TILE), PGM_BLOCK, 0, st>>>(q, next_lb<unsigned long long>(c));
+        c->launches++;
+    }
+    if (R && c->ev_cap) {
+        // stable LSD radix sort of (slot, event index); the last pass is fused with the selection (k_rank)
         StageTimer tsort(c, PGM_STAGE_SORT);
         const uint32_t bits = bit_length(NS - 1);
         const uint32_t passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
@@ -498,45 +526,35 @@ int pgm_emit(pgm_ctx *c) {
         for (uint32_t p = 0; p < passes; p++) {
             const uint32_t shift = p * per;
             k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
-            c->launches++;
-            RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->hist), P<uint32_t>(c->hist), (uint64_t)(1u << per) * ntiles, nullptr, false, c->blk32)));
-            k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
-            c->launches++;
-            // ping-pong: keys key<->key2, values val<->val2
-            uint32_t *t = kin; kin = kout; kout = t;
-            vin = vout; vout = (vout == P<uint32_t>(c->val)) ? P<uint32_t>(c->val2) : P<uint32_t>(c->val);
+            k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->hist), n_ev, 1u << per, ntiles,
+                                                                                           next_lb<uint32_t>(c));
+            c->launches += 2;
+            if (p + 1 < passes) {
+                k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
+                c->launches++;
+                // ping-pong: keys key<->key2, values val<->val2
+                uint32_t *t = kin; kin = kout; kout = t;
+                vin = vout; vout = (vout == P<uint32_t>(c->val)) ? P<uint32_t>(c->val2) : P<uint32_t>(c->val);
+            } else {
+                RankIO r;
+                r.n_events = n_ev; r.keys_in = kin; r.vals_in = vin; r.hist_scanned = P<uint32_t>(c->hist);
+                r.ntiles_cap = ntiles; r.shift = shift; r.bits = per;
+                r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
+                r.ev_start = P<uint32_t>(c->ev_start); r.ev_len = P<uint32_t>(c->ev_len); r.ev_read = P<uint32_t>(c->ev_read);
+                r.sel_start = P<uint32_t>(c->sel_start); r.sel_len = P<uint32_t>(c->sel_len); r.sel_read = P<uint32_t>(c->sel_read);
+                r.ev_out = P<uint32_t>(c->ev_out); r.read_has_sel = P<uint8_t>(c->read_has_sel);
+                k_rank<<<sgrid, PGM_BLOCK, 0, st>>>(r);
+                c->launches++;
+            }
         }
-        skey = kin; sval = vin;
         CU(c, cudaGetLastError());
     }
-    // quota
-    const uint32_t *prior = c->user_prior ? c->user_prior : P<uint32_t>(c->consumed);
-    {
-        StageTimer t(c, PGM_STAGE_SELECT);
-        k_select_prep<<<cdiv(NS, PGM_BLOCK), PGM_BLOCK, 0, st>>>(NS, c->opts.sample_limit, prior, P<uint32_t>(c->counts), P<uint32_t>(c->keep),
-                                                                c->user_consumed ? nullptr : P<uint32_t>(c->totals_next));
-        c->launches++;
-    }
     {
         StageTimer t(c, PGM_STAGE_SCAN);
-        RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->counts), P<uint32_t>(c->bucket_base), NS, nullptr, true, c->blk32)));
-        RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->keep), P<uint32_t>(c->sel_base), NS, nullptr, true, c->blk32)));
-    }
-    const uint32_t *n_sel = P<uint32_t>(c->sel_base) + NS;
-    if (R && c->ev_cap) {
-        StageTimer t(c, PGM_STAGE_SELECT);
-        SelectIO sio;
-        sio.n_events = n_ev; sio.skey = skey; sio.sval = sval; sio.bucket_base = P<uint32_t>(c->bucket_base); sio.keep = P<uint32_t>(c->keep);
-        sio.sel_base = P<uint32_t>(c->sel_base); sio.ev_start = P<uint32_t>(c->ev_start); sio.ev_len = P<uint32_t>(c->ev_len); sio.ev_read = P<uint32_t>(c->ev_read);
-        sio.sel_start = P<uint32_t>(c->sel_start); sio.sel_len = P<uint32_t>(c->sel_len); sio.sel_read = P<uint32_t>(c->sel_read);
-        sio.ev_out = P<uint32_t>(c->ev_out);
-        sio.read_has_sel = P<uint8_t>(c->read_has_sel);
-        k_select<<<pgrid, PGM_BLOCK, 0, st>>>(sio);
+        k_scan_sel<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_len), P<unsigned long long>(c->sel_off),
+                                                                               P<uint32_t>(c->sel_base) + NS, n_ev, P<Scalars>(c->scalars),
+                                                                               next_lb<unsigned long long>(c));
         c->launches++;
-    }
-    {
-        StageTimer t(c, PGM_STAGE_SCAN);
-        RET((scan<uint32_t, uint64_t>(c, P<uint32_t>(c->sel_len), P<uint64_t>(c->sel_off), c->ev_cap, n_sel, true, c->blk64)));
     }
     if (R && c->ev_cap) {
         if (c->opts.scaling && c->need_wide) {
@@ -554,11 +572,6 @@ int pgm_emit(pgm_ctx *c) {
         k_signal<<<R, SIG_THREADS, 0, st>>>(d, c->db, g);
         c->launches++;
     }
-    // kmer_frequency_map after this batch
-    StageTimer tmisc(c, PGM_STAGE_MISC);
-    CU(c, cudaMemcpyAsync(c->consumed.p, c->user_consumed ? (const void *)c->user_consumed : c->totals_next.p, (size_t)NS * 4, cudaMemcpyDeviceToDevice, st));
-    k_collect<<<1, 1, 0, st>>>(P<uint32_t>(c->ev_base), R, P<uint32_t>(c->sel_base), NS, P<uint64_t>(c->sel_off), P<Scalars>(c->scalars));
-    c->launches++;
     CU(c, cudaGetLastError());
     c->state = ST_EMITTED;
     return PGM_OK;

@@ -1,6 +1,7 @@
 // pgm_emit.cuh — per-record preparation, quota selection, exact Med-MAD, sample gather.
 #pragma once
 #include "pgm_device.cuh"
+#include "pgm_scan.cuh"
 
 // ------------------------------------------------------------------------------------------------
 // k_read_prep: one thread per record. Validates the record, derives the in-range code interval and
@@ -92,3 +93,61 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_select(SelectIO io) {
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// k_quota: one launch for everything the quota needs. Per slot s: keep = clamp(limit - prior, 0, counts)
+// and the totals after the batch; a packed look-back scan gives bucket_base = exscan(counts) (where each
+// slot's bucket starts in the sorted order) and sel_base = exscan(keep) (where its emitted events start).
+struct QuotaIO {
+    uint32_t n_slots, limit;
+    const uint32_t *prior;          // totals this rank must treat as already emitted
+    const uint32_t *user_consumed;  // multi-GPU: totals after the round (or nullptr: prior + keep)
+    const uint32_t *counts;
+    uint32_t *keep, *consumed, *bucket_base, *sel_base;   // consumed may alias prior
+};
+
+__global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf<unsigned long long> st) {
+    lb_scan<unsigned long long>(
+        io.n_slots, st,
+        [&](uint64_t s) {
+            const uint32_t c = io.counts[s];
+            const uint32_t p = min(io.prior[s], io.limit);
+            const uint32_t k = min(c, io.limit - p);
+            io.keep[s] = k;
+            io.consumed[s] = io.user_consumed ? io.user_consumed[s] : p + k;
+            return (unsigned long long)c | ((unsigned long long)k << 32);
+        },
+        [&](uint64_t s, unsigned long long ex, unsigned long long) {
+            io.bucket_base[s] = (uint32_t)ex;
+            io.sel_base[s] = (uint32_t)(ex >> 32);
+        },
+        [&](unsigned long long tot) {
+            io.bucket_base[io.n_slots] = (uint32_t)tot;
+            io.sel_base[io.n_slots] = (uint32_t)(tot >> 32);
+        });
+}
+
+// k_scan_sel: sample offsets of the selected events (exclusive scan of their lengths, 64-bit) and the
+// batch summary, in one launch.
+struct BatchScalars {  // device -> host summary of one batch
+    unsigned long long examined;
+    unsigned long long n_sel_samples;
+    uint32_t n_pass;
+    uint32_t n_sel;
+    uint32_t err_flag;
+    uint32_t pad;
+};
+
+__global__ void __launch_bounds__(PGM_BLOCK) k_scan_sel(const uint32_t *sel_len, unsigned long long *sel_off, const uint32_t *n_sel_ptr,
+                                                        const uint32_t *n_pass_ptr, BatchScalars *sc, LbBuf<unsigned long long> st) {
+    const uint32_t n = *n_sel_ptr;
+    lb_scan<unsigned long long>(
+        n, st, [&](uint64_t i) { return (unsigned long long)sel_len[i]; },
+        [&](uint64_t i, unsigned long long ex, unsigned long long) { sel_off[i] = ex; },
+        [&](unsigned long long tot) {
+            sel_off[n] = tot;
+            sc->n_sel_samples = tot;
+            sc->n_sel = n;
+            sc->n_pass = *n_pass_ptr;
+        });
+}

@@ -95,3 +95,98 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_scan_down(const TIn *in, uint64_t
         if (write_total && idx + 1 == n) out[n] = ex;
     }
 }
+
+// ------------------------------------------------------------------------------------------------
+// Single-pass exclusive scan with decoupled look-back (one launch instead of reduce/top/down).
+// Tiles are handed out by an atomic ticket, so a tile only ever waits on tiles that already run.
+// flag[t] = gen << 2 | state (1: tile aggregate published, 2: inclusive prefix published); a stale
+// generation reads as "nothing yet", so the status arrays never need clearing between launches.
+#define LB_ITEMS 16
+#define LB_TILE (PGM_BLOCK * LB_ITEMS)
+
+template <typename T>
+struct LbBuf {
+    uint32_t *flag;    // [tiles]
+    T *agg, *pre;      // [tiles]
+    uint32_t *ticket;  // zeroed before the launch
+    uint32_t gen;
+};
+
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
+__device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *reinterpret_cast<volatile uint32_t *>(p) = v; }
+template <typename T> __device__ __forceinline__ T ld_volatile_t(const T *p) { return *reinterpret_cast<const volatile T *>(p); }
+
+template <typename T>
+__device__ __forceinline__ T warp_sum_t(T v) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// load(idx) -> T, store(idx, exclusive_prefix, own_value), fin(total) (one thread of the last tile).
+template <typename T, typename LoadF, typename StoreF, typename FinalF>
+__device__ __forceinline__ void lb_scan(uint64_t n, LbBuf<T> st, LoadF load, StoreF store, FinalF fin) {
+    __shared__ T sm_scan[PGM_WARPS + 1];
+    __shared__ T sm_prefix;
+    __shared__ uint32_t sm_tile;
+    if (threadIdx.x == 0) sm_tile = atomicAdd(st.ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = sm_tile;
+    const uint64_t ntiles = (n + LB_TILE - 1) / LB_TILE;
+    if (tile >= ntiles) {
+        if (n == 0 && tile == 0 && threadIdx.x == 0) fin((T)0);
+        return;
+    }
+    const uint64_t base = (uint64_t)tile * LB_TILE + (uint64_t)threadIdx.x * LB_ITEMS;
+    T v[LB_ITEMS];
+    T s = 0;
+#pragma unroll
+    for (int i = 0; i < LB_ITEMS; i++) {
+        const uint64_t idx = base + i;
+        v[i] = (idx < n) ? load(idx) : (T)0;
+        s += v[i];
+    }
+    T tot;
+    const T ex = block_excl_scan_add_t<T>(s, sm_scan, &tot);
+    if (threadIdx.x < 32) {
+        const uint32_t lane = threadIdx.x;
+        const uint32_t gen = st.gen;
+        T excl = 0;
+        if (tile == 0) {
+            if (lane == 0) { st.pre[0] = tot; __threadfence(); st_volatile_u32(st.flag, gen << 2 | 2u); }
+        } else {
+            if (lane == 0) { st.agg[tile] = tot; __threadfence(); st_volatile_u32(st.flag + tile, gen << 2 | 1u); }
+            int64_t pos = (int64_t)tile - 1;
+            for (;;) {
+                const int64_t idx = pos - (int64_t)lane;
+                uint32_t f = 2;   // before tile 0: prefix 0
+                T val = 0;
+                if (idx >= 0) {
+                    do { f = ld_volatile_u32(st.flag + idx); } while ((f >> 2) != gen || (f & 3u) == 0);
+                    f &= 3u;
+                    __threadfence();
+                    val = (f == 2) ? ld_volatile_t<T>(st.pre + idx) : ld_volatile_t<T>(st.agg + idx);
+                }
+                const uint32_t m2 = __ballot_sync(0xffffffffu, f == 2);
+                if (m2) {
+                    const uint32_t L = __ffs(m2) - 1;
+                    excl += warp_sum_t<T>(lane <= L ? val : (T)0);
+                    break;
+                }
+                excl += warp_sum_t<T>(val);
+                pos -= 32;
+            }
+            if (lane == 0) { st.pre[tile] = excl + tot; __threadfence(); st_volatile_u32(st.flag + tile, gen << 2 | 2u); }
+        }
+        if (lane == 0) sm_prefix = excl;
+    }
+    __syncthreads();
+    T run = sm_prefix + ex;
+#pragma unroll
+    for (int i = 0; i < LB_ITEMS; i++) {
+        const uint64_t idx = base + i;
+        if (idx < n) store(idx, run, v[i]);
+        run += v[i];
+    }
+    if (tile == ntiles - 1 && threadIdx.x == 0) fin(sm_prefix + tot);
+}

@@ -10,10 +10,11 @@
 // __match_any_sync peer ranks and per-warp digit counters.
 #pragma once
 #include "pgm_device.cuh"
+#include "pgm_scan.cuh"
 
 #define SORT_ITEMS 8
 #define SORT_TILE (PGM_BLOCK * SORT_ITEMS)
-#define SORT_MAX_BITS 8
+#define SORT_MAX_BITS 10
 #define SORT_MAX_BINS (1 << SORT_MAX_BITS)
 
 __global__ void __launch_bounds__(PGM_BLOCK) k_sort_hist(const uint32_t *keys, const uint32_t *n_ptr, uint32_t shift, uint32_t bits,
@@ -93,6 +94,103 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_sort_scatter(const uint32_t *keys
                 const uint32_t pos = goff[d] + wcount[w][d] + lrank[rd];
                 keys_out[pos] = key[rd];
                 vals_out[pos] = val[rd];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// One-launch scan of the digit-major tile histogram hist[bin * ntiles_cap + tile] over the tiles in
+// use (n_events known on the device only), in place.
+__global__ void __launch_bounds__(PGM_BLOCK) k_scan_hist(uint32_t *hist, const uint32_t *n_ptr, uint32_t bins, uint32_t ntiles_cap,
+                                                         LbBuf<uint32_t> st) {
+    const uint32_t n_ev = *n_ptr;
+    const uint32_t ntu = (n_ev + SORT_TILE - 1) / SORT_TILE;
+    const uint64_t n = (uint64_t)bins * ntu;
+    auto addr = [&](uint64_t e) { return (size_t)(e / ntu) * ntiles_cap + (size_t)(e % ntu); };
+    lb_scan<uint32_t>(n, st, [&](uint64_t e) { return hist[addr(e)]; },
+                      [&](uint64_t e, uint32_t ex, uint32_t) { hist[addr(e)] = ex; }, [](uint32_t) {});
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_rank: the LAST radix pass fused with the quota selection. For every passing event it computes
+// the position the stable sort would give it (so its rank inside its slot), decides "emitted" =
+// rank < keep[slot] (reference gmove.cpp:650-652, 680-685) and writes the event straight to its
+// place in the slot-grouped output; no sorted intermediate is materialised.
+// vals_in == nullptr: single pass, the value of item i is i.
+struct RankIO {
+    const uint32_t *n_events;
+    const uint32_t *keys_in, *vals_in;      // full slot keys (in the order of the previous pass) and original event ids
+    const uint32_t *hist_scanned;           // this pass's scanned tile histogram
+    uint32_t ntiles_cap, shift, bits;
+    const uint32_t *bucket_base, *keep, *sel_base;
+    const uint32_t *ev_start, *ev_len, *ev_read;  // [E] record-then-position order
+    uint32_t *sel_start, *sel_len, *sel_read;     // [E_sel] grouped by slot
+    uint32_t *ev_out;                             // [E] selected index q of every passing event, or PGM_INVALID
+    uint8_t *read_has_sel;                        // [R]
+};
+
+__global__ void __launch_bounds__(PGM_BLOCK) k_rank(RankIO io) {
+    __shared__ uint32_t wcount[PGM_WARPS][SORT_MAX_BINS];
+    __shared__ uint32_t goff[SORT_MAX_BINS];
+    const uint32_t n = *io.n_events;
+    const uint32_t bins = 1u << io.bits, mask = bins - 1, shift = io.shift;
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t used_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < PGM_WARPS * bins; i += PGM_BLOCK) wcount[i / bins][i % bins] = 0;
+        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) goff[i] = io.hist_scanned[(size_t)i * io.ntiles_cap + tile];
+        __syncthreads();
+        const uint32_t wbase = tile * SORT_TILE + w * (32 * SORT_ITEMS);
+        uint32_t key[SORT_ITEMS], lrank[SORT_ITEMS];
+#pragma unroll
+        for (int rd = 0; rd < SORT_ITEMS; rd++) {
+            const uint32_t idx = wbase + rd * 32 + lane;
+            const bool valid = idx < n;
+            key[rd] = valid ? io.keys_in[idx] : 0;
+            const uint32_t d = valid ? ((key[rd] >> shift) & mask) : bins;  // invalid lanes form their own group
+            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const uint32_t leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if (valid && lane == leader) {
+                old = wcount[w][d];
+                wcount[w][d] = old + __popc(peers);
+            }
+            old = __shfl_sync(0xffffffffu, old, leader);
+            lrank[rd] = old + __popc(peers & ((1u << lane) - 1));
+            __syncwarp();
+        }
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b < bins; b += PGM_BLOCK) {   // exclusive scan over warps, per digit
+            uint32_t run = 0;
+#pragma unroll
+            for (int ww = 0; ww < PGM_WARPS; ww++) {
+                const uint32_t t = wcount[ww][b];
+                wcount[ww][b] = run;
+                run += t;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int rd = 0; rd < SORT_ITEMS; rd++) {
+            const uint32_t idx = wbase + rd * 32 + lane;
+            if (idx < n) {
+                const uint32_t slot = key[rd];
+                const uint32_t d = (slot >> shift) & mask;
+                const uint32_t pos = goff[d] + wcount[w][d] + lrank[rd];
+                const uint32_t rank = pos - io.bucket_base[slot];
+                const uint32_t id = io.vals_in ? io.vals_in[idx] : idx;
+                const bool sel = rank < io.keep[slot];
+                const uint32_t q = io.sel_base[slot] + rank;
+                io.ev_out[id] = sel ? q : PGM_INVALID;
+                if (sel) {
+                    const uint32_t rr = io.ev_read[id];
+                    io.sel_start[q] = io.ev_start[id];
+                    io.sel_len[q] = io.ev_len[id];
+                    io.sel_read[q] = rr;
+                    io.read_has_sel[rr] = 1;
+                }
             }
         }
     }
