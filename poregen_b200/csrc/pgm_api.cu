@@ -69,7 +69,11 @@ struct pgm_ctx {
     DBuf cal, rflags, n_pass, ev_base, read_has_sel, ss_L, ss_nindel;
     // events / sort / selection
     DBuf key, ev_start, ev_len, ev_read, key2, val, val2, hist, blk32, blk64;
-    DBuf sc_start, sc_end, sc_code, sc_indel;
+    DBuf sc_start, sc_end, sc_key, sc_code, sc_indel;
+    DBuf rec_flag, rec_agg, rec_pre;   // look-back over records (k_decode)
+    DBuf zbatch;                       // zeroed every batch: read_has_sel[R] then the tile histogram
+    size_t hist_off = 0;               // byte offset of the histogram inside zbatch
+    uint32_t sort_ntiles = 0;
     DBuf sel_start, sel_len, sel_read, sel_off, samples, ev_out;
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
 
@@ -127,6 +131,11 @@ void release(DBuf &b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
 void release_host(DBuf &b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
 
 template <typename T> T *P(DBuf &b) { return reinterpret_cast<T *>(b.p); }
+inline uint8_t *HAS_SEL(pgm_ctx *c);
+inline uint32_t *HIST(pgm_ctx *c);
+
+inline uint8_t *HAS_SEL(pgm_ctx *c) { return reinterpret_cast<uint8_t *>(c->zbatch.p); }
+inline uint32_t *HIST(pgm_ctx *c) { return reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(c->zbatch.p) + c->hist_off); }
 
 #define RET(x) do { int rc_ = (x); if (rc_ != PGM_OK) return rc_; } while (0)
 
@@ -193,7 +202,7 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->dev_misc, &c->gscratch, &c->lb_flag, &c->lb_agg, &c->lb_pre, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out};
+                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags};
     for (DBuf *b : host) release_host(*b);
@@ -321,27 +330,30 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->rflags, R));
     RET(ensure(c, c->n_pass, (size_t)R * 4));
     RET(ensure(c, c->ev_base, (size_t)(R + 1) * 4));
-    RET(ensure(c, c->read_has_sel, R));
     const size_t e4 = (size_t)cap * 4;
     DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read, &c->ev_out};
     for (DBuf *x : evb) RET(ensure(c, *x, e4));
     RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
-    RET(ensure(c, c->hist, (size_t)SORT_MAX_BINS * ntiles * 4));
+    c->sort_ntiles = ntiles;
+    c->hist_off = ((size_t)R + 255) & ~(size_t)255;
+    RET(ensure(c, c->zbatch, c->hist_off + (size_t)SORT_MAX_BINS * ntiles * 4));
     RET(ensure(c, c->samples, (size_t)c->samples_cap * 8));
+    RET(ensure(c, c->sc_start, (size_t)b->n_align * 4 + 4));
+    RET(ensure(c, c->sc_end, (size_t)b->n_align * 4 + 4));
+    RET(ensure(c, c->sc_key, (size_t)b->n_align * 4 + 4));
     if (b->mode == PGM_MODE_SS) {
         RET(ensure(c, c->ss_L, (size_t)R * 4));
         RET(ensure(c, c->ss_nindel, (size_t)R * 4));
-        RET(ensure(c, c->sc_start, (size_t)b->n_align * 4));
-        RET(ensure(c, c->sc_end, (size_t)b->n_align * 4));
-        RET(ensure(c, c->sc_code, (size_t)b->n_align));
-        RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4));
+        RET(ensure(c, c->sc_code, (size_t)b->n_align + 4));
+        RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4 + 4));
     }
     if (c->opts.scaling) RET(ensure(c, c->gscratch, (size_t)c->n_sm * 4 * 65536 * 4));
     {
         uint64_t m = (uint64_t)SORT_MAX_BINS * ntiles;
         if (m < c->opts.n_slots) m = c->opts.n_slots;
         if (m < cap + 1) m = cap + 1;
+        if (m < R) m = R;
         const size_t tiles = (size_t)(m / LB_TILE) + 2;
         const bool fresh = !c->lb_flag.p || c->lb_flag.cap < tiles * 4;
         RET(ensure(c, c->lb_flag, tiles * 4));
@@ -393,20 +405,26 @@ int pgm_attach_device(pgm_ctx *c, const pgm_batch *b) {
     return PGM_OK;
 }
 
-static DecodeIO make_io(pgm_ctx *c) {
-    DecodeIO io;
-    memset(&io, 0, sizeof io);
-    io.consumed = P<uint32_t>(c->consumed);
-    io.counts = P<uint32_t>(c->counts);
-    io.n_pass = P<uint32_t>(c->n_pass);
-    io.ev_base = P<uint32_t>(c->ev_base);
-    io.ev_cap = c->ev_cap;
-    io.key = P<uint32_t>(c->key); io.ev_start = P<uint32_t>(c->ev_start); io.ev_len = P<uint32_t>(c->ev_len); io.ev_read = P<uint32_t>(c->ev_read);
-    io.rflags = P<uint8_t>(c->rflags);
-    io.examined = &P<Scalars>(c->scalars)->examined;
-    io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end); io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
-    io.ss_L = P<uint32_t>(c->ss_L); io.ss_nindel = P<uint32_t>(c->ss_nindel);
-    return io;
+extern "C++" {
+template <typename T>
+static LbBuf<T> next_lb(pgm_ctx *c) {
+    LbBuf<T> st;
+    st.flag = P<uint32_t>(c->lb_flag);
+    st.agg = P<T>(c->lb_agg);
+    st.pre = P<T>(c->lb_pre);
+    st.ticket = P<uint32_t>(c->dev_misc) + 8 + (c->lb_ticket++ % (MISC_WORDS - 8));
+    c->lb_gen = (c->lb_gen + 1) & 0x3fffffffu;
+    if (c->lb_gen == 0) c->lb_gen = 1;
+    st.gen = c->lb_gen;
+    return st;
+}
+}  // extern "C++"
+
+// radix pass layout for the slot keys: `passes` passes of `per` bits
+static void sort_plan(const pgm_ctx *c, uint32_t *passes, uint32_t *per) {
+    const uint32_t bits = bit_length(c->opts.n_slots - 1);
+    *passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
+    *per = bits ? (bits + *passes - 1) / *passes : 1;
 }
 
 int pgm_count(pgm_ctx *c) {
@@ -415,13 +433,17 @@ int pgm_count(pgm_ctx *c) {
     CU(c, cudaSetDevice(c->device));
     const uint32_t R = c->db.n_reads;
     cudaStream_t st = c->stream;
+    uint32_t passes, per;
+    sort_plan(c, &passes, &per);
     {
         StageTimer t(c, PGM_STAGE_MISC);
         CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
         CU(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(Scalars), st));
         CU(c, cudaMemsetAsync(c->dev_misc.p, 0, MISC_WORDS * 4, st));
         c->lb_ticket = 0;
-        if (R) CU(c, cudaMemsetAsync(c->read_has_sel.p, 0, R, st));
+        // read_has_sel[R] and the tiles of the first radix pass's histogram
+        CU(c, cudaMemsetAsync(c->zbatch.p, 0, c->hist_off + ((size_t)c->sort_ntiles << per) * 4, st));
+        CU(c, cudaMemsetAsync(P<uint32_t>(c->ev_base), 0, (size_t)(R + 1) * 4, st));
     }
     c->user_prior = c->user_consumed = nullptr;
     DevOpts d = c->dopts;
@@ -435,16 +457,27 @@ int pgm_count(pgm_ctx *c) {
         }
         {
             StageTimer t(c, PGM_STAGE_DECODE_COUNT);
-            DecodeIO io = make_io(c);
-            if (c->db.mode == PGM_MODE_SS) k_decode_ss<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-            else k_decode_moves<false><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-            c->launches++;
+            DecodeIO io;
+            memset(&io, 0, sizeof io);
+            io.consumed = P<uint32_t>(c->consumed);
+            io.counts = P<uint32_t>(c->counts);
+            io.ev_base = P<uint32_t>(c->ev_base);
+            io.ev_cap = c->ev_cap;
+            io.key = P<uint32_t>(c->key); io.ev_start = P<uint32_t>(c->ev_start); io.ev_len = P<uint32_t>(c->ev_len); io.ev_read = P<uint32_t>(c->ev_read);
+            io.rflags = P<uint8_t>(c->rflags);
+            io.examined = &P<Scalars>(c->scalars)->examined;
+            io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end); io.sc_key = P<uint32_t>(c->sc_key);
+            io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
+            io.n_pass = P<uint32_t>(c->n_pass);
+            io.ticket = P<uint32_t>(c->dev_misc) + 1;
+            io.hist = HIST(c); io.ntiles_cap = c->sort_ntiles; io.hist_mask = (1u << per) - 1;
+            const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
+            k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            k_scan_records<<<cdiv(R, LB_TILE), PGM_BLOCK, 0, st>>>(io.n_pass, io.ev_base, R, next_lb<uint32_t>(c));
+            k_place<<<cdiv(R, DEC_WARPS), PGM_BLOCK, 0, st>>>(c->db, io);
+            c->launches += 3;
         }
         CU(c, cudaGetLastError());
-    }
-    {
-        StageTimer t(c, PGM_STAGE_SCAN);
-        RET((scan<uint32_t, uint32_t>(c, P<uint32_t>(c->n_pass), P<uint32_t>(c->ev_base), R, nullptr, true, c->blk32)));
     }
     c->state = ST_COUNTED;
     return PGM_OK;
@@ -467,20 +500,6 @@ int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consume
     return PGM_OK;
 }
 
-extern "C++" {
-template <typename T>
-static LbBuf<T> next_lb(pgm_ctx *c) {
-    LbBuf<T> st;
-    st.flag = P<uint32_t>(c->lb_flag);
-    st.agg = P<T>(c->lb_agg);
-    st.pre = P<T>(c->lb_pre);
-    st.ticket = P<uint32_t>(c->dev_misc) + 8 + (c->lb_ticket++ % (MISC_WORDS - 8));
-    c->lb_gen = (c->lb_gen + 1) & 0x3fffffffu;
-    if (c->lb_gen == 0) c->lb_gen = 1;
-    st.gen = c->lb_gen;
-    return st;
-}
-}  // extern "C++"
 
 int pgm_emit(pgm_ctx *c) {
     if (!c) return PGM_ERR_ARG;
@@ -492,15 +511,6 @@ int pgm_emit(pgm_ctx *c) {
     d.mode = c->db.mode;
     const uint32_t *n_ev = P<uint32_t>(c->ev_base) + R;  // device scalar: passing events
     const uint32_t pgrid = (uint32_t)c->n_sm * 4;
-    if (R && c->ev_cap) {
-        {
-            StageTimer t(c, PGM_STAGE_DECODE_EMIT);
-            DecodeIO io = make_io(c);
-            if (c->db.mode == PGM_MODE_SS) k_decode_ss<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-            else k_decode_moves<true><<<R, PGM_BLOCK, 0, st>>>(d, c->db, io);
-            c->launches++;
-        }
-    }
     // quota: keep / bucket_base / sel_base / totals after the batch, one launch
     {
         StageTimer t(c, PGM_STAGE_SELECT);
@@ -516,33 +526,32 @@ int pgm_emit(pgm_ctx *c) {
     if (R && c->ev_cap) {
         // stable LSD radix sort of (slot, event index); the last pass is fused with the selection (k_rank)
         StageTimer tsort(c, PGM_STAGE_SORT);
-        const uint32_t bits = bit_length(NS - 1);
-        const uint32_t passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
-        const uint32_t per = bits ? (bits + passes - 1) / passes : 1;
-        const uint32_t ntiles = cdiv(c->ev_cap, SORT_TILE);
+        uint32_t passes, per;
+        sort_plan(c, &passes, &per);
+        const uint32_t ntiles = c->sort_ntiles;
         const uint32_t sgrid = ntiles < pgrid ? ntiles : pgrid;
         uint32_t *kin = P<uint32_t>(c->key), *kout = P<uint32_t>(c->key2);
         uint32_t *vin = nullptr, *vout = P<uint32_t>(c->val);
         for (uint32_t p = 0; p < passes; p++) {
             const uint32_t shift = p * per;
-            k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
-            k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->hist), n_ev, 1u << per, ntiles,
+            if (p) { k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, HIST(c), ntiles); c->launches++; }   // pass 0: counted by k_decode
+            k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(HIST(c), n_ev, 1u << per, ntiles,
                                                                                            next_lb<uint32_t>(c));
-            c->launches += 2;
+            c->launches++;
             if (p + 1 < passes) {
-                k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, P<uint32_t>(c->hist), ntiles);
+                k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, HIST(c), ntiles);
                 c->launches++;
                 // ping-pong: keys key<->key2, values val<->val2
                 uint32_t *t = kin; kin = kout; kout = t;
                 vin = vout; vout = (vout == P<uint32_t>(c->val)) ? P<uint32_t>(c->val2) : P<uint32_t>(c->val);
             } else {
                 RankIO r;
-                r.n_events = n_ev; r.keys_in = kin; r.vals_in = vin; r.hist_scanned = P<uint32_t>(c->hist);
+                r.n_events = n_ev; r.keys_in = kin; r.vals_in = vin; r.hist_scanned = HIST(c);
                 r.ntiles_cap = ntiles; r.shift = shift; r.bits = per;
                 r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
                 r.ev_start = P<uint32_t>(c->ev_start); r.ev_len = P<uint32_t>(c->ev_len); r.ev_read = P<uint32_t>(c->ev_read);
                 r.sel_start = P<uint32_t>(c->sel_start); r.sel_len = P<uint32_t>(c->sel_len); r.sel_read = P<uint32_t>(c->sel_read);
-                r.ev_out = P<uint32_t>(c->ev_out); r.read_has_sel = P<uint8_t>(c->read_has_sel);
+                r.ev_out = P<uint32_t>(c->ev_out); r.read_has_sel = HAS_SEL(c);
                 k_rank<<<sgrid, PGM_BLOCK, 0, st>>>(r);
                 c->launches++;
             }
@@ -560,13 +569,13 @@ int pgm_emit(pgm_ctx *c) {
         if (c->opts.scaling && c->need_wide) {
             StageTimer t(c, PGM_STAGE_STATS);
             uint32_t *queue = P<uint32_t>(c->dev_misc);
-            k_stats_wide<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), P<uint8_t>(c->read_has_sel), P<ReadCal>(c->cal), queue,
+            k_stats_wide<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), HAS_SEL(c), P<ReadCal>(c->cal), queue,
                                                             P<uint32_t>(c->gscratch));
             c->launches++;
         }
         StageTimer t(c, PGM_STAGE_GATHER);
         SignalIO g;
-        g.rflags = P<uint8_t>(c->rflags); g.read_has_sel = P<uint8_t>(c->read_has_sel); g.cal = P<ReadCal>(c->cal);
+        g.rflags = P<uint8_t>(c->rflags); g.read_has_sel = HAS_SEL(c); g.cal = P<ReadCal>(c->cal);
         g.ev_base = P<uint32_t>(c->ev_base); g.ev_start = P<uint32_t>(c->ev_start); g.ev_len = P<uint32_t>(c->ev_len); g.ev_out = P<uint32_t>(c->ev_out);
         g.sel_off = P<uint64_t>(c->sel_off); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
         k_signal<<<R, SIG_THREADS, 0, st>>>(d, c->db, g);

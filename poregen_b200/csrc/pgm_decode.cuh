@@ -1,35 +1,42 @@
 // pgm_decode.cuh — alignment decode: move tables and ss:Z strings -> candidate events -> filters.
 //
-// One CTA per alignment record. Both encodings go through the same machinery: a block-wide
-// prefix scan over the alignment bytes turns "boundary" bytes (a set move, or an ss operator
-// with its run length) into event indices and raw-signal ranges; the shared back end
-// (pgm_eval_event) applies the reference's filters in the reference's order.
-//
-// Runs twice per batch: COUNT pass (per-slot counts + per-read totals) and EMIT pass (writes the
-// passing events compactly, in (record, position) order, at the offsets the scan over the
-// per-read totals produced). The ss token scan is only done in the COUNT pass; its per-event
-// scratch (start, end, base code, indel positions) is reused by the EMIT pass.
+// One WARP per alignment record, one launch per batch. Records are handed out by an atomic ticket in
+// alignment-file order. Per record:
+//   1. tokenise: the alignment bytes are read as aligned 16-byte words (32 lanes = 512 bytes per step),
+//      parsed from registers, and warp prefix scans turn "boundary" bytes (a set move, or an ss
+//      operator with its run length) into event indices and raw-signal ranges;
+//   2. evaluate: the shared back end (pgm_eval_event) applies the reference's filters in the reference's
+//      order; passing events are counted per slot and written compactly, in position order, to a
+//      per-record temporary;
+//   3. place (k_scan_records, k_place): a scan over the per-record totals gives the record's offset
+//      in the batch-wide (record, position) order; the events are copied there and, on the way,
+//      counted into the first radix pass's tile histogram.
 #pragma once
 #include "pgm_device.cuh"
+#include "pgm_scan.cuh"
+#include "pgm_sort.cuh"
 
-#define DEC_ITEMS 16  // alignment bytes per thread per chunk
-#define KM_ITEMS 4    // ss: k-mer start positions per thread per chunk
+#define DEC_WARPS PGM_WARPS
 
 struct DecodeIO {
     // quota state
     const uint32_t *consumed;  // [n_slots] kmer_frequency_map at batch start
-    uint32_t *counts;          // [n_slots] passing events of this batch (COUNT)
-    uint32_t *n_pass;          // [R] passing events per record (COUNT)
-    const uint32_t *ev_base;   // [R+1] exclusive scan of n_pass (EMIT)
+    uint32_t *counts;          // [n_slots] passing events of this batch
+    uint32_t *n_pass;          // [R] passing events per record
+    uint32_t *ev_base;         // [R+1] exclusive prefix of n_pass
     uint32_t ev_cap;           // capacity of the event arrays
-    uint32_t *key, *ev_start, *ev_len, *ev_read;  // [E] passing events, record-then-position order (EMIT)
+    uint32_t *key, *ev_start, *ev_len, *ev_read;  // [E] passing events, record-then-position order
     uint8_t *rflags;           // [R] PGM_RF_*
     unsigned long long *examined;
-    // ss scratch, indexed by align_off + event index / indel index
-    uint32_t *sc_start, *sc_end;
-    uint8_t *sc_code;
-    int32_t *sc_indel;
-    uint32_t *ss_L, *ss_nindel;  // [R]
+    // scratch, indexed by the record's alignment offset (+ event / indel index)
+    uint32_t *sc_start, *sc_end;   // ss: event bounds, then (in place) start / length of the passing events
+    uint32_t *sc_key;              // slot of the passing events (temporary, compact per record)
+    uint8_t *sc_code;              // ss: 2-bit base code per event
+    int32_t *sc_indel;             // ss: indel positions
+    uint32_t *ticket;          // record hand-out
+    // tile histogram of the first radix pass: hist[digit * ntiles_cap + tile]
+    uint32_t *hist;
+    uint32_t ntiles_cap, hist_mask;
 };
 
 // Reference gmove.cpp:641-662 (and 916-937, 1204-1225): duration filters, k-mer lookup, quota
@@ -52,109 +59,139 @@ __device__ __forceinline__ bool pgm_eval_event(const DevOpts &o, const uint32_t 
     return true;
 }
 
+__device__ __forceinline__ uint32_t warp_excl_scan_add(uint32_t v, uint32_t *total) {
+    const uint32_t inc = warp_incl_scan_add(v);
+    *total = __shfl_sync(0xffffffffu, inc, 31);
+    return inc - v;
+}
+__device__ __forceinline__ int warp_excl_scan_max(int v, int *total) {
+    const int inc = warp_incl_scan_max(v);
+    *total = __shfl_sync(0xffffffffu, inc, 31);
+    int ex = __shfl_up_sync(0xffffffffu, inc, 1);
+    if ((threadIdx.x & 31) == 0) ex = -1;
+    return ex;
+}
+
+// The 16 alignment bytes a lane owns in the current 512-byte step.
+struct Lane16 {
+    uint32_t w[4];
+    __device__ __forceinline__ uint32_t byte(int i) const { return (w[i >> 2] >> (8 * (i & 3))) & 0xffu; }
+};
+// Aligned 16-byte load of the word at `off` from the aligned base; words without any byte of the
+// record are not touched (a word holding at least one valid byte lies inside the allocation).
+__device__ __forceinline__ Lane16 load_lane16(const uint8_t *abase, uint32_t off, uint32_t span) {
+    Lane16 x;
+    if (off < span) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(abase + off));
+        x.w[0] = q.x; x.w[1] = q.y; x.w[2] = q.z; x.w[3] = q.w;
+    } else { x.w[0] = x.w[1] = x.w[2] = x.w[3] = 0; }
+    return x;
+}
+
+// Copies the record's passing events from the per-record temporary to their place in the batch-wide
+// order and counts them into the first radix pass's tile histogram.
+__device__ __forceinline__ void place_events(const DecodeIO &io, uint32_t r, uint32_t base, uint32_t n_pass, const uint32_t *t_key,
+                                             const uint32_t *t_start, const uint32_t *t_len) {
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t p = lane; p < n_pass; p += 32) {
+        const uint32_t P = base + p;
+        if (P >= io.ev_cap) break;
+        const uint32_t slot = t_key[p];
+        io.key[P] = slot; io.ev_start[P] = t_start[p]; io.ev_len[P] = t_len[p]; io.ev_read[P] = r;
+        atomicAdd(io.hist + (size_t)(slot & io.hist_mask) * io.ntiles_cap + P / SORT_TILE, 1u);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Move tables (TSV '0'/'1' bytes, or mv:B:c int8): reference gmove.cpp:620-690 and 1182-1252.
 // Event e (0-based over ALL set moves) lies between the e-th and (e+1)-th set move; it is examined
 // when e >= m and labelled with the k-mer at base s_off + (e - m). The run after the last set move
 // is never an event (the loop bound reads the terminator, gmove.cpp:632).
-template <bool EMIT>
-__global__ void __launch_bounds__(PGM_BLOCK) k_decode_moves(DevOpts o, DevBatch b, DecodeIO io) {
-    __shared__ uint32_t sm_u[PGM_WARPS + 1];
-    __shared__ int sm_i[PGM_WARPS + 1];
-    const uint32_t r = blockIdx.x;
-    const uint32_t tid = threadIdx.x;
-    if (io.rflags[r] != 0) {
-        if (!EMIT && tid == 0) io.n_pass[r] = 0;
-        return;
-    }
-    const pgm_read rd = b.reads[r];
+// Returns the number of passing events (written to the per-record temporary); *exam += events examined.
+__device__ __forceinline__ uint32_t decode_moves_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd,
+                                                        uint32_t *exam, bool *bad) {
+    const uint32_t lane = threadIdx.x & 31;
     const uint8_t *mv = b.align + rd.align_off;
     const uint8_t *seq = b.bases + rd.seq_off;
     const uint32_t M = rd.align_len;
-    const uint8_t one = (b.mode == PGM_MODE_MOVES_CHAR) ? (uint8_t)'1' : (uint8_t)1;
+    const uint32_t one = (b.mode == PGM_MODE_MOVES_CHAR) ? (uint32_t)'1' : 1u;
     const uint64_t n_sig = (uint64_t)rd.raw_len - rd.trim;
-    uint32_t ones_carry = 0;
+    const uint32_t head = (uint32_t)((uintptr_t)mv & 15);
+    const uint8_t *abase = mv - head;
+    const uint32_t span = head + M;
+    uint32_t *t_key = io.sc_key + rd.align_off, *t_start = io.sc_start + rd.align_off, *t_len = io.sc_end + rd.align_off;
+    uint32_t ones_carry = 0, pbase = 0, my_exam = 0;
     int last_carry = -1;
-    uint32_t out_run = EMIT ? io.ev_base[r] : 0;  // next output index (EMIT)
-    uint32_t pass_total = 0, exam_total = 0;
-
-    for (uint32_t base = 0; base < M; base += PGM_BLOCK * DEC_ITEMS) {
-        const uint32_t p0 = base + tid * DEC_ITEMS;
+    for (uint32_t cb = 0; cb < span; cb += 512) {
+        const uint32_t off = cb + 16 * lane;
+        const Lane16 x = load_lane16(abase, off, span);
+        const int p0 = (int)off - (int)head;     // string position of the lane's byte 0
         uint32_t bits = 0;
-        if (p0 < M) {
-            const uint32_t lim = min((uint32_t)DEC_ITEMS, M - p0);
-            for (uint32_t i = 0; i < lim; i++) bits |= (uint32_t)(__ldg(mv + p0 + i) == one) << i;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const uint32_t pos = off + i;
+            bits |= (uint32_t)(pos >= head && pos < span && x.byte(i) == one) << i;
         }
         const uint32_t cnt = __popc(bits);
-        const int lastpos = bits ? (int)(p0 + 31 - __clz(bits)) : -1;
-        uint32_t tot_cnt; int tot_last;
-        const uint32_t ex_cnt = block_excl_scan_add(cnt, sm_u, &tot_cnt);
-        const int ex_last = block_excl_scan_max(lastpos, sm_i, &tot_last);
-
-        // pass A: evaluate (count), pass B (EMIT only): evaluate again and write in order
-        uint32_t my_pass = 0;
-        for (int phase = 0; phase < (EMIT ? 2 : 1); phase++) {
-            uint32_t rank = ones_carry + ex_cnt;
-            int prev = max(last_carry, ex_last);
-            uint32_t w = bits;
-            uint32_t wr = 0;
-            if (EMIT && phase == 1) {
-                uint32_t tot_pass;
-                const uint32_t ex_pass = block_excl_scan_add(my_pass, sm_u, &tot_pass);
-                wr = out_run + ex_pass;
-                out_run += tot_pass;
+        const int lastpos = bits ? p0 + 31 - __clz(bits) : -1;
+        uint32_t tot_cnt;
+        int tot_last;
+        const uint32_t ex_cnt = ones_carry + warp_excl_scan_add(cnt, &tot_cnt);
+        const int ex_last = max(last_carry, warp_excl_scan_max(lastpos, &tot_last));
+        // the set move at position p with `rank` set moves before it closes event rank-1 (needs rank-1 >= m)
+        auto eval_at = [&](uint32_t rank, int prev, int p, uint32_t *slot, uint32_t *s2, uint32_t *len) {
+            const uint64_t ei = (uint64_t)rank - o.m - 1;
+            const uint64_t seqpos = (uint64_t)o.s_off + ei;
+            const uint32_t start = (uint32_t)((uint64_t)(uint32_t)prev * rd.stride);
+            const uint32_t end = (uint32_t)((uint64_t)(uint32_t)p * rd.stride);
+            bool id_ok = seqpos + o.k <= rd.seq_len;                                   // U4
+            uint32_t id = 0;
+            if (id_ok) {
+                for (uint32_t t = 0; t < o.k; t++) {
+                    const uint32_t c = pgm_base_code(__ldg(seq + seqpos + t), o.fourth, false);
+                    id_ok &= (c != 0xFF);
+                    id = (id << 2) | (c & 3);
+                }
             }
+            return pgm_eval_event(o, io.consumed, start, end, id, id_ok, n_sig, slot, s2, len);
+        };
+        uint32_t okmask = 0;
+        {
+            uint32_t rank = ex_cnt, w = bits;
+            int prev = ex_last;
             while (w) {
-                const uint32_t i = __ffs(w) - 1;
+                const int i = __ffs(w) - 1;
                 w &= w - 1;
-                const uint32_t p = p0 + i;
-                if (rank > o.m) {  // this set move closes event (rank-1); needs rank-1 >= m
-                    const uint64_t ei = (uint64_t)rank - o.m - 1;
-                    const uint64_t seqpos = (uint64_t)o.s_off + ei;
-                    const uint32_t start = (uint32_t)((uint64_t)(uint32_t)prev * rd.stride);
-                    const uint32_t end = (uint32_t)((uint64_t)p * rd.stride);
-                    bool id_ok = seqpos + o.k <= rd.seq_len;                                   // U4
-                    uint32_t id = 0;
-                    if (id_ok) {
-                        for (uint32_t t = 0; t < o.k; t++) {
-                            const uint32_t c = pgm_base_code(__ldg(seq + seqpos + t), o.fourth, false);
-                            id_ok &= (c != 0xFF);
-                            id = (id << 2) | (c & 3);
-                        }
-                    }
+                if (rank > o.m) {
                     uint32_t slot, s2, len;
-                    const bool ok = pgm_eval_event(o, io.consumed, start, end, id, id_ok, n_sig, &slot, &s2, &len);
-                    if (phase == 0) {
-                        exam_total++;
-                        if (ok) {
-                            my_pass++;
-                            if (!EMIT) atomicAdd(io.counts + slot, 1u);
-                        }
-                    } else if (ok) {
-                        if (wr < io.ev_cap) {
-                            io.key[wr] = slot; io.ev_start[wr] = s2; io.ev_len[wr] = len; io.ev_read[wr] = r;
-                        }
-                        wr++;
+                    my_exam++;
+                    if (eval_at(rank, prev, p0 + i, &slot, &s2, &len)) {
+                        okmask |= 1u << i;
+                        atomicAdd(io.counts + slot, 1u);
                     }
                 }
-                prev = (int)p;
+                prev = p0 + i;
                 rank++;
             }
         }
-        pass_total += my_pass;
+        uint32_t tot_pass;
+        uint32_t wr = pbase + warp_excl_scan_add(__popc(okmask), &tot_pass);
+        for (uint32_t w = okmask; w; w &= w - 1) {
+            const int i = __ffs(w) - 1;
+            const uint32_t below = bits & ((1u << i) - 1);
+            const int prev = below ? p0 + 31 - __clz(below) : ex_last;
+            uint32_t slot = 0, s2 = 0, len = 0;
+            eval_at(ex_cnt + __popc(below), prev, p0 + i, &slot, &s2, &len);
+            t_key[wr] = slot; t_start[wr] = s2; t_len[wr] = len;
+            wr++;
+        }
+        pbase += tot_pass;
         ones_carry += tot_cnt;
         last_carry = max(last_carry, tot_last);
     }
-    if (!EMIT) {
-        uint32_t tp, te;
-        block_excl_scan_add(pass_total, sm_u, &tp);
-        block_excl_scan_add(exam_total, sm_u, &te);
-        if (tid == 0) {
-            io.n_pass[r] = tp;
-            if (te) atomicAdd(io.examined, (unsigned long long)te);
-            if (ones_carry <= o.m) io.rflags[r] |= (PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED);       // U1
-        }
-    }
+    *exam += my_exam;
+    *bad = ones_carry <= o.m;                                                          // U1
+    return pbase;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -162,27 +199,10 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_decode_moves(DevOpts o, DevBatch 
 //   ','  a base mapped to n samples: event j (the j-th ','), raw range [i_raw, i_raw+n)
 //   'I'  n samples with no base: i_raw += n, indel position = number of ',' so far
 //   'D'  n bases with no samples: i_k += n, indel position = number of ',' so far
-// The exclusive block scan carries (raw advance, ',' count, deleted bases, indel count).
+// The warp scan carries (raw advance, ',' count, deleted bases, indel count).
 __device__ __forceinline__ bool ss_is_op(uint32_t c) { return c == ',' || c == 'I' || c == 'D'; }
-__device__ __forceinline__ bool ss_is_digit(uint32_t c) { return c >= '0' && c <= '9'; }
-
-// Parses the run length that ends just before position p. Returns false for U7 (no digits, or
-// more than 9 digits).
-__device__ __forceinline__ bool ss_number_before(const uint8_t *ss, uint32_t p, uint32_t *val) {
-    uint32_t v = 0, mult = 1, nd = 0;
-    int q = (int)p - 1;
-    while (q >= 0) {
-        const uint32_t c = __ldg(ss + q);
-        if (!ss_is_digit(c)) break;
-        if (nd == 9) return false;
-        v += (c - '0') * mult;
-        mult *= 10;
-        nd++;
-        q--;
-    }
-    *val = v;
-    return nd > 0;
-}
+__device__ __forceinline__ bool ss_is_digit(uint32_t c) { return c - '0' <= 9u; }
+__constant__ uint32_t c_pow10[10] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u, 1000000000u};
 
 // indel_pos as the reference builds it (gmove.cpp:822-826, 843-845, 877-885), entries 0..n:
 //   P[0] = -st_k ; DNA: P[t] = pos[t-1] ; RNA: P[t] = L - pos[n-t]      (non-decreasing)
@@ -210,132 +230,201 @@ __device__ __forceinline__ bool ss_pick(const int32_t *pos, uint32_t n, int last
     return false;
 }
 
-template <bool EMIT>
-__global__ void __launch_bounds__(PGM_BLOCK) k_decode_ss(DevOpts o, DevBatch b, DecodeIO io) {
-    __shared__ uint32_t sm_u[PGM_WARPS + 1];
-    __shared__ uint32_t sm_bad;
-    const uint32_t r = blockIdx.x;
-    const uint32_t tid = threadIdx.x;
-    if (io.rflags[r] != 0) {
-        if (!EMIT && tid == 0) io.n_pass[r] = 0;
-        return;
-    }
-    const pgm_read rd = b.reads[r];
+// Digits pending at a lane boundary: value and count (count 10 = more than 9 digits, U7).
+struct Pend { uint32_t v, n; };
+__device__ __forceinline__ Pend pend_join(Pend a, Pend b) {   // digits a followed by digits b
+    Pend r;
+    r.n = a.n + b.n;
+    if (r.n > 9) { r.n = 10; r.v = 0; }
+    else r.v = a.v * c_pow10[b.n] + b.v;
+    return r;
+}
+
+__device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd,
+                                                     uint32_t *exam, bool *bad_out) {
+    const uint32_t lane = threadIdx.x & 31;
     const uint8_t *ss = b.align + rd.align_off;
     const uint8_t *seq = b.bases + rd.seq_off;
     const uint32_t T = rd.align_len;
     const bool rna = (rd.flags & PGM_READ_RNA) != 0;
     const uint64_t n_sig = rd.raw_len;                  // the ss path never trims (gmove.cpp:750-753)
-    uint32_t *sc_start = io.sc_start + rd.align_off;
-    uint32_t *sc_end = io.sc_end + rd.align_off;
+    uint32_t *sc_start = io.sc_start + rd.align_off, *sc_end = io.sc_end + rd.align_off, *t_key = io.sc_key + rd.align_off;
     uint8_t *sc_code = io.sc_code + rd.align_off;
     int32_t *sc_indel = io.sc_indel + rd.align_off;
+    const uint32_t head = (uint32_t)((uintptr_t)ss & 15);
+    const uint8_t *abase = ss - head;
+    const uint32_t span = head + T;
 
-    uint32_t L, n_indel;
-    if (!EMIT) {
-        if (tid == 0) sm_bad = 0;
-        uint32_t c_raw = rd.query_start, c_com = 0, c_del = 0, c_ind = 0;  // carries
-        __syncthreads();
-        for (uint32_t base = 0; base < T; base += PGM_BLOCK * DEC_ITEMS) {
-            const uint32_t p0 = base + tid * DEC_ITEMS;
-            const uint32_t lim = (p0 < T) ? min((uint32_t)DEC_ITEMS, T - p0) : 0;
-            uint32_t a = 0, c = 0, d = 0, g = 0;
-            bool bad = false;
-            for (uint32_t i = 0; i < lim; i++) {
-                const uint32_t ch = __ldg(ss + p0 + i);
-                if (ss_is_op(ch)) {
-                    uint32_t num;
-                    if (!ss_number_before(ss, p0 + i, &num)) { bad = true; num = 0; }
-                    if (ch == ',') { a += num; c++; }
-                    else if (ch == 'I') { a += num; g++; }
-                    else { d += num; g++; }
-                } else if (!ss_is_digit(ch)) bad = true;
-            }
-            if (bad) atomicOr(&sm_bad, 1u);
-            uint32_t ta, tc, td, tg;
-            uint32_t xa = c_raw + block_excl_scan_add(a, sm_u, &ta);
-            uint32_t xc = c_com + block_excl_scan_add(c, sm_u, &tc);
-            uint32_t xd = c_del + block_excl_scan_add(d, sm_u, &td);
-            uint32_t xg = c_ind + block_excl_scan_add(g, sm_u, &tg);
-            for (uint32_t i = 0; i < lim; i++) {
-                const uint32_t ch = __ldg(ss + p0 + i);
-                if (!ss_is_op(ch)) continue;
-                uint32_t num = 0;
-                ss_number_before(ss, p0 + i, &num);
-                if (ch == ',') {
-                    const uint64_t ik = (uint64_t)xc + xd;
-                    const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
-                    uint32_t code = 0xFF;
-                    if (si >= 0 && si < (int64_t)rd.seq_len) code = pgm_base_code(__ldg(seq + si), o.fourth, rna);
-                    sc_start[xc] = xa; sc_end[xc] = xa + num; sc_code[xc] = (uint8_t)code;
-                    xa += num; xc++;
-                } else if (ch == 'I') { sc_indel[xg] = (int32_t)xc; xa += num; xg++; }
-                else { sc_indel[xg] = (int32_t)xc; xd += num; xg++; }
-            }
-            c_raw += ta; c_com += tc; c_del += td; c_ind += tg;
+    // ---- 1. tokenise
+    uint32_t c_raw = rd.query_start, c_com = 0, c_del = 0, c_ind = 0;   // carries
+    Pend carry = {0u, 0u};
+    bool bad = false;
+    for (uint32_t cb = 0; cb < span; cb += 512) {
+        const uint32_t off = cb + 16 * lane;
+        const Lane16 x = load_lane16(abase, off, span);
+        // pass A: per-lane sums; the first operator's run length may start in earlier lanes
+        uint32_t num = 0, nd = 0, a = 0, cg = 0, d = 0;
+        uint32_t first_op = 0, lead_v = 0, lead_n = 0;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const uint32_t pos = off + i;
+            if (pos < head || pos >= span) continue;
+            const uint32_t ch = x.byte(i);
+            if (ss_is_digit(ch)) {
+                if (nd < 9) { num = num * 10 + (ch - '0'); nd++; } else nd = 10;
+            } else if (ss_is_op(ch)) {
+                if (!first_op) { first_op = ch; lead_v = num; lead_n = nd; }
+                else {
+                    if (nd == 0 || nd > 9) bad = true;
+                    if (ch == ',') { a += num; cg += 1; }
+                    else if (ch == 'I') { a += num; cg += 0x10000u; }
+                    else { d += num; cg += 0x10000u; }
+                }
+                num = 0; nd = 0;
+            } else bad = true;
         }
-        __syncthreads();  // scratch writes of this CTA are visible to it from here on
-        L = c_com; n_indel = c_ind;
-        if (sm_bad) {     // U7
-            if (tid == 0) { io.rflags[r] |= (PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED); io.n_pass[r] = 0; io.ss_L[r] = 0; io.ss_nindel[r] = 0; }
-            return;
+        // digits pending when the lane starts: the previous lane's trailing digits, joined with earlier
+        // lanes' while the previous lane holds no operator at all
+        Pend pre;
+        bool done;
+        {
+            Pend mine = {num, nd};                       // trailing digits (all of them when the lane has no operator)
+            pre.v = __shfl_up_sync(0xffffffffu, mine.v, 1);
+            pre.n = __shfl_up_sync(0xffffffffu, mine.n, 1);
+            done = __shfl_up_sync(0xffffffffu, first_op != 0 || off >= span, 1);   // lanes past the end terminate a chain
+            if (lane == 0) { pre = carry; done = true; }
+            while (__any_sync(0xffffffffu, !done)) {
+                Pend q;
+                q.v = __shfl_up_sync(0xffffffffu, pre.v, 1);
+                q.n = __shfl_up_sync(0xffffffffu, pre.n, 1);
+                const bool qd = __shfl_up_sync(0xffffffffu, done, 1);
+                if (!done) { pre = pend_join(q, pre); done = qd || pre.n >= 10; }
+            }
+            const Pend out = first_op ? mine : pend_join(pre, mine);
+            carry.v = __shfl_sync(0xffffffffu, out.v, 31);
+            carry.n = __shfl_sync(0xffffffffu, out.n, 31);
         }
-        if (tid == 0) { io.ss_L[r] = L; io.ss_nindel[r] = n_indel; }
-    } else {
-        L = io.ss_L[r]; n_indel = io.ss_nindel[r];
+        uint32_t first_num = 0;
+        if (first_op) {
+            const Pend lead = {lead_v, lead_n};
+            const Pend full = pend_join(pre, lead);
+            if (full.n == 0 || full.n > 9) bad = true;
+            first_num = full.v;
+            if (first_op == ',') { a += first_num; cg += 1; }
+            else if (first_op == 'I') { a += first_num; cg += 0x10000u; }
+            else { d += first_num; cg += 0x10000u; }
+        }
+        uint32_t ta, td, tcg;
+        uint32_t xa = c_raw + warp_excl_scan_add(a, &ta);
+        uint32_t xd = c_del + warp_excl_scan_add(d, &td);
+        const uint32_t ecg = warp_excl_scan_add(cg, &tcg);
+        uint32_t xc = c_com + (ecg & 0xffffu), xg = c_ind + (ecg >> 16);
+        // pass B: the same walk, now writing the per-event scratch
+        if (first_op) {
+            num = 0;
+            bool first = true;
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                const uint32_t pos = off + i;
+                if (pos < head || pos >= span) continue;
+                const uint32_t ch = x.byte(i);
+                if (ss_is_digit(ch)) num = num * 10 + (ch - '0');
+                else if (ss_is_op(ch)) {
+                    const uint32_t v = first ? first_num : num;
+                    first = false;
+                    if (ch == ',') {
+                        const uint64_t ik = (uint64_t)xc + xd;
+                        const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
+                        uint32_t code = 0xFF;
+                        if (si >= 0 && si < (int64_t)rd.seq_len) code = pgm_base_code(__ldg(seq + si), o.fourth, rna);
+                        sc_start[xc] = xa; sc_end[xc] = xa + v; sc_code[xc] = (uint8_t)code;
+                        xa += v; xc++;
+                    } else if (ch == 'I') { sc_indel[xg] = (int32_t)xc; xa += v; xg++; }
+                    else { sc_indel[xg] = (int32_t)xc; xd += v; xg++; }
+                    num = 0;
+                }
+            }
+        }
+        c_raw += ta; c_del += td; c_com += tcg & 0xffffu; c_ind += tcg >> 16;
     }
-
-    uint32_t pass_total = 0, exam_total = 0;
-    uint32_t out_run = EMIT ? io.ev_base[r] : 0;
+    if (__any_sync(0xffffffffu, bad)) { *bad_out = true; return 0; }   // U7
+    __syncwarp();   // scratch writes of this warp are visible to it from here on
+    // ---- 2. evaluate: one k-mer start per lane and round, passing events compacted in place
+    const uint32_t L = c_com, n_indel = c_ind;
     const int k = (int)o.k;
     const int last = (int)((uint32_t)rd.end_k + o.pick_margin);             // gmove.cpp:885
     const uint32_t n_i = ((int)L >= k) ? L - o.k + 1 : 0;                   // U5
-    for (uint32_t base = 0; base < n_i; base += PGM_BLOCK * KM_ITEMS) {
-        const uint32_t i0 = base + tid * KM_ITEMS;
-        uint32_t my_pass = 0;
-        for (int phase = 0; phase < (EMIT ? 2 : 1); phase++) {
-            uint32_t wr = 0;
-            if (EMIT && phase == 1) {
-                uint32_t tot_pass;
-                const uint32_t ex = block_excl_scan_add(my_pass, sm_u, &tot_pass);
-                wr = out_run + ex;
-                out_run += tot_pass;
-            }
-            for (uint32_t u = 0; u < KM_ITEMS; u++) {
-                const uint32_t i = i0 + u;
-                if (i >= n_i) break;
-                const uint64_t j = (uint64_t)i + o.m;
-                if (j >= L) continue;                                        // gmove.cpp:892 (-1 cell), U5
-                const int left = rna ? (int)L - (int)i - k : (int)i;        // gmove.cpp:899,906
-                if (phase == 0) exam_total++;
-                if (!ss_pick(sc_indel, n_indel, last, left, k, (int)o.pick_margin, (int)L, rd.st_k, rna)) continue;
-                uint32_t id = 0; bool id_ok = true;
+    uint32_t pbase = 0, my_exam = 0;
+    for (uint32_t base = 0; base < n_i; base += 32) {
+        const uint32_t i = base + lane;
+        const uint64_t j = (uint64_t)i + o.m;
+        bool ok = false;
+        uint32_t slot = 0, s2 = 0, len = 0;
+        if (i < n_i && j < L) {                                              // gmove.cpp:892 (-1 cell), U5
+            my_exam++;
+            const int left = rna ? (int)L - (int)i - k : (int)i;            // gmove.cpp:899,906
+            if (ss_pick(sc_indel, n_indel, last, left, k, (int)o.pick_margin, (int)L, rd.st_k, rna)) {
+                uint32_t id = 0;
+                bool id_ok = true;
                 for (int t = 0; t < k; t++) {
                     const uint32_t c = sc_code[rna ? (i + k - 1 - t) : (i + t)];
                     id_ok &= (c != 0xFF);
                     id = (id << 2) | (c & 3);
                 }
-                uint32_t slot, s2, len;
-                const bool ok = pgm_eval_event(o, io.consumed, sc_start[j], sc_end[j], id, id_ok, n_sig, &slot, &s2, &len);
-                if (!ok) continue;
-                if (phase == 0) {
-                    my_pass++;
-                    if (!EMIT) atomicAdd(io.counts + slot, 1u);
-                } else {
-                    if (wr < io.ev_cap) { io.key[wr] = slot; io.ev_start[wr] = s2; io.ev_len[wr] = len; io.ev_read[wr] = r; }
-                    wr++;
-                }
+                ok = pgm_eval_event(o, io.consumed, sc_start[j], sc_end[j], id, id_ok, n_sig, &slot, &s2, &len);
             }
         }
-        pass_total += my_pass;
-    }
-    if (!EMIT) {
-        uint32_t tp, te;
-        block_excl_scan_add(pass_total, sm_u, &tp);
-        block_excl_scan_add(exam_total, sm_u, &te);
-        if (tid == 0) {
-            io.n_pass[r] = tp;
-            if (te) atomicAdd(io.examined, (unsigned long long)te);
+        const uint32_t bm = __ballot_sync(0xffffffffu, ok);   // every read of this round is done: positions <= i may be overwritten
+        if (ok) {
+            const uint32_t p = pbase + __popc(bm & ((1u << lane) - 1));
+            atomicAdd(io.counts + slot, 1u);
+            t_key[p] = slot; sc_start[p] = s2; sc_end[p] = len;
         }
+        pbase += __popc(bm);
     }
+    __syncwarp();
+    *exam += my_exam;
+    return pbase;
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, DecodeIO io) {
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t exam = 0;
+    for (;;) {
+        uint32_t r = 0;
+        if (lane == 0) r = atomicAdd(io.ticket, 1u);
+        r = __shfl_sync(0xffffffffu, r, 0);
+        if (r >= b.n_reads) break;
+        uint32_t n_pass = 0;
+        bool bad = false;
+        if (io.rflags[r] == 0) {
+            const pgm_read rd = b.reads[r];
+            if (b.mode == PGM_MODE_SS) n_pass = decode_ss_record(o, b, io, rd, &exam, &bad);
+            else n_pass = decode_moves_record(o, b, io, rd, &exam, &bad);
+            if (bad) {
+                n_pass = 0;
+                if (lane == 0) io.rflags[r] |= (PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED);
+            }
+        }
+        if (lane == 0) io.n_pass[r] = n_pass;
+    }
+    exam = warp_sum_t<uint32_t>(exam);
+    if (lane == 0 && exam) atomicAdd(io.examined, (unsigned long long)exam);
+}
+
+// ev_base = exclusive scan of the per-record totals (one launch, look-back over tiles of 4096 records)
+__global__ void __launch_bounds__(PGM_BLOCK) k_scan_records(const uint32_t *n_pass, uint32_t *ev_base, uint32_t R, LbBuf<uint32_t> st) {
+    lb_scan<uint32_t>(R, st, [&](uint64_t r) { return n_pass[r]; }, [&](uint64_t r, uint32_t ex, uint32_t) { ev_base[r] = ex; },
+                      [&](uint32_t tot) { ev_base[R] = tot; });
+}
+
+// one warp per record: temporary -> batch-wide order (+ first-pass tile histogram)
+__global__ void __launch_bounds__(PGM_BLOCK) k_place(DevBatch b, DecodeIO io) {
+    const uint32_t r = blockIdx.x * DEC_WARPS + (threadIdx.x >> 5);
+    if (r >= b.n_reads) return;
+    const uint32_t base = io.ev_base[r], n_pass = io.ev_base[r + 1] - base;
+    if (!n_pass) return;
+    const uint64_t ao = b.reads[r].align_off;
+    place_events(io, r, base, n_pass, io.sc_key + ao, io.sc_start + ao, io.sc_end + ao);
 }
