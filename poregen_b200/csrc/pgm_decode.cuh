@@ -2,9 +2,10 @@
 //
 // One WARP per alignment record, one launch per batch. Records are handed out by an atomic ticket in
 // alignment-file order. Per record:
-//   1. tokenise: the alignment bytes are read as aligned 16-byte words (32 lanes = 512 bytes per step),
-//      parsed from registers, and warp prefix scans turn "boundary" bytes (a set move, or an ss
-//      operator with its run length) into event indices and raw-signal ranges;
+//   1. tokenise: the alignment bytes are read as aligned 16-byte words (32 lanes = 512 bytes per step);
+//      "boundary" bytes (a set move, or an ss operator) are found with byte-parallel word arithmetic,
+//      one lane per boundary parses the run length, and warp prefix scans turn the boundaries into
+//      event indices and raw-signal ranges;
 //   2. evaluate: the shared back end (pgm_eval_event) applies the reference's filters in the reference's
 //      order; passing events are counted per slot and written compactly, in position order, to a
 //      per-record temporary;
@@ -72,6 +73,11 @@ __device__ __forceinline__ int warp_excl_scan_max(int v, int *total) {
     return ex;
 }
 
+// Byte-parallel helpers on 32-bit words: 0x80 in every byte of y that is zero (exact, no borrow
+// artefacts), and the four flag bits 7,15,23,31 packed into bits 0..3.
+__device__ __forceinline__ uint32_t byte_is_zero(uint32_t y) { return ~(((y & 0x7f7f7f7fu) + 0x7f7f7f7fu) | y | 0x7f7f7f7fu); }
+__device__ __forceinline__ uint32_t byte_nibble(uint32_t m) { return (((m >> 7) * 0x00204081u) >> 21) & 0xfu; }
+
 // The 16 alignment bytes a lane owns in the current 512-byte step.
 struct Lane16 {
     uint32_t w[4];
@@ -114,7 +120,7 @@ __device__ __forceinline__ uint32_t decode_moves_record(const DevOpts &o, const 
     const uint8_t *mv = b.align + rd.align_off;
     const uint8_t *seq = b.bases + rd.seq_off;
     const uint32_t M = rd.align_len;
-    const uint32_t one = (b.mode == PGM_MODE_MOVES_CHAR) ? (uint32_t)'1' : 1u;
+    const uint32_t one4 = (b.mode == PGM_MODE_MOVES_CHAR) ? 0x31313131u : 0x01010101u;
     const uint64_t n_sig = (uint64_t)rd.raw_len - rd.trim;
     const uint32_t head = (uint32_t)((uintptr_t)mv & 15);
     const uint8_t *abase = mv - head;
@@ -126,12 +132,12 @@ __device__ __forceinline__ uint32_t decode_moves_record(const DevOpts &o, const 
         const uint32_t off = cb + 16 * lane;
         const Lane16 x = load_lane16(abase, off, span);
         const int p0 = (int)off - (int)head;     // string position of the lane's byte 0
-        uint32_t bits = 0;
+        const uint32_t lo = (off < head) ? min(16u, head - off) : 0u;
+        const uint32_t hi = (off >= span) ? 0u : min(16u, span - off);
+        uint32_t bits = 0;                       // bit i <=> byte i of the lane is a set move
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const uint32_t pos = off + i;
-            bits |= (uint32_t)(pos >= head && pos < span && x.byte(i) == one) << i;
-        }
+        for (int wi = 0; wi < 4; wi++) bits |= byte_nibble(byte_is_zero(x.w[wi] ^ one4)) << (4 * wi);
+        bits &= (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
         const uint32_t cnt = __popc(bits);
         const int lastpos = bits ? p0 + 31 - __clz(bits) : -1;
         uint32_t tot_cnt;
@@ -202,7 +208,6 @@ __device__ __forceinline__ uint32_t decode_moves_record(const DevOpts &o, const 
 // The warp scan carries (raw advance, ',' count, deleted bases, indel count).
 __device__ __forceinline__ bool ss_is_op(uint32_t c) { return c == ',' || c == 'I' || c == 'D'; }
 __device__ __forceinline__ bool ss_is_digit(uint32_t c) { return c - '0' <= 9u; }
-__constant__ uint32_t c_pow10[10] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u, 1000000000u};
 
 // indel_pos as the reference builds it (gmove.cpp:822-826, 843-845, 877-885), entries 0..n:
 //   P[0] = -st_k ; DNA: P[t] = pos[t-1] ; RNA: P[t] = L - pos[n-t]      (non-decreasing)
@@ -230,18 +235,8 @@ __device__ __forceinline__ bool ss_pick(const int32_t *pos, uint32_t n, int last
     return false;
 }
 
-// Digits pending at a lane boundary: value and count (count 10 = more than 9 digits, U7).
-struct Pend { uint32_t v, n; };
-__device__ __forceinline__ Pend pend_join(Pend a, Pend b) {   // digits a followed by digits b
-    Pend r;
-    r.n = a.n + b.n;
-    if (r.n > 9) { r.n = 10; r.v = 0; }
-    else r.v = a.v * c_pow10[b.n] + b.v;
-    return r;
-}
-
 __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd,
-                                                     uint32_t *exam, bool *bad_out) {
+                                                     uint8_t *wbuf, uint16_t *wpos, uint32_t *exam, bool *bad_out) {
     const uint32_t lane = threadIdx.x & 31;
     const uint8_t *ss = b.align + rd.align_off;
     const uint8_t *seq = b.bases + rd.seq_off;
@@ -255,97 +250,72 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
     const uint8_t *abase = ss - head;
     const uint32_t span = head + T;
 
-    // ---- 1. tokenise
+    // ---- 1. tokenise: 512 bytes per step are staged in the warp's shared buffer (with the previous 16
+    // bytes as a halo); operator positions come from byte-parallel word tricks, then ONE LANE PER TOKEN
+    // parses its run length backwards and three warp scans place the token.
     uint32_t c_raw = rd.query_start, c_com = 0, c_del = 0, c_ind = 0;   // carries
-    Pend carry = {0u, 0u};
     bool bad = false;
+    if (lane < 4) reinterpret_cast<uint32_t *>(wbuf)[lane] = 0;
     for (uint32_t cb = 0; cb < span; cb += 512) {
         const uint32_t off = cb + 16 * lane;
         const Lane16 x = load_lane16(abase, off, span);
-        // pass A: per-lane sums; the first operator's run length may start in earlier lanes
-        uint32_t num = 0, nd = 0, a = 0, cg = 0, d = 0;
-        uint32_t first_op = 0, lead_v = 0, lead_n = 0;
+        // bytes of the lane that belong to the string: bit i <=> head <= off + i < span
+        const uint32_t lo = (off < head) ? min(16u, head - off) : 0u;
+        const uint32_t hi = (off >= span) ? 0u : min(16u, span - off);
+        const uint32_t vm = (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+        uint32_t opm = 0, dgm = 0;
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const uint32_t pos = off + i;
-            if (pos < head || pos >= span) continue;
-            const uint32_t ch = x.byte(i);
-            if (ss_is_digit(ch)) {
-                if (nd < 9) { num = num * 10 + (ch - '0'); nd++; } else nd = 10;
-            } else if (ss_is_op(ch)) {
-                if (!first_op) { first_op = ch; lead_v = num; lead_n = nd; }
-                else {
-                    if (nd == 0 || nd > 9) bad = true;
-                    if (ch == ',') { a += num; cg += 1; }
-                    else if (ch == 'I') { a += num; cg += 0x10000u; }
-                    else { d += num; cg += 0x10000u; }
+        for (int wi = 0; wi < 4; wi++) {
+            const uint32_t w = x.w[wi];
+            const uint32_t e = byte_is_zero(w ^ 0x2c2c2c2cu) | byte_is_zero(w ^ 0x49494949u) | byte_is_zero(w ^ 0x44444444u);   // ',' 'I' 'D'
+            const uint32_t wl = w & 0x7f7f7f7fu;
+            const uint32_t dg = (wl + 0x50505050u) & ~(wl + 0x46464646u) & ~w & 0x80808080u;                 // '0'..'9'
+            opm |= byte_nibble(e) << (4 * wi);
+            dgm |= byte_nibble(dg) << (4 * wi);
+        }
+        opm &= vm; dgm &= vm;
+        if ((opm | dgm) != vm) bad = true;                                   // gmove.cpp:867
+        uint32_t ntok;
+        uint32_t tb = warp_excl_scan_add(__popc(opm), &ntok);
+        *reinterpret_cast<uint4 *>(wbuf + 16 + 16 * lane) = make_uint4(x.w[0], x.w[1], x.w[2], x.w[3]);
+        for (uint32_t m = opm; m; m &= m - 1) wpos[tb++] = (uint16_t)(16 * lane + __ffs(m) - 1);
+        __syncwarp();
+        const int sb = (cb == 0) ? (int)head : -16;                          // first byte a run length may use (chunk coordinates)
+        for (uint32_t t0 = 0; t0 < ntok; t0 += 32) {
+            const uint32_t t = t0 + lane;
+            uint32_t ch = 0, num = 0, a = 0, d = 0, cg = 0;
+            if (t < ntok) {
+                const int pos = wpos[t];
+                ch = wbuf[16 + pos];
+                uint32_t nd = 0, mult = 1;
+                for (int q = pos - 1; q >= sb && nd < 10; q--) {
+                    const uint32_t dgt = (uint32_t)wbuf[16 + q] - '0';
+                    if (dgt > 9) break;
+                    if (nd < 9) num += dgt * mult;
+                    mult *= 10;
+                    nd++;
                 }
-                num = 0; nd = 0;
-            } else bad = true;
-        }
-        // digits pending when the lane starts: the previous lane's trailing digits, joined with earlier
-        // lanes' while the previous lane holds no operator at all
-        Pend pre;
-        bool done;
-        {
-            Pend mine = {num, nd};                       // trailing digits (all of them when the lane has no operator)
-            pre.v = __shfl_up_sync(0xffffffffu, mine.v, 1);
-            pre.n = __shfl_up_sync(0xffffffffu, mine.n, 1);
-            done = __shfl_up_sync(0xffffffffu, first_op != 0 || off >= span, 1);   // lanes past the end terminate a chain
-            if (lane == 0) { pre = carry; done = true; }
-            while (__any_sync(0xffffffffu, !done)) {
-                Pend q;
-                q.v = __shfl_up_sync(0xffffffffu, pre.v, 1);
-                q.n = __shfl_up_sync(0xffffffffu, pre.n, 1);
-                const bool qd = __shfl_up_sync(0xffffffffu, done, 1);
-                if (!done) { pre = pend_join(q, pre); done = qd || pre.n >= 10; }
+                if (nd == 0 || nd > 9) bad = true;                           // gmove.cpp:834, U7
+                if (ch == ',') { a = num; cg = 1; }
+                else if (ch == 'I') { a = num; cg = 0x10000u; }
+                else { d = num; cg = 0x10000u; }
             }
-            const Pend out = first_op ? mine : pend_join(pre, mine);
-            carry.v = __shfl_sync(0xffffffffu, out.v, 31);
-            carry.n = __shfl_sync(0xffffffffu, out.n, 31);
+            uint32_t ta, td, tcg;
+            const uint32_t xa = c_raw + warp_excl_scan_add(a, &ta);
+            const uint32_t xd = c_del + warp_excl_scan_add(d, &td);
+            const uint32_t ecg = warp_excl_scan_add(cg, &tcg);
+            const uint32_t xc = c_com + (ecg & 0xffffu), xg = c_ind + (ecg >> 16);
+            if (ch == ',') {
+                const uint64_t ik = (uint64_t)xc + xd;
+                const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
+                uint32_t code = 0xFF;
+                if (si >= 0 && si < (int64_t)rd.seq_len) code = pgm_base_code(__ldg(seq + si), o.fourth, rna);
+                sc_start[xc] = xa; sc_end[xc] = xa + num; sc_code[xc] = (uint8_t)code;
+            } else if (ch) sc_indel[xg] = (int32_t)xc;
+            c_raw += ta; c_del += td; c_com += tcg & 0xffffu; c_ind += tcg >> 16;
         }
-        uint32_t first_num = 0;
-        if (first_op) {
-            const Pend lead = {lead_v, lead_n};
-            const Pend full = pend_join(pre, lead);
-            if (full.n == 0 || full.n > 9) bad = true;
-            first_num = full.v;
-            if (first_op == ',') { a += first_num; cg += 1; }
-            else if (first_op == 'I') { a += first_num; cg += 0x10000u; }
-            else { d += first_num; cg += 0x10000u; }
-        }
-        uint32_t ta, td, tcg;
-        uint32_t xa = c_raw + warp_excl_scan_add(a, &ta);
-        uint32_t xd = c_del + warp_excl_scan_add(d, &td);
-        const uint32_t ecg = warp_excl_scan_add(cg, &tcg);
-        uint32_t xc = c_com + (ecg & 0xffffu), xg = c_ind + (ecg >> 16);
-        // pass B: the same walk, now writing the per-event scratch
-        if (first_op) {
-            num = 0;
-            bool first = true;
-#pragma unroll
-            for (int i = 0; i < 16; i++) {
-                const uint32_t pos = off + i;
-                if (pos < head || pos >= span) continue;
-                const uint32_t ch = x.byte(i);
-                if (ss_is_digit(ch)) num = num * 10 + (ch - '0');
-                else if (ss_is_op(ch)) {
-                    const uint32_t v = first ? first_num : num;
-                    first = false;
-                    if (ch == ',') {
-                        const uint64_t ik = (uint64_t)xc + xd;
-                        const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
-                        uint32_t code = 0xFF;
-                        if (si >= 0 && si < (int64_t)rd.seq_len) code = pgm_base_code(__ldg(seq + si), o.fourth, rna);
-                        sc_start[xc] = xa; sc_end[xc] = xa + v; sc_code[xc] = (uint8_t)code;
-                        xa += v; xc++;
-                    } else if (ch == 'I') { sc_indel[xg] = (int32_t)xc; xa += v; xg++; }
-                    else { sc_indel[xg] = (int32_t)xc; xd += v; xg++; }
-                    num = 0;
-                }
-            }
-        }
-        c_raw += ta; c_del += td; c_com += tcg & 0xffffu; c_ind += tcg >> 16;
+        __syncwarp();
+        if (lane == 31) *reinterpret_cast<uint4 *>(wbuf) = make_uint4(x.w[0], x.w[1], x.w[2], x.w[3]);   // halo of the next step
     }
     if (__any_sync(0xffffffffu, bad)) { *bad_out = true; return 0; }   // U7
     __syncwarp();   // scratch writes of this warp are visible to it from here on
@@ -389,7 +359,9 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, DecodeIO io) {
-    const uint32_t lane = threadIdx.x & 31;
+    __shared__ __align__(16) uint8_t sm_buf[DEC_WARPS][16 + 512];
+    __shared__ uint16_t sm_pos[DEC_WARPS][512];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t exam = 0;
     for (;;) {
         uint32_t r = 0;
@@ -400,7 +372,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, Dec
         bool bad = false;
         if (io.rflags[r] == 0) {
             const pgm_read rd = b.reads[r];
-            if (b.mode == PGM_MODE_SS) n_pass = decode_ss_record(o, b, io, rd, &exam, &bad);
+            if (b.mode == PGM_MODE_SS) n_pass = decode_ss_record(o, b, io, rd, sm_buf[wid], sm_pos[wid], &exam, &bad);
             else n_pass = decode_moves_record(o, b, io, rd, &exam, &bad);
             if (bad) {
                 n_pass = 0;
