@@ -18,6 +18,7 @@
 #include "pgm_sort.cuh"
 
 #define DEC_WARPS PGM_WARPS
+#define DEC_WSM 2368   // bytes of shared staging per warp
 
 struct DecodeIO {
     // quota state
@@ -236,7 +237,7 @@ __device__ __forceinline__ bool ss_pick(const int32_t *pos, uint32_t n, int last
 }
 
 __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd,
-                                                     uint8_t *wbuf, uint16_t *wpos, uint32_t *exam, bool *bad_out) {
+                                                     uint8_t *wsm, uint32_t *exam, bool *bad_out) {
     const uint32_t lane = threadIdx.x & 31;
     const uint8_t *ss = b.align + rd.align_off;
     const uint8_t *seq = b.bases + rd.seq_off;
@@ -252,13 +253,20 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 
     // ---- 1. tokenise: 512 bytes per step are staged in the warp's shared buffer (with the previous 16
     // bytes as a halo); operator positions come from byte-parallel word tricks, then ONE LANE PER TOKEN
-    // parses its run length backwards and three warp scans place the token.
+    // parses its run length backwards and three warp scans place the token. The next step's bytes are
+    // requested before this step is parsed, and the base look-ups of up to 8 token rounds are in flight
+    // together.
+    uint8_t *wbuf = wsm;                                            // [16 + 512]
+    uint16_t *wpos = reinterpret_cast<uint16_t *>(wsm + 528);       // [512]
     uint32_t c_raw = rd.query_start, c_com = 0, c_del = 0, c_ind = 0;   // carries
     bool bad = false;
+    __syncwarp();   // the previous record's tiles are done with the staging area
     if (lane < 4) reinterpret_cast<uint32_t *>(wbuf)[lane] = 0;
+    Lane16 xn = load_lane16(abase, 16 * lane, span);
     for (uint32_t cb = 0; cb < span; cb += 512) {
         const uint32_t off = cb + 16 * lane;
-        const Lane16 x = load_lane16(abase, off, span);
+        const Lane16 x = xn;
+        xn = load_lane16(abase, off + 512, span);
         // bytes of the lane that belong to the string: bit i <=> head <= off + i < span
         const uint32_t lo = (off < head) ? min(16u, head - off) : 0u;
         const uint32_t hi = (off >= span) ? 0u : min(16u, span - off);
@@ -281,76 +289,108 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
         for (uint32_t m = opm; m; m &= m - 1) wpos[tb++] = (uint16_t)(16 * lane + __ffs(m) - 1);
         __syncwarp();
         const int sb = (cb == 0) ? (int)head : -16;                          // first byte a run length may use (chunk coordinates)
-        for (uint32_t t0 = 0; t0 < ntok; t0 += 32) {
-            const uint32_t t = t0 + lane;
-            uint32_t ch = 0, num = 0, a = 0, d = 0, cg = 0;
-            if (t < ntok) {
-                const int pos = wpos[t];
-                ch = wbuf[16 + pos];
-                uint32_t nd = 0, mult = 1;
-                for (int q = pos - 1; q >= sb && nd < 10; q--) {
-                    const uint32_t dgt = (uint32_t)wbuf[16 + q] - '0';
-                    if (dgt > 9) break;
-                    if (nd < 9) num += dgt * mult;
-                    mult *= 10;
-                    nd++;
+        for (uint32_t g0 = 0; g0 < ntok; g0 += 256) {
+            uint32_t base_ch[8], ev_idx[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const uint32_t t0 = g0 + 32 * u;
+                ev_idx[u] = PGM_INVALID;
+                base_ch[u] = 0;
+                if (t0 >= ntok) continue;
+                const uint32_t t = t0 + lane;
+                uint32_t ch = 0, num = 0, a = 0, d = 0, cg = 0;
+                if (t < ntok) {
+                    const int pos = wpos[t];
+                    ch = wbuf[16 + pos];
+                    uint32_t nd = 0, mult = 1;
+                    for (int q = pos - 1; q >= sb && nd < 10; q--) {
+                        const uint32_t dgt = (uint32_t)wbuf[16 + q] - '0';
+                        if (dgt > 9) break;
+                        if (nd < 9) num += dgt * mult;
+                        mult *= 10;
+                        nd++;
+                    }
+                    if (nd == 0 || nd > 9) bad = true;                       // gmove.cpp:834, U7
+                    if (ch == ',') { a = num; cg = 1; }
+                    else if (ch == 'I') { a = num; cg = 0x10000u; }
+                    else { d = num; cg = 0x10000u; }
                 }
-                if (nd == 0 || nd > 9) bad = true;                           // gmove.cpp:834, U7
-                if (ch == ',') { a = num; cg = 1; }
-                else if (ch == 'I') { a = num; cg = 0x10000u; }
-                else { d = num; cg = 0x10000u; }
+                uint32_t ta, td, tcg;
+                const uint32_t xa = c_raw + warp_excl_scan_add(a, &ta);
+                const uint32_t xd = c_del + warp_excl_scan_add(d, &td);
+                const uint32_t ecg = warp_excl_scan_add(cg, &tcg);
+                const uint32_t xc = c_com + (ecg & 0xffffu), xg = c_ind + (ecg >> 16);
+                if (ch == ',') {
+                    const uint64_t ik = (uint64_t)xc + xd;
+                    const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
+                    ev_idx[u] = xc;
+                    if (si >= 0 && si < (int64_t)rd.seq_len) base_ch[u] = __ldg(seq + si);   // consumed after the 8 rounds
+                    sc_start[xc] = xa; sc_end[xc] = xa + num;
+                } else if (ch) sc_indel[xg] = (int32_t)xc;
+                c_raw += ta; c_del += td; c_com += tcg & 0xffffu; c_ind += tcg >> 16;
             }
-            uint32_t ta, td, tcg;
-            const uint32_t xa = c_raw + warp_excl_scan_add(a, &ta);
-            const uint32_t xd = c_del + warp_excl_scan_add(d, &td);
-            const uint32_t ecg = warp_excl_scan_add(cg, &tcg);
-            const uint32_t xc = c_com + (ecg & 0xffffu), xg = c_ind + (ecg >> 16);
-            if (ch == ',') {
-                const uint64_t ik = (uint64_t)xc + xd;
-                const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
-                uint32_t code = 0xFF;
-                if (si >= 0 && si < (int64_t)rd.seq_len) code = pgm_base_code(__ldg(seq + si), o.fourth, rna);
-                sc_start[xc] = xa; sc_end[xc] = xa + num; sc_code[xc] = (uint8_t)code;
-            } else if (ch) sc_indel[xg] = (int32_t)xc;
-            c_raw += ta; c_del += td; c_com += tcg & 0xffffu; c_ind += tcg >> 16;
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                if (ev_idx[u] != PGM_INVALID) sc_code[ev_idx[u]] = (uint8_t)pgm_base_code(base_ch[u], o.fourth, rna);
         }
         __syncwarp();
         if (lane == 31) *reinterpret_cast<uint4 *>(wbuf) = make_uint4(x.w[0], x.w[1], x.w[2], x.w[3]);   // halo of the next step
     }
     if (__any_sync(0xffffffffu, bad)) { *bad_out = true; return 0; }   // U7
     __syncwarp();   // scratch writes of this warp are visible to it from here on
-    // ---- 2. evaluate: one k-mer start per lane and round, passing events compacted in place
+    // ---- 2. evaluate: one k-mer start per lane and round, passing events compacted in place. The scratch
+    // of 256 events at a time is staged in shared memory, so a round waits on shared, not on L2.
+    uint32_t *t_st = reinterpret_cast<uint32_t *>(wsm);            // [256] start of event i + m
+    uint32_t *t_en = t_st + 256;                                    // [256] end of event i + m
+    uint8_t *t_cd = wsm + 2048;                                     // [256 + 16] base codes from event i on
     const uint32_t L = c_com, n_indel = c_ind;
     const int k = (int)o.k;
     const int last = (int)((uint32_t)rd.end_k + o.pick_margin);             // gmove.cpp:885
     const uint32_t n_i = ((int)L >= k) ? L - o.k + 1 : 0;                   // U5
     uint32_t pbase = 0, my_exam = 0;
-    for (uint32_t base = 0; base < n_i; base += 32) {
-        const uint32_t i = base + lane;
-        const uint64_t j = (uint64_t)i + o.m;
-        bool ok = false;
-        uint32_t slot = 0, s2 = 0, len = 0;
-        if (i < n_i && j < L) {                                              // gmove.cpp:892 (-1 cell), U5
-            my_exam++;
-            const int left = rna ? (int)L - (int)i - k : (int)i;            // gmove.cpp:899,906
-            if (ss_pick(sc_indel, n_indel, last, left, k, (int)o.pick_margin, (int)L, rd.st_k, rna)) {
-                uint32_t id = 0;
-                bool id_ok = true;
-                for (int t = 0; t < k; t++) {
-                    const uint32_t c = sc_code[rna ? (i + k - 1 - t) : (i + t)];
-                    id_ok &= (c != 0xFF);
-                    id = (id << 2) | (c & 3);
+    for (uint32_t tile = 0; tile < n_i; tile += 256) {
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const uint32_t q = 32 * u + lane;
+            const uint64_t e = (uint64_t)tile + q + o.m;
+            t_st[q] = (e < L) ? sc_start[e] : 0u;
+            t_en[q] = (e < L) ? sc_end[e] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 9; u++) {
+            const uint32_t q = 32 * u + lane;
+            if (q < 256 + 16) t_cd[q] = (tile + q < L) ? sc_code[tile + q] : (uint8_t)0xFF;
+        }
+        __syncwarp();
+        const uint32_t tend = min(tile + 256, n_i);
+        for (uint32_t base = tile; base < tend; base += 32) {
+            const uint32_t i = base + lane, q = i - tile;
+            const uint64_t j = (uint64_t)i + o.m;
+            bool ok = false;
+            uint32_t slot = 0, s2 = 0, len = 0;
+            if (i < n_i && j < L) {                                              // gmove.cpp:892 (-1 cell), U5
+                my_exam++;
+                const int left = rna ? (int)L - (int)i - k : (int)i;            // gmove.cpp:899,906
+                if (ss_pick(sc_indel, n_indel, last, left, k, (int)o.pick_margin, (int)L, rd.st_k, rna)) {
+                    uint32_t id = 0;
+                    bool id_ok = true;
+                    for (int t = 0; t < k; t++) {
+                        const uint32_t c = t_cd[rna ? (q + k - 1 - t) : (q + t)];
+                        id_ok &= (c != 0xFF);
+                        id = (id << 2) | (c & 3);
+                    }
+                    ok = pgm_eval_event(o, io.consumed, t_st[q], t_en[q], id, id_ok, n_sig, &slot, &s2, &len);
                 }
-                ok = pgm_eval_event(o, io.consumed, sc_start[j], sc_end[j], id, id_ok, n_sig, &slot, &s2, &len);
             }
+            const uint32_t bm = __ballot_sync(0xffffffffu, ok);
+            if (ok) {   // positions <= i: behind every event still to be staged
+                const uint32_t p = pbase + __popc(bm & ((1u << lane) - 1));
+                atomicAdd(io.counts + slot, 1u);
+                t_key[p] = slot; sc_start[p] = s2; sc_end[p] = len;
+            }
+            pbase += __popc(bm);
         }
-        const uint32_t bm = __ballot_sync(0xffffffffu, ok);   // every read of this round is done: positions <= i may be overwritten
-        if (ok) {
-            const uint32_t p = pbase + __popc(bm & ((1u << lane) - 1));
-            atomicAdd(io.counts + slot, 1u);
-            t_key[p] = slot; sc_start[p] = s2; sc_end[p] = len;
-        }
-        pbase += __popc(bm);
     }
     __syncwarp();
     *exam += my_exam;
@@ -359,8 +399,7 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, DecodeIO io) {
-    __shared__ __align__(16) uint8_t sm_buf[DEC_WARPS][16 + 512];
-    __shared__ uint16_t sm_pos[DEC_WARPS][512];
+    __shared__ __align__(16) uint8_t sm_w[DEC_WARPS][DEC_WSM];   // per-warp staging (tokeniser, then evaluation tiles)
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t exam = 0;
     for (;;) {
@@ -372,7 +411,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, Dec
         bool bad = false;
         if (io.rflags[r] == 0) {
             const pgm_read rd = b.reads[r];
-            if (b.mode == PGM_MODE_SS) n_pass = decode_ss_record(o, b, io, rd, sm_buf[wid], sm_pos[wid], &exam, &bad);
+            if (b.mode == PGM_MODE_SS) n_pass = decode_ss_record(o, b, io, rd, sm_w[wid], &exam, &bad);
             else n_pass = decode_moves_record(o, b, io, rd, &exam, &bad);
             if (bad) {
                 n_pass = 0;
