@@ -33,8 +33,9 @@ struct DBuf {
     size_t cap = 0;
 };
 
+
 typedef BatchScalars Scalars;  // device -> host summary of one batch (pgm_emit.cuh)
-#define MISC_WORDS 64   // dev_misc: word 0 = k_stats_wide queue, words 8.. = look-back scan tickets
+#define MISC_WORDS 64           // word 0 = k_stats_wide queue, word 1 = k_decode record ticket, words 8.. = look-back scan tickets
 
 enum State { ST_IDLE = 0, ST_LOADED, ST_COUNTED, ST_EMITTED };
 
@@ -53,9 +54,9 @@ struct pgm_ctx {
     uint64_t launches = 0;
 
     // per-context persistent device state
-    DBuf lut, consumed, counts, keep, totals_next, bucket_base, sel_base, scalars, dev_misc, gscratch;
-    DBuf lb_flag, lb_agg, lb_pre;   // look-back scan status (shared by the scans of one stream, told apart by generation)
-    uint32_t lb_gen = 0, lb_ticket = 0;
+    DBuf lut, consumed, counts, keep, totals_next, bucket_base, sel_base, gscratch;
+    uint32_t lb_ticket = 0;          // look-back scans launched since the last zeroing (each gets its own ticket + status words)
+    size_t lb_used = 0, lb_words = 0;   // status words handed out / available in zbatch
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
 
     // batch (device view) + owned copies
@@ -71,8 +72,8 @@ struct pgm_ctx {
     DBuf key, ev_start, ev_len, ev_read, key2, val, val2, hist, blk32, blk64;
     DBuf sc_start, sc_end, sc_key, sc_code, sc_indel;
     DBuf rec_flag, rec_agg, rec_pre;   // look-back over records (k_decode)
-    DBuf zbatch;                       // zeroed every batch: read_has_sel[R] then the tile histogram
-    size_t hist_off = 0;               // byte offset of the histogram inside zbatch
+    DBuf zbatch;                       // zeroed every batch: scalars | misc words | scan status | read_has_sel[R] | tile histogram
+    size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
     uint32_t sort_ntiles = 0;
     DBuf sel_start, sel_len, sel_read, sel_off, samples, ev_out;
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
@@ -131,10 +132,13 @@ void release(DBuf &b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
 void release_host(DBuf &b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
 
 template <typename T> T *P(DBuf &b) { return reinterpret_cast<T *>(b.p); }
-inline uint8_t *HAS_SEL(pgm_ctx *c);
-inline uint32_t *HIST(pgm_ctx *c);
 
-inline uint8_t *HAS_SEL(pgm_ctx *c) { return reinterpret_cast<uint8_t *>(c->zbatch.p); }
+
+#define ZB_MISC_OFF 64
+#define ZB_STATUS_OFF (ZB_MISC_OFF + MISC_WORDS * 4)
+inline Scalars *SCALARS(pgm_ctx *c) { return reinterpret_cast<Scalars *>(c->zbatch.p); }
+inline uint32_t *MISC(pgm_ctx *c) { return reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(c->zbatch.p) + ZB_MISC_OFF); }
+inline uint8_t *HAS_SEL(pgm_ctx *c) { return reinterpret_cast<uint8_t *>(c->zbatch.p) + c->has_sel_off; }
 inline uint32_t *HIST(pgm_ctx *c) { return reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(c->zbatch.p) + c->hist_off); }
 
 #define RET(x) do { int rc_ = (x); if (rc_ != PGM_OK) return rc_; } while (0)
@@ -198,8 +202,8 @@ void pgm_destroy(pgm_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->totals_next, &c->bucket_base, &c->sel_base, &c->scalars,
-                   &c->dev_misc, &c->gscratch, &c->lb_flag, &c->lb_agg, &c->lb_pre, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
+    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->totals_next, &c->bucket_base, &c->sel_base,
+                   &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
                    &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out};
@@ -285,7 +289,6 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep, &c->totals_next};
     for (DBuf *b : slotbufs) if ((rc = ensure(c, *b, sb)) != PGM_OK) return bail(rc);
     if ((rc = ensure(c, c->bucket_base, sb + 4)) != PGM_OK || (rc = ensure(c, c->sel_base, sb + 4)) != PGM_OK) return bail(rc);
-    if ((rc = ensure(c, c->scalars, sizeof(Scalars))) != PGM_OK || (rc = ensure(c, c->dev_misc, MISC_WORDS * 4)) != PGM_OK) return bail(rc);
     if (cudaMemset(c->consumed.p, 0, sb) != cudaSuccess) { c->err = "memset failed"; return bail(PGM_ERR_CUDA); }
     if (cudaHostAlloc((void **)&c->h_scalars, sizeof(Scalars), cudaHostAllocDefault) != cudaSuccess) { c->err = "cudaHostAlloc failed"; return bail(PGM_ERR_NOMEM); }
     *out = c;
@@ -310,6 +313,13 @@ int pgm_sync(pgm_ctx *c) {
     return PGM_OK;
 }
 
+// radix pass layout for the slot keys: `passes` passes of `per` bits
+static void sort_plan(const pgm_ctx *c, uint32_t *passes, uint32_t *per) {
+    const uint32_t bits = bit_length(c->opts.n_slots - 1);
+    *passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
+    *per = bits ? (bits + *passes - 1) / *passes : 1;
+}
+
 // ------------------------------------------------------------------------------------------------
 static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     if (b->mode > PGM_MODE_MOVES_I8) return fail(c, PGM_ERR_ARG, "unknown batch mode %u", b->mode);
@@ -321,7 +331,7 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     // needs a k-mer that starts at its own base of the record's sequence.
     uint64_t cap = (b->mode == PGM_MODE_SS) ? b->n_align / 2 + R : b->n_align;
     if (b->n_bases < cap) cap = b->n_bases;
-    if (cap >= 0xFFFFFFF0ull) return fail(c, PGM_ERR_ARG, "batch too large: split it");
+    if (cap >= 0x7FFFFFF0ull) return fail(c, PGM_ERR_ARG, "batch too large: split it");
     c->ev_cap = (uint32_t)cap;
     // every selected sample is one raw sample of one event, widened by --margin on both sides
     c->samples_cap = b->n_raw + 2ull * c->opts.signal_print_margin * cap;
@@ -336,8 +346,15 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
     c->sort_ntiles = ntiles;
-    c->hist_off = ((size_t)R + 255) & ~(size_t)255;
-    RET(ensure(c, c->zbatch, c->hist_off + (size_t)SORT_MAX_BINS * ntiles * 4));
+    {   // per-batch zero region: scalars | misc words | look-back status words | read_has_sel[R] | tile histogram
+        uint32_t passes, per;
+        sort_plan(c, &passes, &per);
+        c->lb_words = (size_t)R / LB_TILE + c->opts.n_slots / LB_TILE + (size_t)cap / LB_TILE + 8 +
+                      passes * (((size_t)ntiles << per) / LB_TILE + 2);
+        c->has_sel_off = (ZB_STATUS_OFF + c->lb_words * 8 + 255) & ~(size_t)255;
+        c->hist_off = (c->has_sel_off + (size_t)R + 255) & ~(size_t)255;
+        RET(ensure(c, c->zbatch, c->hist_off + (size_t)SORT_MAX_BINS * ntiles * 4));
+    }
     RET(ensure(c, c->samples, (size_t)c->samples_cap * 8));
     RET(ensure(c, c->sc_start, (size_t)b->n_align * 4 + 4));
     RET(ensure(c, c->sc_end, (size_t)b->n_align * 4 + 4));
@@ -349,18 +366,6 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
         RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4 + 4));
     }
     if (c->opts.scaling) RET(ensure(c, c->gscratch, (size_t)c->n_sm * 4 * 65536 * 4));
-    {
-        uint64_t m = (uint64_t)SORT_MAX_BINS * ntiles;
-        if (m < c->opts.n_slots) m = c->opts.n_slots;
-        if (m < cap + 1) m = cap + 1;
-        if (m < R) m = R;
-        const size_t tiles = (size_t)(m / LB_TILE) + 2;
-        const bool fresh = !c->lb_flag.p || c->lb_flag.cap < tiles * 4;
-        RET(ensure(c, c->lb_flag, tiles * 4));
-        RET(ensure(c, c->lb_agg, tiles * 8));
-        RET(ensure(c, c->lb_pre, tiles * 8));
-        if (fresh) CU(c, cudaMemsetAsync(c->lb_flag.p, 0, c->lb_flag.cap, c->stream));   // generation 0 = never valid
-    }
     return PGM_OK;
 }
 
@@ -405,26 +410,13 @@ int pgm_attach_device(pgm_ctx *c, const pgm_batch *b) {
     return PGM_OK;
 }
 
-extern "C++" {
-template <typename T>
-static LbBuf<T> next_lb(pgm_ctx *c) {
-    LbBuf<T> st;
-    st.flag = P<uint32_t>(c->lb_flag);
-    st.agg = P<T>(c->lb_agg);
-    st.pre = P<T>(c->lb_pre);
-    st.ticket = P<uint32_t>(c->dev_misc) + 8 + (c->lb_ticket++ % (MISC_WORDS - 8));
-    c->lb_gen = (c->lb_gen + 1) & 0x3fffffffu;
-    if (c->lb_gen == 0) c->lb_gen = 1;
-    st.gen = c->lb_gen;
+// status words + ticket of the next look-back scan of this batch (`tiles` = its grid size)
+static LbBuf next_lb(pgm_ctx *c, size_t tiles) {
+    LbBuf st;
+    st.status = reinterpret_cast<unsigned long long *>(reinterpret_cast<uint8_t *>(c->zbatch.p) + ZB_STATUS_OFF) + c->lb_used;
+    st.ticket = MISC(c) + 8 + c->lb_ticket++;
+    c->lb_used += tiles + 1;
     return st;
-}
-}  // extern "C++"
-
-// radix pass layout for the slot keys: `passes` passes of `per` bits
-static void sort_plan(const pgm_ctx *c, uint32_t *passes, uint32_t *per) {
-    const uint32_t bits = bit_length(c->opts.n_slots - 1);
-    *passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
-    *per = bits ? (bits + *passes - 1) / *passes : 1;
 }
 
 int pgm_count(pgm_ctx *c) {
@@ -438,12 +430,11 @@ int pgm_count(pgm_ctx *c) {
     {
         StageTimer t(c, PGM_STAGE_MISC);
         CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
-        CU(c, cudaMemsetAsync(c->scalars.p, 0, sizeof(Scalars), st));
-        CU(c, cudaMemsetAsync(c->dev_misc.p, 0, MISC_WORDS * 4, st));
-        c->lb_ticket = 0;
-        // read_has_sel[R] and the tiles of the first radix pass's histogram
+        // scalars, tickets, scan status, read_has_sel[R] and the tiles of the first radix pass's histogram
         CU(c, cudaMemsetAsync(c->zbatch.p, 0, c->hist_off + ((size_t)c->sort_ntiles << per) * 4, st));
-        CU(c, cudaMemsetAsync(P<uint32_t>(c->ev_base), 0, (size_t)(R + 1) * 4, st));
+        c->lb_ticket = 0;
+        c->lb_used = 0;
+        if (!R) CU(c, cudaMemsetAsync(P<uint32_t>(c->ev_base), 0, 4, st));
     }
     c->user_prior = c->user_consumed = nullptr;
     DevOpts d = c->dopts;
@@ -451,7 +442,7 @@ int pgm_count(pgm_ctx *c) {
     if (R) {
         {
             StageTimer t(c, PGM_STAGE_PREP);
-            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &P<Scalars>(c->scalars)->err_flag);
+            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &SCALARS(c)->err_flag);
             c->launches++;
             if (c->db.mode == PGM_MODE_MOVES_I8) { k_oor_check<<<R, PGM_BLOCK, 0, st>>>(c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags)); c->launches++; }
         }
@@ -465,15 +456,15 @@ int pgm_count(pgm_ctx *c) {
             io.ev_cap = c->ev_cap;
             io.key = P<uint32_t>(c->key); io.ev_start = P<uint32_t>(c->ev_start); io.ev_len = P<uint32_t>(c->ev_len); io.ev_read = P<uint32_t>(c->ev_read);
             io.rflags = P<uint8_t>(c->rflags);
-            io.examined = &P<Scalars>(c->scalars)->examined;
+            io.examined = &SCALARS(c)->examined;
             io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end); io.sc_key = P<uint32_t>(c->sc_key);
             io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
             io.n_pass = P<uint32_t>(c->n_pass);
-            io.ticket = P<uint32_t>(c->dev_misc) + 1;
+            io.ticket = MISC(c) + 1;
             io.hist = HIST(c); io.ntiles_cap = c->sort_ntiles; io.hist_mask = (1u << per) - 1;
             const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
             k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
-            k_scan_records<<<cdiv(R, LB_TILE), PGM_BLOCK, 0, st>>>(io.n_pass, io.ev_base, R, next_lb<uint32_t>(c));
+            k_scan_records<<<cdiv(R, LB_TILE), PGM_BLOCK, 0, st>>>(io.n_pass, io.ev_base, R, next_lb(c, cdiv(R, LB_TILE)));
             k_place<<<cdiv(R, DEC_WARPS), PGM_BLOCK, 0, st>>>(c->db, io);
             c->launches += 3;
         }
@@ -520,7 +511,7 @@ int pgm_emit(pgm_ctx *c) {
         q.user_consumed = c->user_consumed;
         q.counts = P<uint32_t>(c->counts); q.keep = P<uint32_t>(c->keep); q.consumed = P<uint32_t>(c->consumed);
         q.bucket_base = P<uint32_t>(c->bucket_base); q.sel_base = P<uint32_t>(c->sel_base);
-        k_quota<<<cdiv(NS, LB_TILE), PGM_BLOCK, 0, st>>>(q, next_lb<unsigned long long>(c));
+        k_quota<<<cdiv(NS, LB_TILE), PGM_BLOCK, 0, st>>>(q, next_lb(c, cdiv(NS, LB_TILE)));
         c->launches++;
     }
     if (R && c->ev_cap) {
@@ -536,7 +527,7 @@ int pgm_emit(pgm_ctx *c) {
             const uint32_t shift = p * per;
             if (p) { k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, HIST(c), ntiles); c->launches++; }   // pass 0: counted by k_decode
             k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(HIST(c), n_ev, 1u << per, ntiles,
-                                                                                           next_lb<uint32_t>(c));
+                                                                                           next_lb(c, cdiv((uint64_t)(1u << per) * ntiles, LB_TILE)));
             c->launches++;
             if (p + 1 < passes) {
                 k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, HIST(c), ntiles);
@@ -561,14 +552,14 @@ int pgm_emit(pgm_ctx *c) {
     {
         StageTimer t(c, PGM_STAGE_SCAN);
         k_scan_sel<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_len), P<unsigned long long>(c->sel_off),
-                                                                               P<uint32_t>(c->sel_base) + NS, n_ev, P<Scalars>(c->scalars),
-                                                                               next_lb<unsigned long long>(c));
+                                                                               P<uint32_t>(c->sel_base) + NS, n_ev, SCALARS(c),
+                                                                               next_lb(c, cdiv((uint64_t)c->ev_cap + 1, LB_TILE)));
         c->launches++;
     }
     if (R && c->ev_cap) {
         if (c->opts.scaling && c->need_wide) {
             StageTimer t(c, PGM_STAGE_STATS);
-            uint32_t *queue = P<uint32_t>(c->dev_misc);
+            uint32_t *queue = MISC(c);
             k_stats_wide<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), HAS_SEL(c), P<ReadCal>(c->cal), queue,
                                                             P<uint32_t>(c->gscratch));
             c->launches++;
@@ -592,7 +583,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     CU(c, cudaSetDevice(c->device));
     cudaStream_t st = c->stream;
     const uint32_t R = c->db.n_reads, NS = c->opts.n_slots;
-    CU(c, cudaMemcpyAsync(c->h_scalars, c->scalars.p, sizeof(Scalars), cudaMemcpyDeviceToHost, st));
+    CU(c, cudaMemcpyAsync(c->h_scalars, SCALARS(c), sizeof(Scalars), cudaMemcpyDeviceToHost, st));
     RET(ensure_host(c, c->h_slot_sel, (size_t)NS * 4));
     RET(ensure_host(c, c->h_slot_total, (size_t)NS * 4));
     RET(ensure_host(c, c->h_rflags, R ? R : 1));

@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, Dec
 }
 
 // ev_base = exclusive scan of the per-record totals (one launch, look-back over tiles of 4096 records)
-__global__ void __launch_bounds__(PGM_BLOCK) k_scan_records(const uint32_t *n_pass, uint32_t *ev_base, uint32_t R, LbBuf<uint32_t> st) {
+__global__ void __launch_bounds__(PGM_BLOCK) k_scan_records(const uint32_t *n_pass, uint32_t *ev_base, uint32_t R, LbBuf st) {
     lb_scan<uint32_t>(R, st, [&](uint64_t r) { return n_pass[r]; }, [&](uint64_t r, uint32_t ex, uint32_t) { ev_base[r] = ex; },
                       [&](uint32_t tot) { ev_base[R] = tot; });
 }

@@ -106,7 +106,7 @@ struct QuotaIO {
     uint32_t *keep, *consumed, *bucket_base, *sel_base;   // consumed may alias prior
 };
 
-__global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf<unsigned long long> st) {
+__global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf st) {
     lb_scan<unsigned long long>(
         io.n_slots, st,
         [&](uint64_t s) {
@@ -115,15 +115,15 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf<unsigned 
             const uint32_t k = min(c, io.limit - p);
             io.keep[s] = k;
             io.consumed[s] = io.user_consumed ? io.user_consumed[s] : p + k;
-            return (unsigned long long)c | ((unsigned long long)k << 32);
+            return (unsigned long long)c | ((unsigned long long)k << 31);   // two 31-bit sums in one 62-bit scan value
         },
         [&](uint64_t s, unsigned long long ex, unsigned long long) {
-            io.bucket_base[s] = (uint32_t)ex;
-            io.sel_base[s] = (uint32_t)(ex >> 32);
+            io.bucket_base[s] = (uint32_t)(ex & 0x7fffffffull);
+            io.sel_base[s] = (uint32_t)(ex >> 31);
         },
         [&](unsigned long long tot) {
-            io.bucket_base[io.n_slots] = (uint32_t)tot;
-            io.sel_base[io.n_slots] = (uint32_t)(tot >> 32);
+            io.bucket_base[io.n_slots] = (uint32_t)(tot & 0x7fffffffull);
+            io.sel_base[io.n_slots] = (uint32_t)(tot >> 31);
         });
 }
 
@@ -139,7 +139,7 @@ struct BatchScalars {  // device -> host summary of one batch
 };
 
 __global__ void __launch_bounds__(PGM_BLOCK) k_scan_sel(const uint32_t *sel_len, unsigned long long *sel_off, const uint32_t *n_sel_ptr,
-                                                        const uint32_t *n_pass_ptr, BatchScalars *sc, LbBuf<unsigned long long> st) {
+                                                        const uint32_t *n_pass_ptr, BatchScalars *sc, LbBuf st) {
     const uint32_t n = *n_sel_ptr;
     lb_scan<unsigned long long>(
         n, st, [&](uint64_t i) { return (unsigned long long)sel_len[i]; },

@@ -99,22 +99,19 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_scan_down(const TIn *in, uint64_t
 // ------------------------------------------------------------------------------------------------
 // Single-pass exclusive scan with decoupled look-back (one launch instead of reduce/top/down).
 // Tiles are handed out by an atomic ticket, so a tile only ever waits on tiles that already run.
-// flag[t] = gen << 2 | state (1: tile aggregate published, 2: inclusive prefix published); a stale
-// generation reads as "nothing yet", so the status arrays never need clearing between launches.
+// One 64-bit status word per tile, value << 2 | state (1: tile aggregate, 2: inclusive prefix), read
+// and written whole, so no fence is needed between "flag" and "value". Values are limited to 62 bits.
+// The status words and the ticket are zeroed before the launch (they live in the per-batch zero region).
 #define LB_ITEMS 16
 #define LB_TILE (PGM_BLOCK * LB_ITEMS)
 
-template <typename T>
 struct LbBuf {
-    uint32_t *flag;    // [tiles]
-    T *agg, *pre;      // [tiles]
-    uint32_t *ticket;  // zeroed before the launch
-    uint32_t gen;
+    unsigned long long *status;  // [tiles]
+    uint32_t *ticket;
 };
 
-__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
-__device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *reinterpret_cast<volatile uint32_t *>(p) = v; }
-template <typename T> __device__ __forceinline__ T ld_volatile_t(const T *p) { return *reinterpret_cast<const volatile T *>(p); }
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) { return *reinterpret_cast<const volatile unsigned long long *>(p); }
+__device__ __forceinline__ void st_volatile_u64(unsigned long long *p, unsigned long long v) { *reinterpret_cast<volatile unsigned long long *>(p) = v; }
 
 template <typename T>
 __device__ __forceinline__ T warp_sum_t(T v) {
@@ -125,7 +122,7 @@ __device__ __forceinline__ T warp_sum_t(T v) {
 
 // load(idx) -> T, store(idx, exclusive_prefix, own_value), fin(total) (one thread of the last tile).
 template <typename T, typename LoadF, typename StoreF, typename FinalF>
-__device__ __forceinline__ void lb_scan(uint64_t n, LbBuf<T> st, LoadF load, StoreF store, FinalF fin) {
+__device__ __forceinline__ void lb_scan(uint64_t n, LbBuf st, LoadF load, StoreF store, FinalF fin) {
     __shared__ T sm_scan[PGM_WARPS + 1];
     __shared__ T sm_prefix;
     __shared__ uint32_t sm_tile;
@@ -150,35 +147,31 @@ __device__ __forceinline__ void lb_scan(uint64_t n, LbBuf<T> st, LoadF load, Sto
     const T ex = block_excl_scan_add_t<T>(s, sm_scan, &tot);
     if (threadIdx.x < 32) {
         const uint32_t lane = threadIdx.x;
-        const uint32_t gen = st.gen;
-        T excl = 0;
+        unsigned long long excl = 0;
         if (tile == 0) {
-            if (lane == 0) { st.pre[0] = tot; __threadfence(); st_volatile_u32(st.flag, gen << 2 | 2u); }
+            if (lane == 0) st_volatile_u64(st.status, ((unsigned long long)tot << 2) | 2ull);
         } else {
-            if (lane == 0) { st.agg[tile] = tot; __threadfence(); st_volatile_u32(st.flag + tile, gen << 2 | 1u); }
+            if (lane == 0) st_volatile_u64(st.status + tile, ((unsigned long long)tot << 2) | 1ull);
             int64_t pos = (int64_t)tile - 1;
             for (;;) {
                 const int64_t idx = pos - (int64_t)lane;
-                uint32_t f = 2;   // before tile 0: prefix 0
-                T val = 0;
+                unsigned long long w = 2ull;   // before tile 0: prefix 0
                 if (idx >= 0) {
-                    do { f = ld_volatile_u32(st.flag + idx); } while ((f >> 2) != gen || (f & 3u) == 0);
-                    f &= 3u;
-                    __threadfence();
-                    val = (f == 2) ? ld_volatile_t<T>(st.pre + idx) : ld_volatile_t<T>(st.agg + idx);
+                    do { w = ld_volatile_u64(st.status + idx); } while ((w & 3ull) == 0);
                 }
-                const uint32_t m2 = __ballot_sync(0xffffffffu, f == 2);
+                const uint32_t m2 = __ballot_sync(0xffffffffu, (w & 3ull) == 2ull);
+                const unsigned long long val = w >> 2;
                 if (m2) {
                     const uint32_t L = __ffs(m2) - 1;
-                    excl += warp_sum_t<T>(lane <= L ? val : (T)0);
+                    excl += warp_sum_t<unsigned long long>(lane <= L ? val : 0ull);
                     break;
                 }
-                excl += warp_sum_t<T>(val);
+                excl += warp_sum_t<unsigned long long>(val);
                 pos -= 32;
             }
-            if (lane == 0) { st.pre[tile] = excl + tot; __threadfence(); st_volatile_u32(st.flag + tile, gen << 2 | 2u); }
+            if (lane == 0) st_volatile_u64(st.status + tile, ((excl + (unsigned long long)tot) << 2) | 2ull);
         }
-        if (lane == 0) sm_prefix = excl;
+        if (lane == 0) sm_prefix = (T)excl;
     }
     __syncthreads();
     T run = sm_prefix + ex;

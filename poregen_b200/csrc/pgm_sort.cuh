@@ -12,7 +12,7 @@
 #include "pgm_device.cuh"
 #include "pgm_scan.cuh"
 
-#define SORT_ITEMS 8
+#define SORT_ITEMS 16
 #define SORT_TILE (PGM_BLOCK * SORT_ITEMS)
 #define SORT_MAX_BITS 10
 #define SORT_MAX_BINS (1 << SORT_MAX_BITS)
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_sort_scatter(const uint32_t *keys
 // One-launch scan of the digit-major tile histogram hist[bin * ntiles_cap + tile] over the tiles in
 // use (n_events known on the device only), in place.
 __global__ void __launch_bounds__(PGM_BLOCK) k_scan_hist(uint32_t *hist, const uint32_t *n_ptr, uint32_t bins, uint32_t ntiles_cap,
-                                                         LbBuf<uint32_t> st) {
+                                                         LbBuf st) {
     const uint32_t n_ev = *n_ptr;
     const uint32_t ntu = (n_ev + SORT_TILE - 1) / SORT_TILE;
     const uint64_t n = (uint64_t)bins * ntu;
