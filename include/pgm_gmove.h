@@ -60,7 +60,8 @@ extern "C" {
 
 /* ---- output kinds (pgm_opts.output) ---- */
 #define PGM_OUT_F64 0  /* selected samples as IEEE doubles (bit-exact with the reference vector) */
-#define PGM_OUT_TEXT 1 /* additionally the exact "%.8f," / "%.8f;" text of gmove.cpp:674-678     */
+#define PGM_OUT_TEXT 1 /* the exact "%.8f," / "%.8f;" text of gmove.cpp:674-678, formatted on the
+                          device, INSTEAD of the doubles (pgm_result.samples is NULL)             */
 
 /* Mirrors the fields of the reference's opt_t that the gmove path reads
  * (src/poregen.h:48-79, defaults src/poregen.cpp:209-237) after gmove()'s own option handling
@@ -199,11 +200,17 @@ uint64_t pgm_launch_count(const pgm_ctx *ctx);
 #define PGM_STAGE_SELECT 5       /* k_select_prep, k_select                                        */
 #define PGM_STAGE_STATS 6        /* k_stats_wide (Med-MAD of records with a wide in-range code span) */
 #define PGM_STAGE_GATHER 7       /* k_signal: per-record Med-MAD + gather of the selected samples  */
-#define PGM_STAGE_MISC 8         /* memsets, totals update, k_collect                              */
-#define PGM_N_STAGES 9
+#define PGM_STAGE_MISC 8         /* memsets                                                        */
+#define PGM_STAGE_TEXT 9         /* PGM_OUT_TEXT: k_text_len, k_scan_text (k_text_write runs in pgm_download) */
+#define PGM_N_STAGES 10
 int pgm_profile_enable(pgm_ctx *ctx, int on);
 int pgm_profile_read(pgm_ctx *ctx, float *ms, uint32_t *launches);
 const char *pgm_stage_name(int stage);
+
+/* Test hook for the device formatter: the text of ONE event made of the n host doubles vals[]
+ * ("%.8f," ... "%.8f;", gmove.cpp:674-678) into text_out[cap]; *len_out = its length (also when it
+ * does not fit, in which case nothing is written). */
+int pgm_debug_format(pgm_ctx *ctx, const double *vals, uint32_t n, char *text_out, uint64_t cap, uint64_t *len_out);
 
 #ifdef __cplusplus
 }

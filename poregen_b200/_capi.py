@@ -111,9 +111,9 @@ SYMBOLS = [
     "pgm_create", "pgm_destroy", "pgm_last_error", "pgm_abi_version", "pgm_process", "pgm_upload",
     "pgm_attach_device", "pgm_count", "pgm_emit", "pgm_download", "pgm_sync", "pgm_counts_device",
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
-    "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name",
+    "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
 ]
-PGM_N_STAGES = 9
+PGM_N_STAGES = 10
 
 _lib = None
 
@@ -164,5 +164,7 @@ def load() -> C.CDLL:
     lib.pgm_profile_read.restype = C.c_int
     lib.pgm_stage_name.argtypes = [C.c_int]
     lib.pgm_stage_name.restype = C.c_char_p
+    lib.pgm_debug_format.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, P(C.c_uint64)]
+    lib.pgm_debug_format.restype = C.c_int
     _lib = lib
     return lib

@@ -23,6 +23,7 @@
 #include "pgm_emit.cuh"
 #include "pgm_signal.cuh"
 #include "pgm_sort.cuh"
+#include "pgm_text.cuh"
 
 namespace {
 
@@ -76,11 +77,12 @@ struct pgm_ctx {
     size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
     uint32_t sort_ntiles = 0;
     DBuf sel_start, sel_len, sel_read, sel_off, samples, ev_out;
+    DBuf ev_tlen, ev_toff, text, slot_toff;   // PGM_OUT_TEXT
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
 
     // pinned host results
     Scalars *h_scalars = nullptr;
-    DBuf h_slot_sel, h_slot_total, h_ev_len, h_ev_read, h_ev_start, h_samples, h_rflags;
+    DBuf h_slot_sel, h_slot_total, h_ev_len, h_ev_read, h_ev_start, h_samples, h_rflags, h_text, h_slot_toff;
     // pinned staging for pageable inputs is left to the caller (pass pinned buffers for speed)
 
     // optional per-stage event timing
@@ -206,9 +208,9 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out};
+                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff};
     for (DBuf *b : dev) release(*b);
-    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags};
+    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff};
     for (DBuf *b : host) release_host(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     for (auto &sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -223,7 +225,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     if (opts->kmer_size < 1 || opts->kmer_size > 15) return fail(nullptr, PGM_ERR_ARG, "kmer_size %u outside 1..15", opts->kmer_size);
     if (opts->n_slots < 1) return fail(nullptr, PGM_ERR_ARG, "n_slots must be >= 1");
     if (opts->scaling > 1) return fail(nullptr, PGM_ERR_ARG, "scaling must be 0 or 1");
-    if (opts->output != PGM_OUT_F64) return fail(nullptr, PGM_ERR_ARG, "output kind %u not supported in this build", opts->output);
+    if (opts->output > PGM_OUT_TEXT) return fail(nullptr, PGM_ERR_ARG, "unknown output kind %u", opts->output);
     const uint64_t n_ids = 1ull << (2 * opts->kmer_size);
     if (!opts->kmer_list && (uint64_t)opts->index_lo + opts->n_slots > n_ids)
         return fail(nullptr, PGM_ERR_ARG, "k-mer window [%u,+%u) exceeds 4^k", opts->index_lo, opts->n_slots);
@@ -349,13 +351,18 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     {   // per-batch zero region: scalars | misc words | look-back status words | read_has_sel[R] | tile histogram
         uint32_t passes, per;
         sort_plan(c, &passes, &per);
-        c->lb_words = (size_t)R / LB_TILE + c->opts.n_slots / LB_TILE + (size_t)cap / LB_TILE + 8 +
+        c->lb_words = (size_t)R / LB_TILE + c->opts.n_slots / LB_TILE + 2 * ((size_t)cap / LB_TILE) + 12 +
                       passes * (((size_t)ntiles << per) / LB_TILE + 2);
         c->has_sel_off = (ZB_STATUS_OFF + c->lb_words * 8 + 255) & ~(size_t)255;
         c->hist_off = (c->has_sel_off + (size_t)R + 255) & ~(size_t)255;
         RET(ensure(c, c->zbatch, c->hist_off + (size_t)SORT_MAX_BINS * ntiles * 4));
     }
     RET(ensure(c, c->samples, (size_t)c->samples_cap * 8));
+    if (c->opts.output == PGM_OUT_TEXT) {
+        RET(ensure(c, c->ev_tlen, e4 + 4));
+        RET(ensure(c, c->ev_toff, (size_t)(cap + 1) * 8));
+        RET(ensure(c, c->slot_toff, (size_t)(c->opts.n_slots + 1) * 8));
+    }
     RET(ensure(c, c->sc_start, (size_t)b->n_align * 4 + 4));
     RET(ensure(c, c->sc_end, (size_t)b->n_align * 4 + 4));
     RET(ensure(c, c->sc_key, (size_t)b->n_align * 4 + 4));
@@ -492,6 +499,15 @@ int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consume
 }
 
 
+static TextIO make_text_io(pgm_ctx *c) {
+    TextIO t;
+    t.samples = P<double>(c->samples); t.sel_len = P<uint32_t>(c->sel_len); t.sel_off = P<unsigned long long>(c->sel_off);
+    t.n_sel = P<uint32_t>(c->sel_base) + c->opts.n_slots;
+    t.ev_tlen = P<uint32_t>(c->ev_tlen); t.ev_toff = P<unsigned long long>(c->ev_toff);
+    t.text = P<char>(c->text); t.text_cap = c->text.cap;
+    return t;
+}
+
 int pgm_emit(pgm_ctx *c) {
     if (!c) return PGM_ERR_ARG;
     if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_emit needs pgm_count first");
@@ -572,6 +588,14 @@ int pgm_emit(pgm_ctx *c) {
         k_signal<<<R, SIG_THREADS, 0, st>>>(d, c->db, g);
         c->launches++;
     }
+    if (c->opts.output == PGM_OUT_TEXT) {
+        StageTimer t(c, PGM_STAGE_TEXT);
+        TextIO tio = make_text_io(c);
+        k_text_len<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio);
+        k_scan_text<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, st>>>(tio.ev_tlen, tio.ev_toff, tio.n_sel, &SCALARS(c)->n_text,
+                                                                                next_lb(c, cdiv((uint64_t)c->ev_cap + 1, LB_TILE)));
+        c->launches += 2;
+    }
     CU(c, cudaGetLastError());
     c->state = ST_EMITTED;
     return PGM_OK;
@@ -600,13 +624,27 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     RET(ensure_host(c, c->h_ev_len, ne * 4 + 4));
     RET(ensure_host(c, c->h_ev_read, ne * 4 + 4));
     RET(ensure_host(c, c->h_ev_start, ne * 4 + 4));
-    RET(ensure_host(c, c->h_samples, nsamp * 8 + 8));
+    const bool as_text = c->opts.output == PGM_OUT_TEXT;
+    if (!as_text) RET(ensure_host(c, c->h_samples, nsamp * 8 + 8));
     if (ne) {
         CU(c, cudaMemcpyAsync(c->h_ev_len.p, c->sel_len.p, ne * 4, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_read.p, c->sel_read.p, ne * 4, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_start.p, c->sel_start.p, ne * 4, cudaMemcpyDeviceToHost, st));
     }
-    if (nsamp) CU(c, cudaMemcpyAsync(c->h_samples.p, c->samples.p, nsamp * 8, cudaMemcpyDeviceToHost, st));
+    if (nsamp && !as_text) CU(c, cudaMemcpyAsync(c->h_samples.p, c->samples.p, nsamp * 8, cudaMemcpyDeviceToHost, st));
+    if (as_text) {   // the length is known now: format into an exactly sized buffer, then bring it over
+        const size_t nt = (size_t)s.n_text;
+        RET(ensure(c, c->text, nt + 16));
+        RET(ensure_host(c, c->h_text, nt + 16));
+        RET(ensure_host(c, c->h_slot_toff, (size_t)(NS + 1) * 8));
+        TextIO tio = make_text_io(c);
+        if (ne) { k_text_write<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio); c->launches++; }
+        k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), tio.ev_toff, NS, P<unsigned long long>(c->slot_toff));
+        c->launches++;
+        CU(c, cudaGetLastError());
+        if (nt) CU(c, cudaMemcpyAsync(c->h_text.p, c->text.p, nt, cudaMemcpyDeviceToHost, st));
+        CU(c, cudaMemcpyAsync(c->h_slot_toff.p, c->slot_toff.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
+    }
     CU(c, cudaStreamSynchronize(st));
     memset(out, 0, sizeof *out);
     out->n_slots = NS; out->n_reads = R;
@@ -614,13 +652,13 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     out->n_sel_events = ne; out->n_sel_samples = nsamp;
     out->slot_sel = P<uint32_t>(c->h_slot_sel); out->slot_total = P<uint32_t>(c->h_slot_total);
     out->ev_len = P<uint32_t>(c->h_ev_len); out->ev_read = P<uint32_t>(c->h_ev_read); out->ev_start = P<uint32_t>(c->h_ev_start);
-    out->samples = P<double>(c->h_samples); out->read_flags = P<uint8_t>(c->h_rflags);
-    out->text = nullptr; out->slot_text_off = nullptr;
+    out->samples = as_text ? nullptr : P<double>(c->h_samples); out->read_flags = P<uint8_t>(c->h_rflags);
+    out->text = as_text ? P<char>(c->h_text) : nullptr; out->slot_text_off = as_text ? P<uint64_t>(c->h_slot_toff) : nullptr;
     c->state = ST_IDLE;
     return PGM_OK;
 }
 
-static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats_wide", "signal", "misc"};
+static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats_wide", "signal", "misc", "text"};
 
 const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }
 
@@ -642,6 +680,29 @@ int pgm_profile_read(pgm_ctx *c, float *ms, uint32_t *launches) {
         c->ev_pool.push_back(sp.b);
     }
     c->spans.clear();
+    return PGM_OK;
+}
+
+int pgm_debug_format(pgm_ctx *c, const double *vals, uint32_t n, char *text_out, uint64_t cap, uint64_t *len_out) {
+    if (!c || !len_out || (n && !vals)) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    double *dx = nullptr; char *dt = nullptr; unsigned long long *dl = nullptr;
+    CU(c, cudaMalloc(&dx, (size_t)n * 8 + 8));
+    CU(c, cudaMalloc(&dl, 8));
+    CU(c, cudaMemcpyAsync(dx, vals, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+    k_text_debug<<<1, 32, 0, c->stream>>>(dx, n, nullptr, dl);
+    unsigned long long len = 0;
+    CU(c, cudaMemcpyAsync(&len, dl, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    *len_out = len;
+    if (text_out && len <= cap && len) {
+        CU(c, cudaMalloc(&dt, (size_t)len + 8));
+        k_text_debug<<<1, 32, 0, c->stream>>>(dx, n, dt, dl);
+        CU(c, cudaMemcpyAsync(text_out, dt, (size_t)len, cudaMemcpyDeviceToHost, c->stream));
+        CU(c, cudaStreamSynchronize(c->stream));
+        cudaFree(dt);
+    }
+    cudaFree(dx); cudaFree(dl);
     return PGM_OK;
 }
 

@@ -136,6 +136,7 @@ struct BatchScalars {  // device -> host summary of one batch
     uint32_t n_sel;
     uint32_t err_flag;
     uint32_t pad;
+    unsigned long long n_text;   // PGM_OUT_TEXT: characters of the dump text
 };
 
 __global__ void __launch_bounds__(PGM_BLOCK) k_scan_sel(const uint32_t *sel_len, unsigned long long *sel_off, const uint32_t *n_sel_ptr,

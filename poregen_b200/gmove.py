@@ -61,7 +61,16 @@ class GmoveEngine:
         cb = batch.to_c()
         r = capi.PgmResult()
         self._chk(self.lib.pgm_process(self._ctx, C.byref(cb), C.byref(r)))
-        return GmoveResult.from_c(r, want_text=False)
+        return GmoveResult.from_c(r, want_text=self.opts.output == capi.PGM_OUT_TEXT)
+
+    def format_doubles(self, vals) -> bytes:
+        """Device formatter test hook: the dump text of one event made of `vals`."""
+        v = np.ascontiguousarray(vals, dtype=np.float64)
+        n = C.c_uint64(0)
+        self._chk(self.lib.pgm_debug_format(self._ctx, v.ctypes.data, v.size, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(int(n.value) + 1)
+        self._chk(self.lib.pgm_debug_format(self._ctx, v.ctypes.data, v.size, buf, n.value, C.byref(n)))
+        return buf.raw[:int(n.value)]
 
     # -- split-phase form -----------------------------------------------------------------------
     def upload(self, batch: ReadBatch):
@@ -82,7 +91,7 @@ class GmoveEngine:
     def download(self) -> GmoveResult:
         r = capi.PgmResult()
         self._chk(self.lib.pgm_download(self._ctx, C.byref(r)))
-        return GmoveResult.from_c(r, want_text=False)
+        return GmoveResult.from_c(r, want_text=self.opts.output == capi.PGM_OUT_TEXT)
 
     def sync(self):
         self._chk(self.lib.pgm_sync(self._ctx))
