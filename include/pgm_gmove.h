@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define PGM_ABI_VERSION 1
+#define PGM_ABI_VERSION 2
 
 /* ---- status codes ---- */
 #define PGM_OK 0
@@ -142,6 +142,8 @@ typedef struct pgm_result {
     const uint8_t *read_flags;  /* [n_reads] PGM_RF_*                                             */
     const char *text;           /* PGM_OUT_TEXT: concatenated dump text, grouped by slot          */
     const uint64_t *slot_text_off; /* [n_slots+1] byte range of slot s in text                    */
+    const uint64_t *ev_text_off;   /* PGM_OUT_TEXT: [n_sel_events+1] byte offset of every event's
+                                      text (the writer of `-d` delimiters needs it, gmove.cpp:692-694) */
 } pgm_result;
 
 typedef struct pgm_ctx pgm_ctx;
@@ -179,6 +181,18 @@ int pgm_sync(pgm_ctx *ctx);
 int pgm_counts_device(pgm_ctx *ctx, uint32_t **counts_dev);
 int pgm_totals_device(pgm_ctx *ctx, uint32_t **consumed_dev);
 int pgm_set_prior(pgm_ctx *ctx, const uint32_t *prior_dev, const uint32_t *consumed_dev);
+
+/* Host-side form of the same exchange for callers that do not link the CUDA runtime (the C++ CLI):
+ * pgm_counts_host copies counts[n_slots] out after pgm_count (synchronises the stream);
+ * pgm_set_prior_host uploads prior[] / consumed[] into buffers owned by the context. */
+int pgm_counts_host(pgm_ctx *ctx, uint32_t *counts_out);
+int pgm_totals_host(pgm_ctx *ctx, uint32_t *consumed_out);
+int pgm_set_prior_host(pgm_ctx *ctx, const uint32_t *prior, const uint32_t *consumed);
+
+/* Pinned host memory for batch arrays (uploads from pageable memory are staged by the driver and slow). */
+void *pgm_alloc_pinned(size_t bytes);
+void pgm_free_pinned(void *p);
+int pgm_device_count(void);
 
 /* Forget all per-k-mer totals (start a new run with the same options). */
 int pgm_reset(pgm_ctx *ctx);

@@ -17,7 +17,7 @@ PGM_MODE_MOVES_CHAR, PGM_MODE_SS, PGM_MODE_MOVES_I8 = 0, 1, 2
 PGM_READ_RNA, PGM_READ_SKIP = 1, 2
 PGM_RF_SKIPPED, PGM_RF_BAD_ALIGN, PGM_RF_BAD_CALIB = 1, 2, 4
 PGM_OUT_F64, PGM_OUT_TEXT = 0, 1
-PGM_ABI_VERSION = 1
+PGM_ABI_VERSION = 2
 
 
 class PgmOpts(C.Structure):
@@ -94,6 +94,7 @@ class PgmResult(C.Structure):
         ("read_flags", C.c_void_p),
         ("text", C.c_void_p),
         ("slot_text_off", C.c_void_p),
+        ("ev_text_off", C.c_void_p),
     ]
 
 
@@ -112,6 +113,7 @@ SYMBOLS = [
     "pgm_attach_device", "pgm_count", "pgm_emit", "pgm_download", "pgm_sync", "pgm_counts_device",
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
+    "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
 ]
 PGM_N_STAGES = 10
 

@@ -78,11 +78,12 @@ struct pgm_ctx {
     uint32_t sort_ntiles = 0;
     DBuf sel_start, sel_len, sel_read, sel_off, samples, ev_out;
     DBuf ev_tlen, ev_toff, text, slot_toff;   // PGM_OUT_TEXT
+    DBuf hp_prior, hp_consumed;               // pgm_set_prior_host
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
 
     // pinned host results
     Scalars *h_scalars = nullptr;
-    DBuf h_slot_sel, h_slot_total, h_ev_len, h_ev_read, h_ev_start, h_samples, h_rflags, h_text, h_slot_toff;
+    DBuf h_slot_sel, h_slot_total, h_ev_len, h_ev_read, h_ev_start, h_samples, h_rflags, h_text, h_slot_toff, h_ev_toff;
     // pinned staging for pageable inputs is left to the caller (pass pinned buffers for speed)
 
     // optional per-stage event timing
@@ -208,9 +209,9 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff};
+                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
     for (DBuf *b : dev) release(*b);
-    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff};
+    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff};
     for (DBuf *b : host) release_host(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     for (auto &sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -491,6 +492,45 @@ int pgm_totals_device(pgm_ctx *c, uint32_t **consumed_dev) {
     *consumed_dev = P<uint32_t>(c->consumed);
     return PGM_OK;
 }
+int pgm_counts_host(pgm_ctx *c, uint32_t *out) {
+    if (!c || !out) return PGM_ERR_ARG;
+    if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_counts_host needs pgm_count first");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemcpyAsync(out, c->counts.p, (size_t)c->opts.n_slots * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return PGM_OK;
+}
+int pgm_totals_host(pgm_ctx *c, uint32_t *out) {
+    if (!c || !out) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemcpyAsync(out, c->consumed.p, (size_t)c->opts.n_slots * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return PGM_OK;
+}
+int pgm_set_prior_host(pgm_ctx *c, const uint32_t *prior, const uint32_t *consumed) {
+    if (!c || !prior || !consumed) return PGM_ERR_ARG;
+    if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_set_prior_host belongs between pgm_count and pgm_emit");
+    CU(c, cudaSetDevice(c->device));
+    const size_t sb = (size_t)c->opts.n_slots * 4;
+    RET(ensure(c, c->hp_prior, sb));
+    RET(ensure(c, c->hp_consumed, sb));
+    CU(c, cudaMemcpyAsync(c->hp_prior.p, prior, sb, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemcpyAsync(c->hp_consumed.p, consumed, sb, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));   // the host arrays may go away
+    c->user_prior = P<uint32_t>(c->hp_prior); c->user_consumed = P<uint32_t>(c->hp_consumed);
+    return PGM_OK;
+}
+void *pgm_alloc_pinned(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    return p;
+}
+void pgm_free_pinned(void *p) { if (p) cudaFreeHost(p); }
+int pgm_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
 int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consumed_dev) {
     if (!c || !prior_dev || !consumed_dev) return PGM_ERR_ARG;
     if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_set_prior belongs between pgm_count and pgm_emit");
@@ -637,6 +677,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
         RET(ensure(c, c->text, nt + 16));
         RET(ensure_host(c, c->h_text, nt + 16));
         RET(ensure_host(c, c->h_slot_toff, (size_t)(NS + 1) * 8));
+        RET(ensure_host(c, c->h_ev_toff, (ne + 1) * 8));
         TextIO tio = make_text_io(c);
         if (ne) { k_text_write<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio); c->launches++; }
         k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), tio.ev_toff, NS, P<unsigned long long>(c->slot_toff));
@@ -644,6 +685,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
         CU(c, cudaGetLastError());
         if (nt) CU(c, cudaMemcpyAsync(c->h_text.p, c->text.p, nt, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_slot_toff.p, c->slot_toff.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
+        CU(c, cudaMemcpyAsync(c->h_ev_toff.p, c->ev_toff.p, (ne + 1) * 8, cudaMemcpyDeviceToHost, st));
     }
     CU(c, cudaStreamSynchronize(st));
     memset(out, 0, sizeof *out);
@@ -654,6 +696,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     out->ev_len = P<uint32_t>(c->h_ev_len); out->ev_read = P<uint32_t>(c->h_ev_read); out->ev_start = P<uint32_t>(c->h_ev_start);
     out->samples = as_text ? nullptr : P<double>(c->h_samples); out->read_flags = P<uint8_t>(c->h_rflags);
     out->text = as_text ? P<char>(c->h_text) : nullptr; out->slot_text_off = as_text ? P<uint64_t>(c->h_slot_toff) : nullptr;
+    out->ev_text_off = as_text ? P<uint64_t>(c->h_ev_toff) : nullptr;
     c->state = ST_IDLE;
     return PGM_OK;
 }
