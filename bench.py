@@ -181,8 +181,9 @@ def cpu_baseline_leg(n_reads):
             synth.write_blow5(batch, os.path.join(d, "reads.blow5"))
             fl = synth.write_alignment(batch, d)
             t0 = time.perf_counter()
-            ol.run_reference(opts, os.path.join(d, "reads.blow5"), fl["align"], os.path.join(d, "out"), fastq=fl["fastq"])
+            ref_files = ol.run_reference(opts, os.path.join(d, "reads.blow5"), fl["align"], os.path.join(d, "out"), fastq=fl["fastq"])
             dt = time.perf_counter() - t0
+            cli = _cli_leg(opts, d, fl, ref_files, n_samples)
         finally:
             shutil.rmtree(d, ignore_errors=True)
         kind = "reference"
@@ -193,8 +194,38 @@ def cpu_baseline_leg(n_reads):
         dt = time.perf_counter() - t0
         kind = "port"
         what = "CPU oracle port (oracle/gmove_oracle.c), in memory, incl. text formatting"
-    return {"value": n_samples / dt, "unit": UNIT, "cores": 1, "kind": kind,
-            "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples, {dt:.1f} s): {what}"}
+    out = {"value": n_samples / dt, "unit": UNIT, "cores": 1, "kind": kind,
+           "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples, {dt:.1f} s): {what}"}
+    if kind == "reference" and cli:
+        out["same_files_through_cli"] = cli
+    return out
+
+
+def _cli_leg(opts, d, fl, ref_files, n_samples):
+    """The C++ command line of this build on the SAME files the reference just processed (file to file:
+    BLOW5 decode on host threads, device batches, dump/ written). Also checks the bytes."""
+    import oracle_lib as ol
+    cli = os.path.join(ROOT, "poregen_b200", "bin", "poregen")
+    if not os.path.exists(cli):
+        return None
+    cmd = [cli, "gmove"] + ol.cli_args(opts) + ["--fastq", fl["fastq"], os.path.join(d, "reads.blow5"), fl["align"], os.path.join(d, "cli_out")]
+    best = None
+    for i in range(2):   # the first run pays CUDA context creation and the SLOW5 index
+        shutil.rmtree(os.path.join(d, "cli_out"), ignore_errors=True)
+        t0 = time.perf_counter()
+        p = subprocess.run(cmd, capture_output=True)
+        dt = time.perf_counter() - t0
+        if p.returncode != 0:
+            return {"error": p.stderr.decode()[-300:]}
+        best = dt if best is None else min(best, dt)
+    same = True
+    for name, data in ref_files.items():
+        path = os.path.join(d, "cli_out", name if name == "freq.txt" else os.path.join("dump", name))
+        if not os.path.exists(path) or open(path, "rb").read() != data:
+            same = False
+            break
+    return {"value": n_samples / best, "unit": UNIT, "seconds": best, "identical_to_reference": same,
+            "note": "process start to exit, incl. CUDA context creation (~0.3-0.5 s)"}
 
 
 def run_own_arm(args):
@@ -291,23 +322,25 @@ def run_own_arm(args):
         dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
     ms_step = float(t_res.item()) / args.steps
 
-    # ---- end to end: pinned host buffers in, host result out, every step
+    # ---- end to end: pinned host buffers in, the dump TEXT (what the reference fprintf's, formatted on the
+    # device) out to host memory, every step. A second context with PGM_OUT_TEXT does this leg.
+    import copy
+    import ctypes as C
+    topts = copy.copy(opts)
+    topts.output = capi.PGM_OUT_TEXT
+    eng.close()
+    eng = GmoveEngine(topts, device=local, stream=stream.cuda_stream)
+    if world > 1:
+        counts_t = torch.as_tensor(_DevArr(eng.counts_ptr(), NS), device=f"cuda:{local}")
+
     def step_e2e():
         eng.reset()
+        r = capi.PgmResult()
         if world == 1:
-            r = capi.PgmResult()
-            import ctypes as C
             cb = batch.to_c()
             eng._chk(eng.lib.pgm_process(eng._ctx, C.byref(cb), C.byref(r)))
             return r
         eng.upload(batch)
-        step_resident_no_reset()
-        import ctypes as C
-        r = capi.PgmResult()
-        eng._chk(eng.lib.pgm_download(eng._ctx, C.byref(r)))
-        return r
-
-    def step_resident_no_reset():
         eng.count()
         dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
         c64 = all_counts.to(torch.int64)
@@ -317,6 +350,8 @@ def run_own_arm(args):
         step_resident.keep = (prior, consumed)
         eng.set_prior(prior.data_ptr(), consumed.data_ptr())
         eng.emit()
+        eng._chk(eng.lib.pgm_download(eng._ctx, C.byref(r)))
+        return r
 
     for _ in range(max(1, args.warmup // 2)):
         r = step_e2e()
@@ -331,7 +366,8 @@ def run_own_arm(args):
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     e2e_s = float(t_e2e.item())
     h2d = int(batch.raw.nbytes + batch.align.nbytes + batch.bases.nbytes + batch.reads.nbytes)
-    d2h = int(r.n_sel_samples * 8 + r.n_sel_events * 12 + NS * 8 + batch.n_reads + 32)
+    text_bytes = int(C.cast(r.slot_text_off, C.POINTER(C.c_uint64))[NS])
+    d2h = int(text_bytes + r.n_sel_events * 20 + NS * 16 + batch.n_reads + 48)
     examined = int(r.n_events_examined)
 
     tot = torch.tensor([n_samples, examined, int(r.n_sel_events), int(r.n_sel_samples)], dtype=torch.float64, device=f"cuda:{local}")
@@ -346,10 +382,10 @@ def run_own_arm(args):
         E_pass, E_sel, S_sel = int(res0.n_events_pass), int(res0.ev_len.size), int(res0.samples.size)
         act = np.unique(res0.ev_read)
         S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
-        alg = {"prep": 120 * R, "decode_count": T + NB + 88 * R, "decode_emit": T + NB + 16 * E_pass,
-               "sort": 16 * E_pass, "select": 8 * E_pass + 12 * E_sel, "stats_wide": 0,
+        alg = {"prep": 120 * R, "decode_count": T + NB + 88 * R + 16 * E_pass, "decode_emit": 0,
+               "sort": 16 * E_pass + 12 * E_sel, "select": 16 * NS, "stats_wide": 0,
                "signal": (2 * S_act if opts.scaling else 2 * S_sel) + 8 * S_sel + 12 * E_pass,
-               "scan": 4 * R + 12 * E_sel, "misc": 8 * NS}
+               "scan": 12 * E_sel, "misc": 8 * NS, "text": 0}
         alg_step = 2 * n_samples + T + NB + 24 * R + 8 * S_sel + 12 * E_sel + 4 * NS
         peak, peak_src = measured_peak()
         stage_rows = {}
@@ -367,7 +403,8 @@ def run_own_arm(args):
                 "events_per_sec": tot_events / (ms_step * 1e-3),
                 "events_selected_per_step": tot_sel_ev, "samples_selected_per_step": tot_sel_samp,
                 "e2e": {"value": tot_samples / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "events_per_sec": tot_events / e2e_s,
-                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "output": "dump text (%.8f, formatted on the device), per-event index, per-k-mer counts"},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": ncu_traffic(dom), "peak_source": peak_src,

@@ -12,6 +12,9 @@ OUT="$PKG/bin/poregen"
 if [ ! -d "$SLOW5LIB/src" ]; then
     echo "build_cli: $SLOW5LIB not present; keeping prebuilt $OUT (if any)"; exit 0
 fi
+if [ -x "$OUT" ] && [ "$OUT" -nt "$HERE/gmove_cli.cpp" ] && [ "$OUT" -nt "$PKG/../include/pgm_gmove.h" ] && [ "$OUT" -nt "$PKG/libpgm_gmove.so" ]; then
+    exit 0
+fi
 CC=${CC:-gcc}; CXX=${CXX:-g++}
 DEPS="$PKG/_deps"; mkdir -p "$DEPS/obj" "$PKG/bin"
 SVB="$SLOW5LIB/thirdparty/streamvbyte"
