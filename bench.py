@@ -93,7 +93,7 @@ def run_reference_arm(args):
                              "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples) per step; "
                                        "reference binary built -O2, end to end incl. BLOW5 read and dump/ text output"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -278,12 +278,7 @@ def run_own_arm(args):
         eng.count()
         if world > 1:
             dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
-            c64 = all_counts.to(torch.int64)
-            excl = torch.cumsum(c64, 0)[rank] - c64[rank]
-            prior = torch.clamp(excl, max=limit).to(torch.int32)
-            consumed = torch.clamp(c64.sum(0), max=limit).to(torch.int32)
-            step_resident.keep = (prior, consumed)
-            eng.set_prior(prior.data_ptr(), consumed.data_ptr())
+            eng.set_gathered(all_counts.data_ptr(), world, rank)   # lower-rank / all-rank sums inside k_quota
         eng.emit()
 
     def barrier():
@@ -343,12 +338,7 @@ def run_own_arm(args):
         eng.upload(batch)
         eng.count()
         dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
-        c64 = all_counts.to(torch.int64)
-        excl = torch.cumsum(c64, 0)[rank] - c64[rank]
-        prior = torch.clamp(excl, max=limit).to(torch.int32)
-        consumed = torch.clamp(c64.sum(0), max=limit).to(torch.int32)
-        step_resident.keep = (prior, consumed)
-        eng.set_prior(prior.data_ptr(), consumed.data_ptr())
+        eng.set_gathered(all_counts.data_ptr(), world, rank)
         eng.emit()
         eng._chk(eng.lib.pgm_download(eng._ctx, C.byref(r)))
         return r
@@ -415,14 +405,36 @@ def run_own_arm(args):
                 "stages": stage_rows, "clocks": clocks}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(args.cpu_reads)
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def protect_stdout():
+    """The contract is ONE JSON line on stdout. Libraries (NCCL's version banner, build scripts) write to
+    fd 1 behind Python's back, so fd 1 is pointed at stderr for the whole run and the line goes to a
+    duplicate of the original stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

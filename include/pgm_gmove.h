@@ -181,6 +181,11 @@ int pgm_sync(pgm_ctx *ctx);
 int pgm_counts_device(pgm_ctx *ctx, uint32_t **counts_dev);
 int pgm_totals_device(pgm_ctx *ctx, uint32_t **consumed_dev);
 int pgm_set_prior(pgm_ctx *ctx, const uint32_t *prior_dev, const uint32_t *consumed_dev);
+/* Fused form: hand over the all-gathered counts themselves (device uint32[n_ranks][n_slots], rank
+ * order = record order) and this context's rank; the quota kernel of pgm_emit sums the lower ranks
+ * (prior) and all ranks (totals after the round) per slot on the fly, on top of the totals the
+ * context carried into the round. The exchange is then one all-gather and no extra launch. */
+int pgm_set_gathered(pgm_ctx *ctx, const uint32_t *all_counts_dev, uint32_t n_ranks, uint32_t rank);
 
 /* Host-side form of the same exchange for callers that do not link the CUDA runtime (the C++ CLI):
  * pgm_counts_host copies counts[n_slots] out after pgm_count (synchronises the stream);

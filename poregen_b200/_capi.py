@@ -114,6 +114,7 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
+    "pgm_set_gathered",
 ]
 PGM_N_STAGES = 10
 
@@ -156,6 +157,8 @@ def load() -> C.CDLL:
     lib.pgm_totals_device.restype = C.c_int
     lib.pgm_set_prior.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.pgm_set_prior.restype = C.c_int
+    lib.pgm_set_gathered.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    lib.pgm_set_gathered.restype = C.c_int
     lib.pgm_stream.argtypes = [C.c_void_p]
     lib.pgm_stream.restype = C.c_void_p
     lib.pgm_launch_count.argtypes = [C.c_void_p]

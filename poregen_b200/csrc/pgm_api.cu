@@ -59,6 +59,8 @@ struct pgm_ctx {
     uint32_t lb_ticket = 0;          // look-back scans launched since the last zeroing (each gets its own ticket + status words)
     size_t lb_used = 0, lb_words = 0;   // status words handed out / available in zbatch
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
+    const uint32_t *gathered = nullptr;       // pgm_set_gathered
+    uint32_t n_ranks = 1, rank = 0;
 
     // batch (device view) + owned copies
     DevBatch db{};
@@ -302,7 +304,7 @@ int pgm_reset(pgm_ctx *c) {
     if (!c) return PGM_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaMemsetAsync(c->consumed.p, 0, (size_t)c->opts.n_slots * 4, c->stream));
-    c->user_prior = c->user_consumed = nullptr;
+    c->user_prior = c->user_consumed = nullptr; c->gathered = nullptr;
     if (c->state != ST_IDLE) c->state = ST_LOADED;  // the loaded batch stays usable: count/emit can be re-run
     return PGM_OK;
 }
@@ -444,7 +446,7 @@ int pgm_count(pgm_ctx *c) {
         c->lb_used = 0;
         if (!R) CU(c, cudaMemsetAsync(P<uint32_t>(c->ev_base), 0, 4, st));
     }
-    c->user_prior = c->user_consumed = nullptr;
+    c->user_prior = c->user_consumed = nullptr; c->gathered = nullptr;
     DevOpts d = c->dopts;
     d.mode = c->db.mode;
     if (R) {
@@ -517,7 +519,7 @@ int pgm_set_prior_host(pgm_ctx *c, const uint32_t *prior, const uint32_t *consum
     CU(c, cudaMemcpyAsync(c->hp_prior.p, prior, sb, cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaMemcpyAsync(c->hp_consumed.p, consumed, sb, cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));   // the host arrays may go away
-    c->user_prior = P<uint32_t>(c->hp_prior); c->user_consumed = P<uint32_t>(c->hp_consumed);
+    c->user_prior = P<uint32_t>(c->hp_prior); c->user_consumed = P<uint32_t>(c->hp_consumed); c->gathered = nullptr;
     return PGM_OK;
 }
 void *pgm_alloc_pinned(size_t bytes) {
@@ -531,10 +533,18 @@ int pgm_device_count(void) {
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
     return n;
 }
+int pgm_set_gathered(pgm_ctx *c, const uint32_t *all_counts_dev, uint32_t n_ranks, uint32_t rank) {
+    if (!c || !all_counts_dev || !n_ranks || rank >= n_ranks) return PGM_ERR_ARG;
+    if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_set_gathered belongs between pgm_count and pgm_emit");
+    c->gathered = all_counts_dev; c->n_ranks = n_ranks; c->rank = rank;
+    c->user_prior = nullptr; c->user_consumed = nullptr;
+    return PGM_OK;
+}
+
 int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consumed_dev) {
     if (!c || !prior_dev || !consumed_dev) return PGM_ERR_ARG;
     if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_set_prior belongs between pgm_count and pgm_emit");
-    c->user_prior = prior_dev; c->user_consumed = consumed_dev;
+    c->user_prior = prior_dev; c->user_consumed = consumed_dev; c->gathered = nullptr;
     return PGM_OK;
 }
 
@@ -565,6 +575,7 @@ int pgm_emit(pgm_ctx *c) {
         q.n_slots = NS; q.limit = c->opts.sample_limit;
         q.prior = c->user_prior ? c->user_prior : P<uint32_t>(c->consumed);
         q.user_consumed = c->user_consumed;
+        q.gathered = c->gathered; q.n_ranks = c->n_ranks; q.rank = c->rank;
         q.counts = P<uint32_t>(c->counts); q.keep = P<uint32_t>(c->keep); q.consumed = P<uint32_t>(c->consumed);
         q.bucket_base = P<uint32_t>(c->bucket_base); q.sel_base = P<uint32_t>(c->sel_base);
         k_quota<<<cdiv(NS, LB_TILE), PGM_BLOCK, 0, st>>>(q, next_lb(c, cdiv(NS, LB_TILE)));

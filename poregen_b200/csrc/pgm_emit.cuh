@@ -103,6 +103,8 @@ struct QuotaIO {
     const uint32_t *prior;          // totals this rank must treat as already emitted
     const uint32_t *user_consumed;  // multi-GPU: totals after the round (or nullptr: prior + keep)
     const uint32_t *counts;
+    const uint32_t *gathered;       // multi-GPU, fused form: counts of every rank [n_ranks][n_slots] (or nullptr)
+    uint32_t n_ranks, rank;
     uint32_t *keep, *consumed, *bucket_base, *sel_base;   // consumed may alias prior
 };
 
@@ -111,10 +113,22 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf st) {
         io.n_slots, st,
         [&](uint64_t s) {
             const uint32_t c = io.counts[s];
-            const uint32_t p = min(io.prior[s], io.limit);
+            uint32_t p = min(io.prior[s], io.limit), after;
+            if (io.gathered) {
+                // prior = before + counts of the lower ranks, totals after the round = before + all ranks
+                unsigned long long lower = p, all = p;
+                for (uint32_t h = 0; h < io.n_ranks; h++) {
+                    const uint32_t v = io.gathered[(size_t)h * io.n_slots + s];
+                    all += v;
+                    if (h < io.rank) lower += v;
+                }
+                p = (uint32_t)min(lower, (unsigned long long)io.limit);
+                after = (uint32_t)min(all, (unsigned long long)io.limit);
+            }
             const uint32_t k = min(c, io.limit - p);
             io.keep[s] = k;
-            io.consumed[s] = io.user_consumed ? io.user_consumed[s] : p + k;
+            if (!io.gathered) after = io.user_consumed ? io.user_consumed[s] : p + k;
+            io.consumed[s] = after;
             return (unsigned long long)c | ((unsigned long long)k << 31);   // two 31-bit sums in one 62-bit scan value
         },
         [&](uint64_t s, unsigned long long ex, unsigned long long) {

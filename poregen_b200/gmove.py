@@ -112,6 +112,10 @@ class GmoveEngine:
     def set_prior(self, prior_dev_ptr: int, consumed_dev_ptr: int):
         self._chk(self.lib.pgm_set_prior(self._ctx, C.c_void_p(prior_dev_ptr), C.c_void_p(consumed_dev_ptr)))
 
+    def set_gathered(self, all_counts_dev_ptr: int, n_ranks: int, rank: int):
+        """Fused exchange: the all-gathered [n_ranks, n_slots] uint32 counts (device) and this rank."""
+        self._chk(self.lib.pgm_set_gathered(self._ctx, C.c_void_p(all_counts_dev_ptr), n_ranks, rank))
+
     def profile_enable(self, on: bool = True):
         self._chk(self.lib.pgm_profile_enable(self._ctx, 1 if on else 0))
 

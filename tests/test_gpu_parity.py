@@ -50,7 +50,8 @@ def test_streamed_batches(built, label, cfg, opts):
             assert_same(res, ref, f"{label}[{lo}:{hi}]")
 
 
-def test_two_rank_quota_exchange_on_one_gpu(built):
+@pytest.mark.parametrize("fused", [False, True], ids=["set_prior", "set_gathered"])
+def test_two_rank_quota_exchange_on_one_gpu(built, fused):
     """The multi-GPU rule (all-gather of per-k-mer counts, exclusive scan over ranks) emulated with
     two contexts on one device: rank 0 owns the first half of the records, rank 1 the second. The
     concatenation of the two slices must equal the serial oracle run."""
@@ -79,10 +80,14 @@ def test_two_rank_quota_exchange_on_one_gpu(built):
             counts.append(torch.as_tensor(Dev(e.counts_ptr(), ns), device="cuda").cpu().numpy().astype(np.uint32))
         prior, consumed = quota_exchange(np.stack(counts), np.zeros(ns, np.uint32), opts.sample_limit)
         outs = []
+        gathered = torch.from_numpy(np.stack(counts).astype(np.int32)).cuda()
         for g, e in enumerate(engs):
             p = torch.from_numpy(prior[g].astype(np.int32)).cuda()
             c = torch.from_numpy(consumed.astype(np.int32)).cuda()
-            e.set_prior(p.data_ptr(), c.data_ptr())
+            if fused:
+                e.set_gathered(gathered.data_ptr(), 2, g)      # sums over ranks inside the quota kernel
+            else:
+                e.set_prior(p.data_ptr(), c.data_ptr())
             e.emit()
             outs.append(e.download())
     finally:
