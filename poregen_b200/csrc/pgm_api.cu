@@ -60,6 +60,7 @@ struct pgm_ctx {
     size_t lb_used = 0, lb_words = 0;   // status words handed out / available in zbatch
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
     const uint32_t *gathered = nullptr;       // pgm_set_gathered
+    size_t text_written_cap = 0;              // capacity of `text` when pgm_emit formatted into it (0: it did not)
     uint32_t n_ranks = 1, rank = 0;
 
     // batch (device view) + owned copies
@@ -646,6 +647,16 @@ int pgm_emit(pgm_ctx *c) {
         k_scan_text<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, st>>>(tio.ev_tlen, tio.ev_toff, tio.n_sel, &SCALARS(c)->n_text,
                                                                                 next_lb(c, cdiv((uint64_t)c->ev_cap + 1, LB_TILE)));
         c->launches += 2;
+        // The exact text size is a device-side number. When the buffer of an earlier batch is still around, write
+        // into it right away (the kernel drops what does not fit): pgm_download then only has to check that the
+        // text fitted, and the formatting overlaps whatever the host does before it calls pgm_download.
+        c->text_written_cap = 0;
+        if (c->text.cap) {
+            k_text_write<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio);
+            k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), tio.ev_toff, NS, P<unsigned long long>(c->slot_toff));
+            c->launches += 2;
+            c->text_written_cap = c->text.cap;
+        }
     }
     CU(c, cudaGetLastError());
     c->state = ST_EMITTED;
@@ -685,15 +696,17 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     if (nsamp && !as_text) CU(c, cudaMemcpyAsync(c->h_samples.p, c->samples.p, nsamp * 8, cudaMemcpyDeviceToHost, st));
     if (as_text) {   // the length is known now: format into an exactly sized buffer, then bring it over
         const size_t nt = (size_t)s.n_text;
-        RET(ensure(c, c->text, nt + 16));
         RET(ensure_host(c, c->h_text, nt + 16));
         RET(ensure_host(c, c->h_slot_toff, (size_t)(NS + 1) * 8));
         RET(ensure_host(c, c->h_ev_toff, (ne + 1) * 8));
-        TextIO tio = make_text_io(c);
-        if (ne) { k_text_write<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio); c->launches++; }
-        k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), tio.ev_toff, NS, P<unsigned long long>(c->slot_toff));
-        c->launches++;
-        CU(c, cudaGetLastError());
+        if (nt + 16 > c->text_written_cap) {   // first batch, or the text outgrew the buffer pgm_emit wrote into
+            RET(ensure(c, c->text, nt + nt / 8 + 16));
+            TextIO tio = make_text_io(c);
+            if (ne) { k_text_write<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio); c->launches++; }
+            k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), tio.ev_toff, NS, P<unsigned long long>(c->slot_toff));
+            c->launches++;
+            CU(c, cudaGetLastError());
+        }
         if (nt) CU(c, cudaMemcpyAsync(c->h_text.p, c->text.p, nt, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_slot_toff.p, c->slot_toff.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_toff.p, c->ev_toff.p, (ne + 1) * 8, cudaMemcpyDeviceToHost, st));
