@@ -1,0 +1,8 @@
+import sys; sys.path.insert(0,'.')
+from poregen_b200 import synth, workloads
+from poregen_b200.gmove import GmoveEngine
+cfg,opts=workloads.c2(n_reads=10000)
+b=synth.make_batch(cfg)
+with GmoveEngine(opts) as e:
+    for i in range(2):
+        e.upload(b); e.count(); e.emit(); e.sync()

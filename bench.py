@@ -395,8 +395,8 @@ def run_own_arm(args):
         act = np.unique(res0.ev_read)
         S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
         alg = {"prep": 120 * R, "decode_count": T + NB + 88 * R + 16 * E_pass, "decode_emit": 0,
-               "sort": 16 * E_pass + 12 * E_sel, "select": 16 * NS, "stats_wide": 0,
-               "signal": (2 * S_act if opts.scaling else 2 * S_sel) + 8 * S_sel + 12 * E_pass,
+               "sort": 16 * E_pass + 12 * E_sel, "select": 16 * NS, "stats": (2 * S_act + 48 * R) if opts.scaling else 0,
+               "gather": 2 * S_sel + 8 * S_sel + 20 * E_sel,
                "scan": 12 * E_sel, "misc": 8 * NS, "text": 0}
         alg_step = 2 * n_samples + T + NB + 24 * R + 8 * S_sel + 12 * E_sel + 4 * NS
         peak, peak_src = measured_peak()

@@ -217,8 +217,8 @@ uint64_t pgm_launch_count(const pgm_ctx *ctx);
 #define PGM_STAGE_DECODE_EMIT 3  /* k_decode_* <EMIT>                                              */
 #define PGM_STAGE_SORT 4         /* radix sort passes (histogram, scan, scatter)                   */
 #define PGM_STAGE_SELECT 5       /* k_select_prep, k_select                                        */
-#define PGM_STAGE_STATS 6        /* k_stats_wide (Med-MAD of records with a wide in-range code span) */
-#define PGM_STAGE_GATHER 7       /* k_signal: per-record Med-MAD + gather of the selected samples  */
+#define PGM_STAGE_STATS 6        /* k_stats (+ k_stats_wide): exact Med-MAD of every record that owns a selected event */
+#define PGM_STAGE_GATHER 7       /* k_gather: the selected samples as doubles, in output order     */
 #define PGM_STAGE_MISC 8         /* memsets                                                        */
 #define PGM_STAGE_TEXT 9         /* PGM_OUT_TEXT: k_text_len, k_scan_text (k_text_write runs in pgm_download) */
 #define PGM_N_STAGES 10

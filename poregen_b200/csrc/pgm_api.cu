@@ -244,6 +244,9 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         return fail(nullptr, PGM_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
     if (prop.major != 10) return fail(nullptr, PGM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
 
+    if ((e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess)
+        return fail(nullptr, PGM_ERR_CUDA, "cudaFuncSetAttribute(k_stats): %s", cudaGetErrorString(e));
+
     pgm_ctx *c = new pgm_ctx();
     c->opts = *opts;
     c->device = device;
@@ -625,19 +628,26 @@ int pgm_emit(pgm_ctx *c) {
         c->launches++;
     }
     if (R && c->ev_cap) {
-        if (c->opts.scaling && c->need_wide) {
+        if (c->opts.scaling) {
             StageTimer t(c, PGM_STAGE_STATS);
-            uint32_t *queue = MISC(c);
-            k_stats_wide<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), HAS_SEL(c), P<ReadCal>(c->cal), queue,
-                                                            P<uint32_t>(c->gscratch));
+            if (c->need_wide) {
+                k_stats_wide<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, P<uint8_t>(c->rflags), HAS_SEL(c), P<ReadCal>(c->cal), MISC(c),
+                                                                P<uint32_t>(c->gscratch));
+                c->launches++;
+            }
+            StatsIO si;
+            si.rflags = P<uint8_t>(c->rflags); si.read_has_sel = HAS_SEL(c); si.cal = P<ReadCal>(c->cal); si.ticket = MISC(c) + 2;
+            const uint32_t sgrid = (uint32_t)std::min<uint64_t>(cdiv(R, STATS_WARPS), (uint64_t)c->n_sm * 3);
+            k_stats<<<sgrid, STATS_WARPS * 32, STATS_DYN_SMEM, st>>>(d, c->db, si);
             c->launches++;
         }
         StageTimer t(c, PGM_STAGE_GATHER);
-        SignalIO g;
-        g.rflags = P<uint8_t>(c->rflags); g.read_has_sel = HAS_SEL(c); g.cal = P<ReadCal>(c->cal);
-        g.ev_base = P<uint32_t>(c->ev_base); g.ev_start = P<uint32_t>(c->ev_start); g.ev_len = P<uint32_t>(c->ev_len); g.ev_out = P<uint32_t>(c->ev_out);
-        g.sel_off = P<uint64_t>(c->sel_off); g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
-        k_signal<<<R, SIG_THREADS, 0, st>>>(d, c->db, g);
+        GatherIO g;
+        g.sel_start = P<uint32_t>(c->sel_start); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
+        g.sel_off = P<uint64_t>(c->sel_off); g.n_sel = P<uint32_t>(c->sel_base) + NS; g.cal = P<ReadCal>(c->cal);
+        g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
+        if (c->opts.scaling) k_gather<true><<<c->n_sm * 2, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        else k_gather<false><<<c->n_sm * 2, PGM_BLOCK, 0, st>>>(d, c->db, g);
         c->launches++;
     }
     if (c->opts.output == PGM_OUT_TEXT) {
@@ -725,7 +735,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     return PGM_OK;
 }
 
-static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats_wide", "signal", "misc", "text"};
+static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats", "gather", "misc", "text"};
 
 const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }
 

@@ -1,5 +1,5 @@
-// pgm_signal.cuh — the signal side of gmove: exact Med-MAD and the gather of selected samples,
-// fused into one kernel per record so the raw signal is read from HBM once.
+// pgm_signal.cuh — the signal side of gmove: exact Med-MAD per record (k_stats, k_stats_wide) and the
+// gather of the selected samples in output order (k_gather).
 //
 // Med-MAD without sorting doubles (reference gmove.cpp:142-184, 600-609): pA(code) is monotone in the
 // int16 code, so the multiset {x_i} (every out-of-range sample replaced by 0.0) is a
@@ -9,13 +9,9 @@
 #pragma once
 #include "pgm_device.cuh"
 
-#define SIG_SMEM_BINS 2048      // in-range code span handled in shared memory by k_signal
+#define SIG_SMEM_BINS 2048      // in-range code span k_stats handles (per-warp shared-memory histogram)
 #define STATS_SMEM_BINS 8192    // k_stats_wide: shared memory up to here, then global scratch
-#define SIG_THREADS 128         // k_signal CTA: many small CTAs per SM overlap each other's serial phases
-#define SIG_WARPS (SIG_THREADS / 32)
-#define SIG_CH 4096             // samples per TMA chunk (8 KB)
-#define SIG_NST 3               // ring stages; records of up to SIG_NST*SIG_CH samples stay resident for the gather
-#define SIG_EV_TILE SIG_THREADS
+#define SIG_GATHER_U 4          // selected events a warp of k_gather keeps in flight
 #define PGM_FULL 0xffffffffu
 
 struct StatsCtx {
@@ -103,6 +99,7 @@ __device__ __forceinline__ void stats_histogram(const int16_t *raw, uint64_t fir
     }
 }
 
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void red_shared_inc(uint32_t saddr) { asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(saddr) : "memory"); }
 
 // ------------------------------------------------------------------------------------------------
@@ -270,7 +267,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_stats_wide(DevOpts o, DevBatch b,
         const ReadCal rc = cal[r];
         StatsCtx c;
         c.nb = (rc.chi >= rc.clo) ? (uint32_t)(rc.chi - rc.clo + 1) : 0u;
-        if (c.nb <= SIG_SMEM_BINS) continue;   // k_signal does these itself
+        if (c.nb <= SIG_SMEM_BINS) continue;   // k_stats does these itself
         const pgm_read rd = b.reads[r];
         const uint64_t first = rd.raw_off + rd.trim;
         const uint32_t n = rd.raw_len - rd.trim;
@@ -290,49 +287,129 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_stats_wide(DevOpts o, DevBatch b,
 }
 
 // ------------------------------------------------------------------------------------------------
-// TMA 1-D bulk copy + mbarrier (sm_90+/sm_100a PTX): one elected thread streams a record's signal
-// from HBM into a shared-memory ring; the copy engine signals a transaction barrier per chunk.
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+// The signal side runs as two kernels. Measured on B200 (profiles/micro/smem_hist.cu):
+// shared-memory red.add retires 8-10 increments per clock per SM on nanopore-like code distributions, so the
+// histogram is cheap; what a one-CTA-per-record kernel pays for is LATENCY (dependent metadata loads, the
+// serial order-statistics search, the per-event gather), with three of four warps idle most of the time.
+// So: k_stats gives every record to ONE warp (no block barriers, many records in flight per SM), and
+// k_gather walks the selected events in OUTPUT order (coalesced metadata, coalesced stores), independent
+// of records.
+
+struct StatsIO {
+    const uint8_t *rflags, *read_has_sel;
+    ReadCal *cal;
+    uint32_t *ticket;    // zeroed per batch
+};
+
+#define STATS_WARPS 8
+#define STATS_HWORDS (SIG_SMEM_BINS + 4)
+#define STATS_DYN_SMEM (STATS_WARPS * STATS_HWORDS * 4)
+
+__device__ __forceinline__ int4 ldg_stream_v4(const int4 *p) {
+    int4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
 }
-__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+
+// k_stats: exact Med-MAD (gmove.cpp:142-184, 600-609) of every record that owns a selected event and whose
+// in-range code span fits SIG_SMEM_BINS. Persistent warps take records from a ticket counter; a warp
+// streams its record from HBM (four 16-byte loads per lane in flight), counts the codes into its own
+// shared-memory histogram with red.shared, and derives med / mad on the histogram (warp_medmad).
+__global__ void __launch_bounds__(STATS_WARPS * 32) k_stats(DevOpts o, DevBatch b, StatsIO io) {
+    extern __shared__ __align__(16) uint32_t sm_stats[];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t *H = sm_stats + w * STATS_HWORDS;
+    const uint32_t sbase = smem_u32(H);
+    for (;;) {
+        uint32_t r = 0;
+        if (lane == 0) r = atomicAdd(io.ticket, 1u);
+        r = __shfl_sync(PGM_FULL, r, 0);
+        if (r >= b.n_reads) break;
+        const pgm_read *rp = b.reads + r;
+        const uint8_t f_skip = io.rflags[r], f_sel = io.read_has_sel[r];
+        const uint64_t raw_off = rp->raw_off;
+        const uint32_t raw_len = rp->raw_len, trim = rp->trim;
+        const double offset = rp->offset;
+        const ReadCal rc = io.cal[r];
+        if (f_skip != 0 || !f_sel) continue;
+        const uint32_t nb = (rc.chi >= rc.clo) ? (uint32_t)(rc.chi - rc.clo + 1) : 0u;
+        if (nb > SIG_SMEM_BINS) continue;   // k_stats_wide
+        const int clo = rc.clo;
+        const uint64_t first = raw_off + trim;
+        const uint32_t n = raw_len - trim;
+        const uint64_t endp = first + n;
+        const uint64_t a0 = first & ~(uint64_t)7;
+        uint64_t a1 = (endp + 7) & ~(uint64_t)7;
+        if (a1 > (b.n_raw & ~(uint64_t)7)) a1 = b.n_raw & ~(uint64_t)7;   // never read past the array: the last few samples go scalar
+        if (a1 < a0) a1 = a0;
+        const uint32_t ng = (uint32_t)((a1 - a0) >> 3);
+        const uint32_t head = (uint32_t)(first - a0), rel_end = head + n;   // record = [head, rel_end) relative to a0
+        const int4 *v4 = reinterpret_cast<const int4 *>(b.raw + a0);
+        // first loads on their way while the histogram is cleared
+        int4 q[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) q[u] = (lane + 32u * u < ng) ? ldg_stream_v4(v4 + lane + 32u * u) : make_int4(0, 0, 0, 0);
+        for (uint32_t i = lane; i < (nb + 4) / 4; i += 32) reinterpret_cast<uint4 *>(H)[i] = make_uint4(0, 0, 0, 0);
+        __syncwarp();
+        // out-of-range codes are clamped into the extra bin H[nb] (never read by the order statistics)
+        auto add = [&](int code) { red_shared_inc(sbase + 4u * min((uint32_t)(code - clo), nb)); };
+        auto add8 = [&](const int4 &x, uint32_t g) {
+            const uint32_t i0 = 8u * g;
+            const int v[8] = {(int)(int16_t)(x.x & 0xffff), x.x >> 16, (int)(int16_t)(x.y & 0xffff), x.y >> 16,
+                              (int)(int16_t)(x.z & 0xffff), x.z >> 16, (int)(int16_t)(x.w & 0xffff), x.w >> 16};
+            if (i0 >= head && i0 + 8 <= rel_end) {
+#pragma unroll
+                for (int t = 0; t < 8; t++) add(v[t]);
+            } else {
+#pragma unroll
+                for (int t = 0; t < 8; t++)
+                    if (i0 + t >= head && i0 + t < rel_end) add(v[t]);
+            }
+        };
+        for (uint32_t g0 = 0; g0 < ng; g0 += 128) {
+            int4 nx[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t g = g0 + 128u + lane + 32u * u;
+                nx[u] = (g < ng) ? ldg_stream_v4(v4 + g) : make_int4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t g = g0 + lane + 32u * u;
+                if (g < ng) add8(q[u], g);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) q[u] = nx[u];
+        }
+        {   // samples the aligned image does not cover (only at the very end of raw[])
+            const uint64_t t0 = (a1 > first) ? a1 : first;
+            for (uint64_t i = t0 + lane; i < endp; i += 32) add(b.raw[i]);
+        }
+        __syncwarp();
+        StatsCtx c;
+        c.nb = nb; c.clo = clo; c.off = offset; c.scale = rc.scale; c.inc = !(rc.scale < 0.0);
+        c.H = H;
+        double med, mad;
+        warp_medmad(c, n, (o.debug & 1u) != 0, &med, &mad);
+        if (lane == 0) { io.cal[r].med = med; io.cal[r].mad = mad; }
+        __syncwarp();
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_signal: one CTA per record that owns at least one selected event.
-//   1. (scaling) the record's signal is streamed by TMA bulk copies into a shared-memory ring and
-//      histogrammed from there (in-range codes); warp 0 then derives the exact med / mad. Records of
-//      up to SIG_NST * SIG_CH samples stay resident in the ring for step 2.
-//   2. gather: for every selected event of the record, raw -> pA (0.0 when out of range)
-//      -> (x - med) / mad (gmove.cpp:611-613) -> the event's place in the slot-grouped output
-//      (the doubles gmove.cpp:664-678 prints). Selected events are compacted into shared memory
-//      (start, length, output offset) and every warp keeps four events in flight.
-// The record's passing events are the contiguous id range [ev_base[r], ev_base[r+1]); ev_out[id]
-// is the event's index in the selected order (or PGM_INVALID), sel_off its sample offset.
-struct SignalIO {
-    const uint8_t *rflags, *read_has_sel;
-    ReadCal *cal;
-    const uint32_t *ev_base;                      // [R+1]
-    const uint32_t *ev_start, *ev_len, *ev_out;   // [E]
-    const uint64_t *sel_off;                      // [E_sel+1]
+// k_gather: the doubles the reference prints (gmove.cpp:664-678), in slot-grouped output order.
+// A warp takes 32 consecutive selected events: lane j fetches event j's metadata and its record's
+// calibration (coalesced / L2-resident), then the warp walks the 32 events SIG_GATHER_U at a time, all lanes on
+// one event's samples: raw -> pA (0.0 when out of range) -> (x - med) / mad (gmove.cpp:611-613).
+// Output offsets of consecutive events are consecutive, so the stores of a warp form one contiguous stream.
+struct GatherIO {
+    const uint32_t *sel_start, *sel_len, *sel_read;   // [E_sel]
+    const uint64_t *sel_off;                          // [E_sel+1]
+    const uint32_t *n_sel;
+    const ReadCal *cal;
     double *samples;
     uint64_t samples_cap;
 };
-
-struct SelEv { uint32_t st, ln; uint64_t off; };
 
 struct SigConv {   // raw code -> the double the reference prints
     int clo; uint32_t nbins;
@@ -356,161 +433,127 @@ struct SigConv {   // raw code -> the double the reference prints
     }
 };
 
-// Every warp walks the compacted selected events four at a time (independent load -> convert -> store
-// chains); x is the record's signal relative to its first (trimmed) sample, in shared or global memory.
-__device__ __forceinline__ void sig_gather(const SelEv *sel, uint32_t ns, const int16_t *__restrict__ x, const SigConv &cv,
-                                           double *__restrict__ samples) {
-    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (uint32_t base = w * 4; base < ns; base += SIG_WARPS * 4) {
-        SelEv m[4];
-        int c[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const uint32_t e = base + u;
-            m[u] = sel[min(e, ns - 1)];
-            if (e >= ns) m[u].ln = 0;
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) c[u] = (lane < m[u].ln) ? (int)x[m[u].st + lane] : 0;
-#pragma unroll
-        for (int u = 0; u < 4; u++)
-            if (lane < m[u].ln) samples[m[u].off + lane] = cv(c[u]);
-        if (max(max(m[0].ln, m[1].ln), max(m[2].ln, m[3].ln)) > 32) {
-#pragma unroll
-            for (int u = 0; u < 4; u++)
-                for (uint32_t t = lane + 32; t < m[u].ln; t += 32) samples[m[u].off + t] = cv((int)x[m[u].st + t]);
-        }
-    }
-}
+__device__ __forceinline__ double shfl_f64(double v, int src) { return __shfl_sync(PGM_FULL, v, src); }
+__device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shfl_sync(PGM_FULL, (unsigned long long)v, src); }
 
-__global__ void __launch_bounds__(SIG_THREADS) k_signal(DevOpts o, DevBatch b, SignalIO io) {
-    __shared__ __align__(128) int16_t sm_ring[SIG_NST * SIG_CH];
-    __shared__ __align__(8) uint64_t sm_full[SIG_NST];
-    __shared__ __align__(16) uint32_t sm_hist[SIG_SMEM_BINS + 4];   // reused for the selected-event list after the statistics
-    __shared__ double sm_mm[2];
-    __shared__ uint32_t sm_nsel;
-    SelEv *sm_sel = reinterpret_cast<SelEv *>(sm_hist);
-    static_assert(SIG_EV_TILE * sizeof(SelEv) <= sizeof(uint32_t) * (SIG_SMEM_BINS + 4), "event list must fit the histogram area");
-    const uint32_t r = blockIdx.x;
-    const uint32_t tid = threadIdx.x;
-    if (io.rflags[r] != 0 || !io.read_has_sel[r]) return;
-    const pgm_read *rp = b.reads + r;
-    const uint64_t first = rp->raw_off + rp->trim;
-    const uint32_t n = rp->raw_len - rp->trim;
-    const double offset = rp->offset;
-    const ReadCal rc = io.cal[r];
-    const uint32_t e0 = io.ev_base[r], e1 = io.ev_base[r + 1];
-    // metadata of the first tile of events: requested now, used after the statistics
-    uint32_t pq = PGM_INVALID, pst = 0, pln = 0;
-    uint64_t poff = 0;
-    if (e0 + tid < e1) {
-        pq = io.ev_out[e0 + tid];
-        if (pq != PGM_INVALID) { pst = io.ev_start[e0 + tid]; pln = io.ev_len[e0 + tid]; poff = io.sel_off[pq]; }
-    }
-    if (tid == 0) sm_nsel = 0;
-    SigConv cv;
-    cv.clo = rc.clo; cv.nbins = (rc.chi >= rc.clo) ? (uint32_t)(rc.chi - rc.clo + 1) : 0u;
-    cv.offset = offset; cv.scale = rc.scale; cv.med = rc.med; cv.mad = rc.mad;   // wide records: filled by k_stats_wide
-    cv.scaling = o.scaling != 0;
-    bool resident = false;
-    uint32_t head = 0;   // samples between the 16-byte aligned start of the ring image and the record's first sample
-    if (o.scaling && cv.nbins <= SIG_SMEM_BINS) {
-        const uint32_t nb = cv.nbins;
-        const int clo = rc.clo;
-        const uint64_t endp = first + n;
-        const uint64_t a0 = first & ~(uint64_t)7;
-        uint64_t a1 = (endp + 7) & ~(uint64_t)7;
-        if (a1 > (b.n_raw & ~(uint64_t)7)) a1 = b.n_raw & ~(uint64_t)7;   // never read past the array: the last few samples go scalar
-        if (a1 < a0) a1 = a0;
-        const uint32_t nal = (uint32_t)(a1 - a0);
-        const uint32_t nch = (nal + SIG_CH - 1) / SIG_CH;
-        head = (uint32_t)(first - a0);
-        const uint32_t rel_end = head + n;       // record = [head, rel_end) relative to a0
-        if (tid == 0) {
-            for (int s = 0; s < SIG_NST; s++) mbar_init(&sm_full[s], 1);
-            mbar_fence_init();
+// What lane j holds for event q0 + j.
+struct GatherEv {
+    uint32_t ln;          // samples (0: nothing to write)
+    uint64_t src, off;    // first sample in raw[], first output slot
+    int clo; uint32_t nbins;
+    double offset, scale, med, mad, rcp;
+    int fast_div;
+};
+
+template <bool SCALING>
+__global__ void __launch_bounds__(PGM_BLOCK, 2) k_gather(DevOpts o, DevBatch b, GatherIO io) {
+    const uint32_t n = *io.n_sel;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t stride = gridDim.x * PGM_WARPS * 32;
+    uint32_t q0 = (blockIdx.x * PGM_WARPS + (threadIdx.x >> 5)) * 32;
+    if (q0 >= n) return;
+    // level 1: the event's own row (coalesced). level 2: its record's calibration (needs level 1's record index).
+    // Both only ISSUE loads: nothing here may look at a loaded value (no selects on them either), or the warp
+    // would wait for the round trip on the spot; finish() does the arithmetic one batch later.
+    uint32_t st1 = 0, rd1 = 0, ln1 = 0, ok1 = 0;
+    uint64_t off1 = 0;
+    auto level1 = [&](uint32_t base) {
+        const uint32_t q = base + lane;
+        ok1 = (q < n) ? 1u : 0u;
+        const uint32_t qq = min(q, n - 1);
+        st1 = io.sel_start[qq]; rd1 = io.sel_read[qq]; ln1 = io.sel_len[qq]; off1 = io.sel_off[qq];
+    };
+    uint64_t raw_off2 = 0;
+    uint32_t trim2 = 0, st2 = 0, ok2 = 0;
+    int chi2 = 0;
+    auto level2 = [&]() {
+        GatherEv e;
+        const uint32_t rd = ok1 ? rd1 : 0u;     // level 1 arrived an iteration ago
+        const pgm_read *rp = b.reads + rd;
+        const ReadCal *rc = io.cal + rd;
+        e.ln = ln1; e.off = off1; st2 = st1; ok2 = ok1;
+        raw_off2 = rp->raw_off; trim2 = rp->trim;
+        e.offset = rp->offset;
+        e.clo = rc->clo; chi2 = rc->chi; e.scale = rc->scale;
+        e.med = 0.0; e.mad = 1.0; e.rcp = 1.0; e.fast_div = 1; e.src = 0; e.nbins = 0;
+        if (SCALING) { e.med = rc->med; e.mad = rc->mad; }
+        return e;
+    };
+    auto finish = [&](GatherEv &e) {   // one reciprocal per event's record (see SigConv)
+        e.src = raw_off2 + trim2 + st2;
+        e.nbins = (chi2 >= e.clo) ? (uint32_t)(chi2 - e.clo + 1) : 0u;
+        if (!ok2 || e.off + e.ln > io.samples_cap) e.ln = 0;
+        if (e.ln == 0) e.src = 0;   // the load below is unconditional: keep its address inside raw[]
+        if (SCALING) {
+            e.rcp = __drcp_rn(e.mad);
+            e.fast_div = ((__double_as_longlong(e.mad) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1 : 0;
         }
-        for (uint32_t i = tid; i <= nb; i += SIG_THREADS) sm_hist[i] = 0;
-        __syncthreads();
-        auto issue = [&](uint32_t j) {
-            const uint32_t s = j % SIG_NST;
-            const uint32_t len = min((uint32_t)SIG_CH, nal - j * SIG_CH);
-            mbar_expect_tx(&sm_full[s], len * 2);
-            tma_bulk_g2s(sm_ring + s * SIG_CH, b.raw + a0 + (uint64_t)j * SIG_CH, len * 2, &sm_full[s]);
-        };
-        if (tid == 0)
-            for (uint32_t j = 0; j < nch && j < SIG_NST; j++) issue(j);
-        const uint32_t sbase = smem_u32(sm_hist);
-        // out-of-range codes are clamped into the extra bin H[nb] (never read by the order statistics)
-        auto add = [&](int code) { red_shared_inc(sbase + 4u * min((uint32_t)(code - clo), nb)); };
-        {   // samples the aligned image does not cover (only at the very end of raw[])
-            const uint64_t t0 = (a1 > first) ? a1 : first;
-            for (uint64_t i = t0 + tid; i < endp; i += SIG_THREADS) add(b.raw[i]);
+    };
+    // Software pipeline over the warp's batches: while batch k is converted, the calibration loads of batch k+1
+    // (level 2) and the rows of batch k+2 (level 1) are in flight.
+    level1(q0);
+    GatherEv cur = level2();
+    finish(cur);
+    if (q0 + stride < n) level1(q0 + stride);
+    for (;;) {
+        const bool more = q0 + stride < n;
+        GatherEv nxt;
+        if (more) {
+            nxt = level2();
+            if (q0 + 2 * stride < n) level1(q0 + 2 * stride);
         }
-        for (uint32_t j = 0; j < nch; j++) {
-            const uint32_t s = j % SIG_NST;
-            while (!mbar_try_wait(&sm_full[s], (j / SIG_NST) & 1)) {}
-            const uint32_t rel0 = j * SIG_CH;
-            const uint32_t ng = min((uint32_t)SIG_CH, nal - rel0) >> 3;
-            const int4 *v4 = reinterpret_cast<const int4 *>(sm_ring + s * SIG_CH);
-            for (uint32_t g = tid; g < ng; g += SIG_THREADS) {
-                const int4 q = v4[g];
-                const uint32_t i0 = rel0 + 8u * g;
-                const int v[8] = {(int)(int16_t)(q.x & 0xffff), q.x >> 16, (int)(int16_t)(q.y & 0xffff), q.y >> 16,
-                                  (int)(int16_t)(q.z & 0xffff), q.z >> 16, (int)(int16_t)(q.w & 0xffff), q.w >> 16};
-                if (i0 >= head && i0 + 8 <= rel_end) {
 #pragma unroll
-                    for (int t = 0; t < 8; t++) add(v[t]);
-                } else {
+        for (int half = 0; half < 2; half++) {
+            constexpr int U = 16;
+            // One aligned 4-byte load per lane covers an event of up to 63 samples: lane j reads samples
+            // 2j and 2j+1 counted from the even address at or below the event's first sample. Loads are
+            // unconditional (inactive lanes re-read the event's first word) so that all U of them are in
+            // flight before the first conversion.
+            uint32_t word[U];
 #pragma unroll
-                    for (int t = 0; t < 8; t++)
-                        if (i0 + t >= head && i0 + t < rel_end) add(v[t]);
+            for (int u = 0; u < U; u++) {
+                const int s = half * U + u;
+                const uint32_t eln = __shfl_sync(PGM_FULL, cur.ln, s);
+                const uint64_t esrc = shfl_u64(cur.src, s);
+                const uint64_t a = esrc & ~(uint64_t)1;
+                uint64_t idx = a + 2u * lane;
+                if (idx >= esrc + eln) idx = a;
+                // the word holding the very last sample of raw[] would reach past the array: read that sample alone
+                word[u] = (idx + 1 < b.n_raw) ? *reinterpret_cast<const uint32_t *>(b.raw + idx) : (uint32_t)(uint16_t)b.raw[idx];
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int s = half * U + u;
+                const uint32_t eln = __shfl_sync(PGM_FULL, cur.ln, s);
+                const uint64_t esrc = shfl_u64(cur.src, s);
+                const uint64_t eoff = shfl_u64(cur.off, s);
+                SigConv cv;
+                cv.clo = __shfl_sync(PGM_FULL, cur.clo, s);
+                cv.nbins = __shfl_sync(PGM_FULL, cur.nbins, s);
+                cv.offset = shfl_f64(cur.offset, s);
+                cv.scale = shfl_f64(cur.scale, s);
+                cv.scaling = SCALING;
+                cv.med = 0.0; cv.mad = 1.0; cv.rcp = 1.0; cv.fast_div = true;
+                if (SCALING) {
+                    cv.med = shfl_f64(cur.med, s);
+                    cv.mad = shfl_f64(cur.mad, s);
+                    cv.rcp = shfl_f64(cur.rcp, s);
+                    cv.fast_div = __shfl_sync(PGM_FULL, cur.fast_div, s) != 0;
                 }
+                const uint32_t odd = (uint32_t)(esrc & 1);
+                const uint32_t t0 = 2u * lane - odd;   // index within the event of the word's low half (lane 0 of an odd start: -1, fails t0 < eln)
+                const uint32_t w = word[u];
+                const double v0 = cv((int)(int16_t)(w & 0xffffu)), v1 = cv((int)w >> 16);
+                if (t0 < eln) io.samples[eoff + t0] = v0;
+                const uint32_t t1 = t0 + 1;            // 32-bit on purpose: -1 + 1 = 0
+                if (t1 < eln) io.samples[eoff + t1] = v1;
+                if (eln > 64 - odd)   // events longer than one row of words (--max_dur above 63)
+                    for (uint32_t t = 64 - odd + lane; t < eln; t += 32) io.samples[eoff + t] = cv((int)b.raw[esrc + t]);
             }
-            if (j + SIG_NST < nch) {   // ring slot is reused: everybody is done reading it
-                __syncthreads();
-                if (tid == 0) {
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    issue(j + SIG_NST);
-                }
-            }
         }
-        resident = (nch <= SIG_NST) && (a1 >= endp);
-        __syncthreads();
-        if (tid < 32) {
-            StatsCtx c;
-            c.nb = nb; c.clo = clo; c.off = offset; c.scale = rc.scale; c.inc = !(rc.scale < 0.0);
-            c.H = sm_hist;
-            double med, mad;
-            warp_medmad(c, n, (o.debug & 1u) != 0, &med, &mad);
-            if (tid == 0) { sm_mm[0] = med; sm_mm[1] = mad; }
-        }
-        __syncthreads();
-        cv.med = sm_mm[0]; cv.mad = sm_mm[1];
-    }
-    cv.rcp = __drcp_rn(cv.mad);
-    cv.fast_div = ((__double_as_longlong(cv.mad) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll);
-    const int16_t *xg = b.raw + first;
-    const int16_t *xs = sm_ring + head;
-    for (uint32_t t0 = e0; t0 < e1; t0 += SIG_EV_TILE) {
-        if (t0 != e0) {
-            __syncthreads();   // previous tile gathered
-            if (tid == 0) sm_nsel = 0;
-            pq = PGM_INVALID;
-            if (t0 + tid < e1) {
-                pq = io.ev_out[t0 + tid];
-                if (pq != PGM_INVALID) { pst = io.ev_start[t0 + tid]; pln = io.ev_len[t0 + tid]; poff = io.sel_off[pq]; }
-            }
-            __syncthreads();
-        }
-        if (pq != PGM_INVALID && poff + pln <= io.samples_cap) {
-            const uint32_t p = atomicAdd(&sm_nsel, 1u);
-            SelEv e; e.st = pst; e.ln = pln; e.off = poff;
-            sm_sel[p] = e;
-        }
-        __syncthreads();
-        const uint32_t ns = sm_nsel;
-        if (resident) sig_gather(sm_sel, ns, xs, cv, io.samples);
-        else sig_gather(sm_sel, ns, xg, cv, io.samples);
+        if (!more) break;
+        finish(nxt);
+        cur = nxt;
+        q0 += stride;
     }
 }

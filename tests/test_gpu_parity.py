@@ -123,3 +123,23 @@ def test_medmad_rank_every_bin_path(built, label, cfg, opts, monkeypatch):
     with GmoveEngine(opts) as eng:
         res = eng.process(batch)
     assert_same(res, ref, label)
+
+
+@pytest.mark.parametrize("flat", [False, True], ids=["events", "constant"])
+def test_medmad_long_records(built, flat):
+    """Records several times longer than the shared-memory ring of k_signal (streamed, not resident for the
+    gather). The 'constant' variant puts every sample of a record on ONE code: one histogram bin takes
+    every increment."""
+    from cases import _o
+    from poregen_b200.synth import SynthConfig
+    opts = _o(kmer_size=5, sample_limit=200, scaling=1)
+    batch = synth.make_batch(SynthConfig(n_reads=5, median_samples=150000, seed=91))
+    if flat:
+        raw = batch.raw.copy()
+        for r in batch.reads:
+            raw[r["raw_off"]:r["raw_off"] + r["raw_len"]] = 500 + int(r["raw_len"]) % 7
+        batch = type(batch)(batch.mode, raw, batch.align, batch.bases, batch.reads, batch.read_ids)
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        res = eng.process(batch)
+    assert_same(res, ref, "long")
