@@ -646,8 +646,8 @@ int pgm_emit(pgm_ctx *c) {
         g.sel_start = P<uint32_t>(c->sel_start); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
         g.sel_off = P<uint64_t>(c->sel_off); g.n_sel = P<uint32_t>(c->sel_base) + NS; g.cal = P<ReadCal>(c->cal);
         g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
-        if (c->opts.scaling) k_gather<true><<<c->n_sm * 2, PGM_BLOCK, 0, st>>>(d, c->db, g);
-        else k_gather<false><<<c->n_sm * 2, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        if (c->opts.scaling) k_gather<true><<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        else k_gather<false><<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, g);
         c->launches++;
     }
     if (c->opts.output == PGM_OUT_TEXT) {

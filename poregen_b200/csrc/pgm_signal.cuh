@@ -436,124 +436,102 @@ struct SigConv {   // raw code -> the double the reference prints
 __device__ __forceinline__ double shfl_f64(double v, int src) { return __shfl_sync(PGM_FULL, v, src); }
 __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shfl_sync(PGM_FULL, (unsigned long long)v, src); }
 
-// What lane j holds for event q0 + j.
-struct GatherEv {
-    uint32_t ln;          // samples (0: nothing to write)
-    uint64_t src, off;    // first sample in raw[], first output slot
-    int clo; uint32_t nbins;
-    double offset, scale, med, mad, rcp;
-    int fast_div;
+// Per-warp staging area of k_gather: the 32 events of a batch as structure-of-arrays, and the map from an
+// output position of the batch (window of GATHER_MAP positions) to its event.
+#define GATHER_MAP 2048
+struct GatherStage {
+    uint8_t map[GATHER_MAP];
+    long long base[32];       // raw index of output position 0 of the batch, as seen from this event: src - rel
+    int clo[32];
+    uint32_t nbins[32];
+    double offset[32], scale[32], med[32], mad[32], rcp[32];
+    uint32_t fast[32];
 };
 
+// k_gather: a warp takes 32 consecutive selected events. Lane j fetches event j's row and its record's
+// calibration (coalesced / L2-resident, prefetched two batches ahead) and publishes them in shared memory;
+// the batch's output is one contiguous range of samples[], which the warp then walks position by position:
+// lane -> position -> event (byte map) -> raw sample -> double -> coalesced 256-byte stores. Every lane converts
+// a sample in every step, whatever the event lengths are.
 template <bool SCALING>
-__global__ void __launch_bounds__(PGM_BLOCK, 2) k_gather(DevOpts o, DevBatch b, GatherIO io) {
+__global__ void __launch_bounds__(PGM_BLOCK) k_gather(DevOpts o, DevBatch b, GatherIO io) {
+    __shared__ __align__(16) GatherStage sm_stage[PGM_WARPS];
+    GatherStage &S = sm_stage[threadIdx.x >> 5];
     const uint32_t n = *io.n_sel;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t stride = gridDim.x * PGM_WARPS * 32;
     uint32_t q0 = (blockIdx.x * PGM_WARPS + (threadIdx.x >> 5)) * 32;
     if (q0 >= n) return;
-    // level 1: the event's own row (coalesced). level 2: its record's calibration (needs level 1's record index).
-    // Both only ISSUE loads: nothing here may look at a loaded value (no selects on them either), or the warp
-    // would wait for the round trip on the spot; finish() does the arithmetic one batch later.
-    uint32_t st1 = 0, rd1 = 0, ln1 = 0, ok1 = 0;
-    uint64_t off1 = 0;
+    // level 1: the event's own row. level 2: its record's calibration (needs level 1's record index). Both only
+    // ISSUE loads; nothing looks at a loaded value until a batch later.
+    uint32_t st1, rd1, ln1, ok1;
+    uint64_t off1;
     auto level1 = [&](uint32_t base) {
         const uint32_t q = base + lane;
         ok1 = (q < n) ? 1u : 0u;
         const uint32_t qq = min(q, n - 1);
         st1 = io.sel_start[qq]; rd1 = io.sel_read[qq]; ln1 = io.sel_len[qq]; off1 = io.sel_off[qq];
     };
-    uint64_t raw_off2 = 0;
-    uint32_t trim2 = 0, st2 = 0, ok2 = 0;
-    int chi2 = 0;
+    uint64_t raw_off2, off2;
+    uint32_t trim2, st2, ok2, ln2;
+    int clo2, chi2;
+    double offset2, scale2, med2 = 0.0, mad2 = 1.0;
     auto level2 = [&]() {
-        GatherEv e;
         const uint32_t rd = ok1 ? rd1 : 0u;     // level 1 arrived an iteration ago
         const pgm_read *rp = b.reads + rd;
         const ReadCal *rc = io.cal + rd;
-        e.ln = ln1; e.off = off1; st2 = st1; ok2 = ok1;
-        raw_off2 = rp->raw_off; trim2 = rp->trim;
-        e.offset = rp->offset;
-        e.clo = rc->clo; chi2 = rc->chi; e.scale = rc->scale;
-        e.med = 0.0; e.mad = 1.0; e.rcp = 1.0; e.fast_div = 1; e.src = 0; e.nbins = 0;
-        if (SCALING) { e.med = rc->med; e.mad = rc->mad; }
-        return e;
+        ln2 = ln1; off2 = off1; st2 = st1; ok2 = ok1;
+        raw_off2 = rp->raw_off; trim2 = rp->trim; offset2 = rp->offset;
+        clo2 = rc->clo; chi2 = rc->chi; scale2 = rc->scale;
+        if (SCALING) { med2 = rc->med; mad2 = rc->mad; }
     };
-    auto finish = [&](GatherEv &e) {   // one reciprocal per event's record (see SigConv)
-        e.src = raw_off2 + trim2 + st2;
-        e.nbins = (chi2 >= e.clo) ? (uint32_t)(chi2 - e.clo + 1) : 0u;
-        if (!ok2 || e.off + e.ln > io.samples_cap) e.ln = 0;
-        if (e.ln == 0) e.src = 0;   // the load below is unconditional: keep its address inside raw[]
-        if (SCALING) {
-            e.rcp = __drcp_rn(e.mad);
-            e.fast_div = ((__double_as_longlong(e.mad) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1 : 0;
-        }
-    };
-    // Software pipeline over the warp's batches: while batch k is converted, the calibration loads of batch k+1
-    // (level 2) and the rows of batch k+2 (level 1) are in flight.
     level1(q0);
-    GatherEv cur = level2();
-    finish(cur);
+    level2();
     if (q0 + stride < n) level1(q0 + stride);
     for (;;) {
+        // ---- publish the batch (level 2 of this batch has arrived by now)
+        uint32_t ln = ok2 ? ln2 : 0u;
+        if (off2 + ln > io.samples_cap) ln = 0;
+        const uint64_t out0 = __shfl_sync(PGM_FULL, (unsigned long long)off2, 0);        // first output position of the batch
+        // positions are relative to out0; an event that writes nothing keeps rel = its (unused) offset
+        const uint32_t rel = (uint32_t)(off2 - out0);
+        const uint32_t endrel = ln ? rel + ln : 0u;
+        uint32_t total = endrel;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) total = max(total, __shfl_xor_sync(PGM_FULL, total, d));
+        S.base[lane] = (long long)(raw_off2 + trim2 + st2) - (long long)rel;
+        S.clo[lane] = clo2;
+        S.nbins[lane] = (chi2 >= clo2) ? (uint32_t)(chi2 - clo2 + 1) : 0u;
+        S.offset[lane] = offset2; S.scale[lane] = scale2;
+        if (SCALING) {
+            S.med[lane] = med2; S.mad[lane] = mad2; S.rcp[lane] = __drcp_rn(mad2);
+            S.fast[lane] = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
+        }
         const bool more = q0 + stride < n;
-        GatherEv nxt;
         if (more) {
-            nxt = level2();
+            level2();
             if (q0 + 2 * stride < n) level1(q0 + 2 * stride);
         }
-#pragma unroll
-        for (int half = 0; half < 2; half++) {
-            constexpr int U = 16;
-            // One aligned 4-byte load per lane covers an event of up to 63 samples: lane j reads samples
-            // 2j and 2j+1 counted from the even address at or below the event's first sample. Loads are
-            // unconditional (inactive lanes re-read the event's first word) so that all U of them are in
-            // flight before the first conversion.
-            uint32_t word[U];
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int s = half * U + u;
-                const uint32_t eln = __shfl_sync(PGM_FULL, cur.ln, s);
-                const uint64_t esrc = shfl_u64(cur.src, s);
-                const uint64_t a = esrc & ~(uint64_t)1;
-                uint64_t idx = a + 2u * lane;
-                if (idx >= esrc + eln) idx = a;
-                // the word holding the very last sample of raw[] would reach past the array: read that sample alone
-                word[u] = (idx + 1 < b.n_raw) ? *reinterpret_cast<const uint32_t *>(b.raw + idx) : (uint32_t)(uint16_t)b.raw[idx];
-            }
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int s = half * U + u;
-                const uint32_t eln = __shfl_sync(PGM_FULL, cur.ln, s);
-                const uint64_t esrc = shfl_u64(cur.src, s);
-                const uint64_t eoff = shfl_u64(cur.off, s);
+        // ---- walk the batch's output range window by window
+        for (uint32_t w0 = 0; w0 < total; w0 += GATHER_MAP) {
+            __syncwarp();
+            const uint32_t lo = max(rel, w0), hi = min(endrel, w0 + GATHER_MAP);
+            for (uint32_t t = lo; t < hi; t++) S.map[t - w0] = (uint8_t)lane;
+            __syncwarp();
+            const uint32_t wend = min(total, w0 + GATHER_MAP);
+            for (uint32_t p = w0 + lane; p < wend; p += 32) {
+                const uint32_t e = S.map[p - w0];
+                const int code = (int)b.raw[S.base[e] + (long long)p];
                 SigConv cv;
-                cv.clo = __shfl_sync(PGM_FULL, cur.clo, s);
-                cv.nbins = __shfl_sync(PGM_FULL, cur.nbins, s);
-                cv.offset = shfl_f64(cur.offset, s);
-                cv.scale = shfl_f64(cur.scale, s);
+                cv.clo = S.clo[e]; cv.nbins = S.nbins[e]; cv.offset = S.offset[e]; cv.scale = S.scale[e];
                 cv.scaling = SCALING;
                 cv.med = 0.0; cv.mad = 1.0; cv.rcp = 1.0; cv.fast_div = true;
-                if (SCALING) {
-                    cv.med = shfl_f64(cur.med, s);
-                    cv.mad = shfl_f64(cur.mad, s);
-                    cv.rcp = shfl_f64(cur.rcp, s);
-                    cv.fast_div = __shfl_sync(PGM_FULL, cur.fast_div, s) != 0;
-                }
-                const uint32_t odd = (uint32_t)(esrc & 1);
-                const uint32_t t0 = 2u * lane - odd;   // index within the event of the word's low half (lane 0 of an odd start: -1, fails t0 < eln)
-                const uint32_t w = word[u];
-                const double v0 = cv((int)(int16_t)(w & 0xffffu)), v1 = cv((int)w >> 16);
-                if (t0 < eln) io.samples[eoff + t0] = v0;
-                const uint32_t t1 = t0 + 1;            // 32-bit on purpose: -1 + 1 = 0
-                if (t1 < eln) io.samples[eoff + t1] = v1;
-                if (eln > 64 - odd)   // events longer than one row of words (--max_dur above 63)
-                    for (uint32_t t = 64 - odd + lane; t < eln; t += 32) io.samples[eoff + t] = cv((int)b.raw[esrc + t]);
+                if (SCALING) { cv.med = S.med[e]; cv.mad = S.mad[e]; cv.rcp = S.rcp[e]; cv.fast_div = S.fast[e] != 0; }
+                io.samples[out0 + p] = cv(code);
             }
         }
         if (!more) break;
-        finish(nxt);
-        cur = nxt;
         q0 += stride;
+        __syncwarp();
     }
 }
