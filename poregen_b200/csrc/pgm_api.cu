@@ -79,7 +79,7 @@ struct pgm_ctx {
     DBuf zbatch;                       // zeroed every batch: scalars | misc words | scan status | read_has_sel[R] | tile histogram
     size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
     uint32_t sort_ntiles = 0;
-    DBuf sel_start, sel_len, sel_read, sel_off, samples, ev_out;
+    DBuf sel_start, sel_len, sel_read, sel_src, sel_off, samples;
     DBuf ev_tlen, ev_toff, text, slot_toff;   // PGM_OUT_TEXT
     DBuf hp_prior, hp_consumed;               // pgm_set_prior_host
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
@@ -212,7 +212,7 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->ev_out, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
+                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff};
     for (DBuf *b : host) release_host(*b);
@@ -244,8 +244,10 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         return fail(nullptr, PGM_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
     if (prop.major != 10) return fail(nullptr, PGM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
 
-    if ((e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess)
-        return fail(nullptr, PGM_ERR_CUDA, "cudaFuncSetAttribute(k_stats): %s", cudaGetErrorString(e));
+    if ((e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_gather<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_gather<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess)
+        return fail(nullptr, PGM_ERR_CUDA, "cudaFuncSetAttribute(k_stats / k_gather): %s", cudaGetErrorString(e));
 
     pgm_ctx *c = new pgm_ctx();
     c->opts = *opts;
@@ -350,9 +352,10 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->n_pass, (size_t)R * 4));
     RET(ensure(c, c->ev_base, (size_t)(R + 1) * 4));
     const size_t e4 = (size_t)cap * 4;
-    DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read, &c->ev_out};
+    DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read};
     for (DBuf *x : evb) RET(ensure(c, *x, e4));
     RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
+    RET(ensure(c, c->sel_src, (size_t)(cap + 1) * 8));
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
     c->sort_ntiles = ntiles;
     {   // per-batch zero region: scalars | misc words | look-back status words | read_has_sel[R] | tile histogram
@@ -613,7 +616,7 @@ int pgm_emit(pgm_ctx *c) {
                 r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
                 r.ev_start = P<uint32_t>(c->ev_start); r.ev_len = P<uint32_t>(c->ev_len); r.ev_read = P<uint32_t>(c->ev_read);
                 r.sel_start = P<uint32_t>(c->sel_start); r.sel_len = P<uint32_t>(c->sel_len); r.sel_read = P<uint32_t>(c->sel_read);
-                r.ev_out = P<uint32_t>(c->ev_out); r.read_has_sel = HAS_SEL(c);
+                r.sel_src = P<unsigned long long>(c->sel_src); r.reads = c->db.reads; r.read_has_sel = HAS_SEL(c);
                 k_rank<<<sgrid, PGM_BLOCK, 0, st>>>(r);
                 c->launches++;
             }
@@ -643,11 +646,11 @@ int pgm_emit(pgm_ctx *c) {
         }
         StageTimer t(c, PGM_STAGE_GATHER);
         GatherIO g;
-        g.sel_start = P<uint32_t>(c->sel_start); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
+        g.sel_src = P<unsigned long long>(c->sel_src); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
         g.sel_off = P<uint64_t>(c->sel_off); g.n_sel = P<uint32_t>(c->sel_base) + NS; g.cal = P<ReadCal>(c->cal);
         g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
-        if (c->opts.scaling) k_gather<true><<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, g);
-        else k_gather<false><<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(d, c->db, g);
+        if (c->opts.scaling) k_gather<true><<<c->n_sm * 5, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
+        else k_gather<false><<<c->n_sm * 5, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
         c->launches++;
     }
     if (c->opts.output == PGM_OUT_TEXT) {

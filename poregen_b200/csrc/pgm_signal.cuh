@@ -403,8 +403,9 @@ __global__ void __launch_bounds__(STATS_WARPS * 32) k_stats(DevOpts o, DevBatch 
 // one event's samples: raw -> pA (0.0 when out of range) -> (x - med) / mad (gmove.cpp:611-613).
 // Output offsets of consecutive events are consecutive, so the stores of a warp form one contiguous stream.
 struct GatherIO {
-    const uint32_t *sel_start, *sel_len, *sel_read;   // [E_sel]
-    const uint64_t *sel_off;                          // [E_sel+1]
+    const unsigned long long *sel_src;      // [E_sel] index in raw[] of the event's first sample
+    const uint32_t *sel_len, *sel_read;     // [E_sel]
+    const uint64_t *sel_off;                // [E_sel+1]
     const uint32_t *n_sel;
     const ReadCal *cal;
     double *samples;
@@ -436,82 +437,117 @@ struct SigConv {   // raw code -> the double the reference prints
 __device__ __forceinline__ double shfl_f64(double v, int src) { return __shfl_sync(PGM_FULL, v, src); }
 __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shfl_sync(PGM_FULL, (unsigned long long)v, src); }
 
-// Per-warp staging area of k_gather: the 32 events of a batch as structure-of-arrays, and the map from an
-// output position of the batch (window of GATHER_MAP positions) to its event.
-#define GATHER_MAP 2048
+// Per-warp staging area of k_gather: the raw samples of the batch's events (two buffers: the next batch's
+// arrive by cp.async while this one is converted), the 32 events as structure-of-arrays, and the map from
+// an output position of the batch (window of GATHER_MAP positions) to its event.
+#define GATHER_WARPS 4
+#define GATHER_MAP 1536
+#define GATHER_CH 6                         // 16-byte chunks staged per event: covers 41 samples at the worst alignment
+#define GATHER_EV_SAMPLES (GATHER_CH * 8)
+struct __align__(16) GatherEvP {   // 64 bytes, read with four 16-byte shared-memory loads
+    double offset, scale;
+    double med, mad;
+    double rcp;
+    int clo; uint32_t nbins;
+    int sidx;                 // index into the staged copy of output position 0 of the batch
+    uint32_t slim;            // positions below this one are staged (rel + staged samples)
+    uint32_t fast, pad;
+};
 struct GatherStage {
+    int16_t raw[2][32 * GATHER_EV_SAMPLES];
+    GatherEvP ev[32];
+    long long base[32];       // raw[] index of output position 0 of the batch as seen from this event: src - rel
     uint8_t map[GATHER_MAP];
-    long long base[32];       // raw index of output position 0 of the batch, as seen from this event: src - rel
-    int clo[32];
-    uint32_t nbins[32];
-    double offset[32], scale[32], med[32], mad[32], rcp[32];
-    uint32_t fast[32];
 };
 
-// k_gather: a warp takes 32 consecutive selected events. Lane j fetches event j's row and its record's
-// calibration (coalesced / L2-resident, prefetched two batches ahead) and publishes them in shared memory;
-// the batch's output is one contiguous range of samples[], which the warp then walks position by position:
-// lane -> position -> event (byte map) -> raw sample -> double -> coalesced 256-byte stores. Every lane converts
-// a sample in every step, whatever the event lengths are.
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// k_gather: a warp takes 32 consecutive selected events. Lane j fetches event j's row (two batches ahead), then
+// its record's calibration and - by cp.async, 16 bytes at a time, straight into shared memory - the event's
+// raw samples (one batch ahead), so nothing in the conversion loop waits on global memory. The batch's output
+// is one contiguous range of samples[], which the warp walks position by position: lane -> position -> event
+// (byte map) -> staged raw sample -> double -> coalesced 256-byte stores; every lane converts a sample in every
+// step, whatever the event lengths are.
 template <bool SCALING>
-__global__ void __launch_bounds__(PGM_BLOCK) k_gather(DevOpts o, DevBatch b, GatherIO io) {
-    __shared__ __align__(16) GatherStage sm_stage[PGM_WARPS];
-    GatherStage &S = sm_stage[threadIdx.x >> 5];
+__global__ void __launch_bounds__(GATHER_WARPS * 32) k_gather(DevOpts o, DevBatch b, GatherIO io) {
+    extern __shared__ __align__(16) uint8_t sm_gather[];
+    GatherStage &S = reinterpret_cast<GatherStage *>(sm_gather)[threadIdx.x >> 5];
     const uint32_t n = *io.n_sel;
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t stride = gridDim.x * PGM_WARPS * 32;
-    uint32_t q0 = (blockIdx.x * PGM_WARPS + (threadIdx.x >> 5)) * 32;
+    const uint32_t stride = gridDim.x * GATHER_WARPS * 32;
+    uint32_t q0 = (blockIdx.x * GATHER_WARPS + (threadIdx.x >> 5)) * 32;
     if (q0 >= n) return;
-    // level 1: the event's own row. level 2: its record's calibration (needs level 1's record index). Both only
-    // ISSUE loads; nothing looks at a loaded value until a batch later.
-    uint32_t st1, rd1, ln1, ok1;
-    uint64_t off1;
+    // level 1: the event's own row. level 2: its record's calibration and its raw samples (need level 1).
+    // Both only ISSUE loads; nothing looks at a loaded value until a batch later.
+    uint32_t rd1, ln1, ok1;
+    uint64_t off1, src1;
     auto level1 = [&](uint32_t base) {
         const uint32_t q = base + lane;
         ok1 = (q < n) ? 1u : 0u;
         const uint32_t qq = min(q, n - 1);
-        st1 = io.sel_start[qq]; rd1 = io.sel_read[qq]; ln1 = io.sel_len[qq]; off1 = io.sel_off[qq];
+        src1 = io.sel_src[qq]; rd1 = io.sel_read[qq]; ln1 = io.sel_len[qq]; off1 = io.sel_off[qq];
     };
-    uint64_t raw_off2, off2;
-    uint32_t trim2, st2, ok2, ln2;
+    uint64_t off2, src2;
+    uint32_t ln2, nst2;      // nst2: samples of the event present in the staged copy
     int clo2, chi2;
     double offset2, scale2, med2 = 0.0, mad2 = 1.0;
-    auto level2 = [&]() {
+    auto level2 = [&](uint32_t buf) {
         const uint32_t rd = ok1 ? rd1 : 0u;     // level 1 arrived an iteration ago
         const pgm_read *rp = b.reads + rd;
         const ReadCal *rc = io.cal + rd;
-        ln2 = ln1; off2 = off1; st2 = st1; ok2 = ok1;
-        raw_off2 = rp->raw_off; trim2 = rp->trim; offset2 = rp->offset;
+        ln2 = ok1 ? ln1 : 0u;
+        off2 = off1; src2 = src1;
+        if (off2 + ln2 > io.samples_cap) ln2 = 0;
+        offset2 = rp->offset;
         clo2 = rc->clo; chi2 = rc->chi; scale2 = rc->scale;
         if (SCALING) { med2 = rc->med; mad2 = rc->mad; }
+        // raw samples: the 16-byte chunks that hold [src, src + ln), at most GATHER_CH of them
+        const uint32_t mis = (uint32_t)(src2 & 7);                       // samples between the chunk boundary and src
+        const uint64_t c0 = src2 - mis;
+        const uint32_t need = ln2 ? (mis + ln2 + 7) >> 3 : 0u;
+        const uint32_t dst = smem_u32(&S.raw[buf][lane * GATHER_EV_SAMPLES]);
+#pragma unroll
+        for (int c = 0; c < GATHER_CH; c++)
+            if ((uint32_t)c < need) cp_async16(dst + 16u * c, b.raw + c0 + 8u * c);
+        cp_async_commit();
+        nst2 = ln2 ? min(ln2, (uint32_t)GATHER_EV_SAMPLES - mis) : 0u;
     };
     level1(q0);
-    level2();
+    level2(0);
     if (q0 + stride < n) level1(q0 + stride);
-    for (;;) {
-        // ---- publish the batch (level 2 of this batch has arrived by now)
-        uint32_t ln = ok2 ? ln2 : 0u;
-        if (off2 + ln > io.samples_cap) ln = 0;
+    for (uint32_t buf = 0;; buf ^= 1) {
+        // ---- publish the batch
+        const uint32_t ln = ln2;
         const uint64_t out0 = __shfl_sync(PGM_FULL, (unsigned long long)off2, 0);        // first output position of the batch
-        // positions are relative to out0; an event that writes nothing keeps rel = its (unused) offset
         const uint32_t rel = (uint32_t)(off2 - out0);
         const uint32_t endrel = ln ? rel + ln : 0u;
         uint32_t total = endrel;
 #pragma unroll
         for (int d = 16; d; d >>= 1) total = max(total, __shfl_xor_sync(PGM_FULL, total, d));
-        S.base[lane] = (long long)(raw_off2 + trim2 + st2) - (long long)rel;
-        S.clo[lane] = clo2;
-        S.nbins[lane] = (chi2 >= clo2) ? (uint32_t)(chi2 - clo2 + 1) : 0u;
-        S.offset[lane] = offset2; S.scale[lane] = scale2;
-        if (SCALING) {
-            S.med[lane] = med2; S.mad[lane] = mad2; S.rcp[lane] = __drcp_rn(mad2);
-            S.fast[lane] = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
+        S.base[lane] = (long long)src2 - (long long)rel;
+        {
+            GatherEvP ev;
+            ev.offset = offset2; ev.scale = scale2; ev.med = med2; ev.mad = mad2;
+            ev.rcp = SCALING ? __drcp_rn(mad2) : 1.0;
+            ev.clo = clo2; ev.nbins = (chi2 >= clo2) ? (uint32_t)(chi2 - clo2 + 1) : 0u;
+            ev.sidx = (int)(lane * GATHER_EV_SAMPLES + (uint32_t)(src2 & 7)) - (int)rel;
+            ev.slim = rel + nst2;
+            ev.fast = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
+            ev.pad = 0;
+            S.ev[lane] = ev;
         }
+        const bool all_staged = __all_sync(PGM_FULL, nst2 == ln);   // no event of the batch longer than its staged copy
+        cp_async_wait_all();      // this batch's raw samples (issued a batch ago) have landed
         const bool more = q0 + stride < n;
         if (more) {
-            level2();
+            level2(buf ^ 1);
             if (q0 + 2 * stride < n) level1(q0 + 2 * stride);
         }
+        const int16_t *staged = S.raw[buf];
         // ---- walk the batch's output range window by window
         for (uint32_t w0 = 0; w0 < total; w0 += GATHER_MAP) {
             __syncwarp();
@@ -519,15 +555,27 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_gather(DevOpts o, DevBatch b, Gat
             for (uint32_t t = lo; t < hi; t++) S.map[t - w0] = (uint8_t)lane;
             __syncwarp();
             const uint32_t wend = min(total, w0 + GATHER_MAP);
-            for (uint32_t p = w0 + lane; p < wend; p += 32) {
+            auto convert = [&](uint32_t p, auto fetch) {
                 const uint32_t e = S.map[p - w0];
-                const int code = (int)b.raw[S.base[e] + (long long)p];
+                const uint4 *ep = reinterpret_cast<const uint4 *>(&S.ev[e]);
+                const uint4 a0 = ep[0], a1 = ep[1], a2 = ep[2], a3 = ep[3];
                 SigConv cv;
-                cv.clo = S.clo[e]; cv.nbins = S.nbins[e]; cv.offset = S.offset[e]; cv.scale = S.scale[e];
-                cv.scaling = SCALING;
-                cv.med = 0.0; cv.mad = 1.0; cv.rcp = 1.0; cv.fast_div = true;
-                if (SCALING) { cv.med = S.med[e]; cv.mad = S.mad[e]; cv.rcp = S.rcp[e]; cv.fast_div = S.fast[e] != 0; }
+                cv.offset = __hiloint2double((int)a0.y, (int)a0.x); cv.scale = __hiloint2double((int)a0.w, (int)a0.z);
+                cv.med = __hiloint2double((int)a1.y, (int)a1.x); cv.mad = __hiloint2double((int)a1.w, (int)a1.z);
+                cv.rcp = __hiloint2double((int)a2.y, (int)a2.x); cv.clo = (int)a2.z; cv.nbins = a2.w;
+                cv.scaling = SCALING; cv.fast_div = a3.z != 0;
+                const int code = fetch(e, (int)a3.x, a3.y);
                 io.samples[out0 + p] = cv(code);
+            };
+            if (all_staged) {
+#pragma unroll 2
+                for (uint32_t p = w0 + lane; p < wend; p += 32)
+                    convert(p, [&](uint32_t, int sidx, uint32_t) { return (int)staged[sidx + (int)p]; });
+            } else {   // some event is longer than GATHER_EV_SAMPLES: its tail comes from global memory
+                for (uint32_t p = w0 + lane; p < wend; p += 32)
+                    convert(p, [&](uint32_t e, int sidx, uint32_t slim) {
+                        return (p < slim) ? (int)staged[sidx + (int)p] : (int)b.raw[S.base[e] + (long long)p];
+                    });
             }
         }
         if (!more) break;

@@ -126,7 +126,8 @@ struct RankIO {
     const uint32_t *bucket_base, *keep, *sel_base;
     const uint32_t *ev_start, *ev_len, *ev_read;  // [E] record-then-position order
     uint32_t *sel_start, *sel_len, *sel_read;     // [E_sel] grouped by slot
-    uint32_t *ev_out;                             // [E] selected index q of every passing event, or PGM_INVALID
+    unsigned long long *sel_src;                  // [E_sel] index in raw[] of the event's first sample
+    const pgm_read *reads;
     uint8_t *read_has_sel;                        // [R]
 };
 
@@ -183,10 +184,11 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_rank(RankIO io) {
                 const uint32_t id = io.vals_in ? io.vals_in[idx] : idx;
                 const bool sel = rank < io.keep[slot];
                 const uint32_t q = io.sel_base[slot] + rank;
-                io.ev_out[id] = sel ? q : PGM_INVALID;
                 if (sel) {
                     const uint32_t rr = io.ev_read[id];
-                    io.sel_start[q] = io.ev_start[id];
+                    const uint32_t st = io.ev_start[id];
+                    io.sel_start[q] = st;
+                    io.sel_src[q] = io.reads[rr].raw_off + io.reads[rr].trim + st;
                     io.sel_len[q] = io.ev_len[id];
                     io.sel_read[q] = rr;
                     io.read_has_sel[rr] = 1;

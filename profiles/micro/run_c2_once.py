@@ -1,4 +1,4 @@
-import sys; sys.path.insert(0,'.')
+import os, sys; sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
 from poregen_b200 import synth, workloads
 from poregen_b200.gmove import GmoveEngine
 cfg,opts=workloads.c2(n_reads=10000)
