@@ -394,7 +394,7 @@ def run_own_arm(args):
         E_pass, E_sel, S_sel = int(res0.n_events_pass), int(res0.ev_len.size), int(res0.samples.size)
         act = np.unique(res0.ev_read)
         S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
-        alg = {"prep": 120 * R, "decode_count": T + NB + 88 * R + 16 * E_pass, "decode_emit": 0,
+        alg = {"prep": 120 * R, "decode": T + NB + 88 * R + 16 * E_pass, "place": 32 * E_pass + 8 * R,
                "sort": 16 * E_pass + 12 * E_sel, "select": 16 * NS, "stats": (2 * S_act + 48 * R) if opts.scaling else 0,
                "gather": 2 * S_sel + 8 * S_sel + 20 * E_sel,
                "scan": 12 * E_sel, "misc": 8 * NS, "text": 0}

@@ -212,9 +212,9 @@ uint64_t pgm_launch_count(const pgm_ctx *ctx);
  * pgm_profile_read synchronises, adds up the elapsed time and launch count of every stage since
  * the last read into ms[PGM_N_STAGES] / launches[PGM_N_STAGES], and clears the record. */
 #define PGM_STAGE_PREP 0         /* k_read_prep, k_oor_check                                       */
-#define PGM_STAGE_DECODE_COUNT 1 /* k_decode_* <COUNT>                                             */
+#define PGM_STAGE_DECODE_COUNT 1 /* k_decode: alignment -> events, filters, per-k-mer counts      */
 #define PGM_STAGE_SCAN 2         /* prefix sums outside the sort                                   */
-#define PGM_STAGE_DECODE_EMIT 3  /* k_decode_* <EMIT>                                              */
+#define PGM_STAGE_PLACE 3        /* k_scan_records, k_place: events into batch-wide order          */
 #define PGM_STAGE_SORT 4         /* radix sort passes (histogram, scan, scatter)                   */
 #define PGM_STAGE_SELECT 5       /* k_select_prep, k_select                                        */
 #define PGM_STAGE_STATS 6        /* k_stats (+ k_stats_wide): exact Med-MAD of every record that owns a selected event */

@@ -188,11 +188,13 @@ struct StageTimer {
         a = get(c); b = get(c);
         cudaEventRecord(a, c->stream);
     }
-    ~StageTimer() {
+    void stop() {
         if (!a) return;
         cudaEventRecord(b, c->stream);
         c->spans.push_back({stage, a, b, (uint32_t)(c->launches - l0)});
+        a = nullptr;
     }
+    ~StageTimer() { stop(); }
 };
 
 }  // namespace
@@ -481,9 +483,12 @@ int pgm_count(pgm_ctx *c) {
             io.hist = HIST(c); io.ntiles_cap = c->sort_ntiles; io.hist_mask = (1u << per) - 1;
             const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
             k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            c->launches++;
+            t.stop();
+            StageTimer t2(c, PGM_STAGE_PLACE);
             k_scan_records<<<cdiv(R, LB_TILE), PGM_BLOCK, 0, st>>>(io.n_pass, io.ev_base, R, next_lb(c, cdiv(R, LB_TILE)));
             k_place<<<cdiv(R, DEC_WARPS), PGM_BLOCK, 0, st>>>(c->db, io);
-            c->launches += 3;
+            c->launches += 2;
         }
         CU(c, cudaGetLastError());
     }
@@ -738,7 +743,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     return PGM_OK;
 }
 
-static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode_count", "scan", "decode_emit", "sort", "select", "stats", "gather", "misc", "text"};
+static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode", "scan", "place", "sort", "select", "stats", "gather", "misc", "text"};
 
 const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }
 
