@@ -226,6 +226,26 @@ int pgm_profile_enable(pgm_ctx *ctx, int on);
 int pgm_profile_read(pgm_ctx *ctx, float *ms, uint32_t *launches);
 const char *pgm_stage_name(int stage);
 
+/* Model aggregation (K7; reference scripts/poregen.sh:54-85, calculate_mean_stddev_all): per k-mer, over
+ * all values of dump/<KMER> except the first (`tail -n +2`), `datamash median` and `datamash sstdev`, the
+ * latter clamped to stddev_limit. The script reads the dump TEXT, so the values are the "%.8f" decimals:
+ * value = N * 1e-8 with N the printed integer. pgm_model_begin starts (or restarts) a log of every
+ * following batch's selected samples (taken in pgm_download); pgm_model_finalize groups the log by k-mer
+ * in file order and returns rows[n_slots] (host memory owned by the context, valid until the next call).
+ * median = median_num / 2e8 exactly (median_num = sum of the two middle N, or twice the middle one). */
+typedef struct pgm_model_row {
+    double median, stddev;      /* NaN where datamash would print nothing / nan                    */
+    int64_t median_num;
+    uint64_t n;                 /* values used: the file's values minus the first                    */
+    uint32_t flags, pad;        /* PGM_MODEL_*                                                       */
+} pgm_model_row;
+#define PGM_MODEL_EMPTY 1u      /* fewer than two values in the file                                 */
+#define PGM_MODEL_NO_SD 2u      /* exactly two values: one left after the drop, sstdev undefined     */
+#define PGM_MODEL_RANGE 4u      /* some |value| * 1e8 does not fit int64 (or inf/nan): row not computed */
+#define PGM_MODEL_CLAMPED 8u    /* stddev was above stddev_limit                                     */
+int pgm_model_begin(pgm_ctx *ctx);
+int pgm_model_finalize(pgm_ctx *ctx, double stddev_limit, const pgm_model_row **rows_out);
+
 /* Test hook for the device formatter: the text of ONE event made of the n host doubles vals[]
  * ("%.8f," ... "%.8f;", gmove.cpp:674-678) into text_out[cap]; *len_out = its length (also when it
  * does not fit, in which case nothing is written). */

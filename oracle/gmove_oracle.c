@@ -373,3 +373,47 @@ int oracle_model_row(const double *vals, size_t n, double limit, double *median,
     free(c);
     return PGM_OK;
 }
+
+/* The same row computed the way the script really does it: from the TEXT of dump/<KMER>
+ * (scripts/poregen.sh:73-74: `tr ';,' '\n' < file | tail -n +2 | datamash median 1` / `sstdev 1`).
+ * Values are parsed with strtold, as GNU datamash does, and all arithmetic is long double (datamash's
+ * field type); datamash prints with "%.14Lg" (its default numeric format), which is what *_str hold.
+ * PARITY UNPINNED: GNU datamash is not installed here, its version is not pinned by the reference, and no
+ * reference test holds a model row.  Returns the number of values used (after the drop), 0 when the
+ * file has fewer than two values (datamash prints an empty line then). */
+static int ld_cmp(const void *a, const void *b) { long double x = *(const long double *)a, y = *(const long double *)b; return (x > y) - (x < y); }
+size_t oracle_model_row_text(const char *text, size_t len, double limit, double *median, double *stddev, char *median_str, char *stddev_str) {
+    size_t cap = 1024, n = 0;
+    long double *v = (long double *)malloc(cap * sizeof(long double));
+    size_t i = 0;
+    while (i < len) {
+        size_t j = i;
+        while (j < len && text[j] != ',' && text[j] != ';') j++;
+        if (j > i) {
+            char buf[512];
+            size_t L = j - i < sizeof buf - 1 ? j - i : sizeof buf - 1;
+            memcpy(buf, text + i, L); buf[L] = 0;
+            if (n == cap) { cap *= 2; v = (long double *)realloc(v, cap * sizeof(long double)); }
+            v[n++] = strtold(buf, NULL);
+        }
+        i = j + 1;
+    }
+    *median = NAN; *stddev = NAN;
+    if (median_str) median_str[0] = 0;
+    if (stddev_str) stddev_str[0] = 0;
+    if (n < 2) { free(v); return 0; }
+    size_t m = n - 1;
+    long double *c = v + 1;                                   /* tail -n +2 */
+    qsort(c, m, sizeof(long double), ld_cmp);
+    long double med = (m & 1) ? c[m / 2] : (c[m / 2 - 1] + c[m / 2]) / 2.0L;
+    long double mean = 0; for (size_t k = 0; k < m; k++) mean += c[k]; mean /= (long double)m;
+    long double ss = 0; for (size_t k = 0; k < m; k++) ss += (c[k] - mean) * (c[k] - mean);
+    long double sd = (m > 1) ? sqrtl(ss / (long double)(m - 1)) : (long double)NAN;
+    *median = (double)med;
+    if (median_str) sprintf(median_str, "%.14Lg", med);
+    if (sd > (long double)limit) { sd = limit; }              /* poregen.sh:77-79 */
+    *stddev = (double)sd;
+    if (stddev_str) sprintf(stddev_str, "%.14Lg", sd);
+    free(v);
+    return m;
+}

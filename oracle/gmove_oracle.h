@@ -43,6 +43,7 @@ int oracle_pick_kmer(const int *indel_pos, size_t n, int left, int k, int margin
  * value, median (mean of the two middles), sample stddev clamped to `limit`.  PARITY UNPINNED:
  * the arithmetic lives in GNU datamash, which is neither in the reference tree nor installed. */
 int oracle_model_row(const double *vals, size_t n, double limit, double *median, double *stddev);
+size_t oracle_model_row_text(const char *text, size_t len, double limit, double *median, double *stddev, char *median_str, char *stddev_str);
 
 #ifdef __cplusplus
 }

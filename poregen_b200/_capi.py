@@ -114,9 +114,12 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
-    "pgm_set_gathered",
+    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize",
 ]
 PGM_N_STAGES = 10
+# pgm_model_row (include/pgm_gmove.h)
+MODEL_ROW_DTYPE = [("median", "<f8"), ("stddev", "<f8"), ("median_num", "<i8"), ("n", "<u8"), ("flags", "<u4"), ("pad", "<u4")]
+PGM_MODEL_EMPTY, PGM_MODEL_NO_SD, PGM_MODEL_RANGE, PGM_MODEL_CLAMPED = 1, 2, 4, 8
 
 _lib = None
 
@@ -159,6 +162,10 @@ def load() -> C.CDLL:
     lib.pgm_set_prior.restype = C.c_int
     lib.pgm_set_gathered.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
     lib.pgm_set_gathered.restype = C.c_int
+    lib.pgm_model_begin.argtypes = [C.c_void_p]
+    lib.pgm_model_begin.restype = C.c_int
+    lib.pgm_model_finalize.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_void_p)]
+    lib.pgm_model_finalize.restype = C.c_int
     lib.pgm_stream.argtypes = [C.c_void_p]
     lib.pgm_stream.restype = C.c_void_p
     lib.pgm_launch_count.argtypes = [C.c_void_p]

@@ -24,6 +24,7 @@
 #include "pgm_signal.cuh"
 #include "pgm_sort.cuh"
 #include "pgm_text.cuh"
+#include "pgm_model.cuh"
 
 namespace {
 
@@ -60,6 +61,12 @@ struct pgm_ctx {
     size_t lb_used = 0, lb_words = 0;   // status words handed out / available in zbatch
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
     const uint32_t *gathered = nullptr;       // pgm_set_gathered
+    // model aggregation log (pgm_model_begin / pgm_model_finalize): one entry per batch
+    struct ModelBatch { long long *vals; unsigned long long *slot_off; std::vector<unsigned long long> h_slot_off; };
+    bool model_on = false;
+    std::vector<ModelBatch> model_log;
+    DBuf model_bad, model_grouped, model_off, model_dst, model_rows;
+    std::vector<pgm_model_row> h_model_rows;
     size_t text_written_cap = 0;              // capacity of `text` when pgm_emit formatted into it (0: it did not)
     uint32_t n_ranks = 1, rank = 0;
 
@@ -210,6 +217,9 @@ void pgm_destroy(pgm_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); }
+    c->model_log.clear();
+    for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
     DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->totals_next, &c->bucket_base, &c->sel_base,
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
@@ -729,6 +739,19 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
         CU(c, cudaMemcpyAsync(c->h_slot_toff.p, c->slot_toff.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_toff.p, c->ev_toff.p, (ne + 1) * 8, cudaMemcpyDeviceToHost, st));
     }
+    if (c->model_on && nsamp) {   // K7: this batch's selected samples, as the integers their "%.8f" text spells
+        pgm_ctx::ModelBatch mb;
+        mb.vals = nullptr; mb.slot_off = nullptr;
+        CU(c, cudaMalloc(&mb.vals, nsamp * 8));
+        CU(c, cudaMalloc(&mb.slot_off, (size_t)(NS + 1) * 8));
+        mb.h_slot_off.resize(NS + 1);
+        k_model_scale<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(P<double>(c->samples), &SCALARS(c)->n_sel_samples, mb.vals, P<uint32_t>(c->model_bad));
+        k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), P<unsigned long long>(c->sel_off), NS, mb.slot_off);
+        c->launches += 2;
+        CU(c, cudaGetLastError());
+        CU(c, cudaMemcpyAsync(mb.h_slot_off.data(), mb.slot_off, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
+        c->model_log.push_back(std::move(mb));
+    }
     CU(c, cudaStreamSynchronize(st));
     memset(out, 0, sizeof *out);
     out->n_slots = NS; out->n_reads = R;
@@ -765,6 +788,70 @@ int pgm_profile_read(pgm_ctx *c, float *ms, uint32_t *launches) {
         c->ev_pool.push_back(sp.b);
     }
     c->spans.clear();
+    return PGM_OK;
+}
+
+static void model_clear(pgm_ctx *c) {
+    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); }
+    c->model_log.clear();
+}
+
+int pgm_model_begin(pgm_ctx *c) {
+    if (!c) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    model_clear(c);
+    RET(ensure(c, c->model_bad, 4));
+    CU(c, cudaMemsetAsync(c->model_bad.p, 0, 4, c->stream));
+    c->model_on = true;
+    return PGM_OK;
+}
+
+int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **rows_out) {
+    if (!c || !rows_out) return PGM_ERR_ARG;
+    if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_finalize needs pgm_model_begin first");
+    static_assert(sizeof(ModelRowDev) == sizeof(pgm_model_row), "device and ABI rows must agree");
+    CU(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint32_t NS = c->opts.n_slots;
+    // where every batch's slot range goes in the grouped array: file order = batch order inside a slot
+    std::vector<unsigned long long> off(NS + 1, 0);
+    for (auto &mb : c->model_log)
+        for (uint32_t s = 0; s < NS; s++) off[s + 1] += mb.h_slot_off[s + 1] - mb.h_slot_off[s];
+    for (uint32_t s = 0; s < NS; s++) off[s + 1] += off[s];
+    const unsigned long long total = off[NS];
+    RET(ensure(c, c->model_off, (size_t)(NS + 1) * 8));
+    RET(ensure(c, c->model_rows, (size_t)NS * sizeof(ModelRowDev)));
+    CU(c, cudaMemcpyAsync(c->model_off.p, off.data(), (size_t)(NS + 1) * 8, cudaMemcpyHostToDevice, st));
+    const long long *grouped = nullptr;
+    std::vector<unsigned long long> dst;   // must outlive the copies below
+    if (c->model_log.size() == 1) grouped = c->model_log[0].vals;   // one batch: its order is the grouped order
+    else if (total) {
+        RET(ensure(c, c->model_grouped, (size_t)total * 8));
+        RET(ensure(c, c->model_dst, (size_t)NS * 8 * c->model_log.size()));
+        dst.assign((size_t)NS * c->model_log.size(), 0);
+        std::vector<unsigned long long> cur(off.begin(), off.end() - 1);
+        for (size_t bi = 0; bi < c->model_log.size(); bi++)
+            for (uint32_t s = 0; s < NS; s++) {
+                dst[bi * NS + s] = cur[s];
+                cur[s] += c->model_log[bi].h_slot_off[s + 1] - c->model_log[bi].h_slot_off[s];
+            }
+        CU(c, cudaMemcpyAsync(c->model_dst.p, dst.data(), dst.size() * 8, cudaMemcpyHostToDevice, st));
+        for (size_t bi = 0; bi < c->model_log.size(); bi++) {
+            k_model_group<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(c->model_log[bi].vals, c->model_log[bi].slot_off,
+                                                             P<unsigned long long>(c->model_dst) + bi * NS, NS, P<long long>(c->model_grouped));
+            c->launches++;
+        }
+        grouped = P<long long>(c->model_grouped);
+    }
+    k_model_rows<<<NS < (uint32_t)c->n_sm * 8 ? NS : (uint32_t)c->n_sm * 8, PGM_BLOCK, 0, st>>>(grouped, P<unsigned long long>(c->model_off), NS, stddev_limit,
+                                                                                              P<ModelRowDev>(c->model_rows));
+    c->launches++;
+    CU(c, cudaGetLastError());
+    c->h_model_rows.resize(NS);
+    CU(c, cudaMemcpyAsync(c->h_model_rows.data(), c->model_rows.p, (size_t)NS * sizeof(pgm_model_row), cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+    *rows_out = c->h_model_rows.data();
     return PGM_OK;
 }
 

@@ -116,6 +116,18 @@ class GmoveEngine:
         """Fused exchange: the all-gathered [n_ranks, n_slots] uint32 counts (device) and this rank."""
         self._chk(self.lib.pgm_set_gathered(self._ctx, C.c_void_p(all_counts_dev_ptr), n_ranks, rank))
 
+    def model_begin(self):
+        """Start logging the selected samples of every following batch for the model rows (K7)."""
+        self._chk(self.lib.pgm_model_begin(self._ctx))
+
+    def model_finalize(self, stddev_limit: float) -> np.ndarray:
+        """Per-k-mer (median, stddev, ...) over everything logged since model_begin (scripts/poregen.sh:54-85)."""
+        p = C.c_void_p()
+        self._chk(self.lib.pgm_model_finalize(self._ctx, float(stddev_limit), C.byref(p)))
+        n = self.n_slots
+        buf = (C.c_char * (n * 40)).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.dtype(capi.MODEL_ROW_DTYPE), count=n).copy()
+
     def profile_enable(self, on: bool = True):
         self._chk(self.lib.pgm_profile_enable(self._ctx, 1 if on else 0))
 

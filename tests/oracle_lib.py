@@ -54,7 +54,17 @@ def lib():
         _lib.oracle_mad.restype = C.c_double
         _lib.oracle_model_row.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         _lib.oracle_model_row.restype = C.c_int
+        _lib.oracle_model_row_text.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p, C.c_char_p]
+        _lib.oracle_model_row_text.restype = C.c_size_t
     return _lib
+
+
+def model_row_text(text: bytes, limit: float):
+    """scripts/poregen.sh:54-85 on the text of one dump file: (values used, median, stddev, '%.14Lg' strings)."""
+    med, sd = C.c_double(), C.c_double()
+    ms, ss = C.create_string_buffer(64), C.create_string_buffer(64)
+    n = lib().oracle_model_row_text(text, len(text), limit, C.byref(med), C.byref(sd), ms, ss)
+    return int(n), med.value, sd.value, ms.value.decode(), ss.value.decode()
 
 
 def oracle_run(opts: GmoveOptions, batch: ReadBatch, totals: np.ndarray | None = None) -> GmoveResult:

@@ -1,0 +1,88 @@
+"""K7 — per-k-mer model rows (reference scripts/poregen.sh:54-85) on the device against the script's
+arithmetic restated on the dump TEXT (oracle_model_row_text: strtold + long double, like GNU datamash).
+
+Parity of this row is UNPINNED (datamash is not installed, no reference test holds a model row), so the
+bar is: the median, an exact quantity, must agree digit for digit; the stddev within 1e-12 relative of the
+long-double evaluation."""
+import math
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from cases import _o
+from poregen_b200 import _capi as capi, synth
+from poregen_b200.gmove import GmoveEngine
+from poregen_b200.synth import SynthConfig
+
+pytestmark = pytest.mark.gpu
+
+
+def _slot_texts(res):
+    off = np.concatenate(([0], np.cumsum(res.slot_sel.astype(np.int64))))
+    soff = np.concatenate(([0], np.cumsum(res.ev_len.astype(np.int64))))
+    out = []
+    for s in range(res.slot_sel.size):
+        parts = []
+        for e in range(off[s], off[s + 1]):
+            parts.append(",".join("%.8f" % v for v in res.samples[soff[e]:soff[e + 1]]) + ";")
+        out.append("".join(parts).encode())
+    return out
+
+
+def _check(rows, texts, limit):
+    assert rows.size == len(texts)
+    for s, text in enumerate(texts):
+        n, med, sd, med_s, sd_s = ol.model_row_text(text, limit)
+        r = rows[s]
+        if n == 0:
+            assert r["flags"] & capi.PGM_MODEL_EMPTY and math.isnan(r["median"])
+            continue
+        assert int(r["n"]) == n
+        # the median is exact: median_num / 2e8, printed like datamash prints it
+        assert "%.14g" % (int(r["median_num"]) / 2e8) == med_s, (s, r, med_s)
+        assert r["median"] == med
+        if n < 2:
+            assert r["flags"] & capi.PGM_MODEL_NO_SD and math.isnan(r["stddev"])
+        else:
+            assert abs(r["stddev"] - sd) <= 1e-12 * abs(sd), (s, r["stddev"], sd)
+            assert bool(r["flags"] & capi.PGM_MODEL_CLAMPED) == (sd == limit and r["stddev"] == limit)
+
+
+@pytest.mark.parametrize("scaling,limit", [(0, 1e9), (1, 1e9), (1, 0.9)], ids=["pA", "medmad", "clamped"])
+def test_model_rows_one_batch(built, scaling, limit):
+    opts = _o(kmer_size=4, sample_limit=60, scaling=scaling)
+    batch = synth.make_batch(SynthConfig(n_reads=80, median_samples=4000, seed=301))
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        eng.model_begin()
+        eng.process(batch)
+        rows = eng.model_finalize(limit)
+    _check(rows, _slot_texts(ref), limit)
+
+
+def test_model_rows_accumulate_over_batches(built):
+    """The dump files grow over the record loop; so does the model log. Four batches, totals carried:
+    the rows must be those of the whole run."""
+    opts = _o(kmer_size=3, sample_limit=500, scaling=1)
+    batch = synth.make_batch(SynthConfig(n_reads=64, median_samples=3000, seed=302))
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        eng.model_begin()
+        for lo in range(0, 64, 16):
+            eng.process(batch.slice(lo, lo + 16))
+        rows = eng.model_finalize(1e9)
+    _check(rows, _slot_texts(ref), 1e9)
+
+
+def test_model_rows_few_values(built):
+    """k-mers with zero, one or two values: datamash prints nothing / a median and nan."""
+    opts = _o(kmer_size=6, sample_limit=1, scaling=0, min_dur=1, max_dur=2)
+    batch = synth.make_batch(SynthConfig(n_reads=6, median_samples=1500, seed=303))
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        eng.model_begin()
+        eng.process(batch)
+        rows = eng.model_finalize(1e9)
+    _check(rows, _slot_texts(ref), 1e9)
+    assert (rows["flags"] & capi.PGM_MODEL_EMPTY).any()
