@@ -317,6 +317,18 @@ def run_own_arm(args):
         dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
     ms_step = float(t_res.item()) / args.steps
 
+    # ---- K7 (model rows of the whole batch; scripts/poregen.sh:54-85), timed once around pgm_model_finalize
+    eng.model_begin()
+    eng.reset()
+    eng.upload(batch); eng.count(); eng.emit()
+    eng.download()
+    torch.cuda.synchronize()
+    tm0 = time.perf_counter()
+    rows = eng.model_finalize(1e300)
+    model_ms = (time.perf_counter() - tm0) * 1e3
+    model_info = {"ms": model_ms, "values": int(rows["n"].sum()), "rows": int(rows.size),
+                  "note": "pgm_model_finalize on this rank's C2 batch: median by int64 radix selection + exact 128-bit variance per k-mer, incl. the rows' download"}
+
     # ---- end to end: pinned host buffers in, the dump TEXT (what the reference fprintf's, formatted on the
     # device) out to host memory, every step. A second context with PGM_OUT_TEXT does this leg.
     import copy
@@ -425,7 +437,7 @@ def run_own_arm(args):
                              "ms_per_launch": dom_per_launch_ms},
                 "roofline_step": {"algorithmic_bytes": alg_step, "gbs": alg_step / (ms_step * 1e-3) / 1e9,
                                   "frac": alg_step / (ms_step * 1e-3) / 1e9 / peak},
-                "stages": stage_rows, "clocks": clocks}
+                "stages": stage_rows, "model_aggregation": model_info, "clocks": clocks}
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(args.cpu_reads)
         emit_line(line)

@@ -75,6 +75,8 @@ struct Opt {
     // extensions
     int gpus = 1, threads = 0;
     uint64_t batch_samples = 64ull << 20;
+    const char *model_out = nullptr;   // --model FILE: kmer<TAB>median<TAB>stddev (scripts/poregen.sh:54-85)
+    double stddev_limit = 1e300;
 };
 
 void print_help(FILE *fp, const Opt &o) {
@@ -105,6 +107,8 @@ void print_help(FILE *fp, const Opt &o) {
     fprintf(fp, "   --gpus INT                 GPUs to spread every batch over [%d]\n", o.gpus);
     fprintf(fp, "   --threads INT              host threads decoding SLOW5 records [all cores]\n");
     fprintf(fp, "   --batch-samples INT        raw samples per device batch [%" PRIu64 "]\n", o.batch_samples);
+    fprintf(fp, "   --model FILE               also write kmer<TAB>median<TAB>stddev per dumped k-mer (calculate_mean_stddev_all of scripts/poregen.sh)\n");
+    fprintf(fp, "   --stddev_limit FLOAT       upper clamp of the stddev column [none]\n");
 }
 
 // 0 created / exists and empty, -1 exists and not empty, -2 cannot create (reference gmove.cpp:126-140)
@@ -558,7 +562,7 @@ void process_batch(Run &R, Batch &b) {
 
 enum { LO_SCALING = 3, LO_MARGIN, LO_SAMPLE_LIMIT, LO_FILE_LIMIT, LO_KMER_FILE, LO_INDEX_START, LO_INDEX_END, LO_FASTQ, LO_D,
        LO_MAX_DUR, LO_MIN_DUR, LO_PA_MIN, LO_PA_MAX, LO_PICK_MARGIN, LO_RNA, LO_VERBOSE, LO_HELP, LO_VERSION, LO_DEBUG_BREAK,
-       LO_GPUS, LO_THREADS, LO_BATCH };
+       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT };
 
 const struct option long_options[] = {
     {"kmer_size", required_argument, 0, 'k'},          // 0
@@ -586,6 +590,8 @@ const struct option long_options[] = {
     {"gpus", required_argument, 0, 0},                 // 22 (B200 build)
     {"threads", required_argument, 0, 0},              // 23
     {"batch-samples", required_argument, 0, 0},        // 24
+    {"model", required_argument, 0, 0},                // 25
+    {"stddev_limit", required_argument, 0, 0},         // 26
     {0, 0, 0, 0}};
 
 }  // namespace
@@ -641,6 +647,8 @@ int gmove(int argc, char *argv[]) {
                 case LO_GPUS: opt.gpus = atoi(optarg); break;
                 case LO_THREADS: opt.threads = atoi(optarg); break;
                 case LO_BATCH: opt.batch_samples = strtoull(optarg, nullptr, 10); break;
+                case LO_MODEL: opt.model_out = optarg; break;
+                case LO_SDLIMIT: opt.stddev_limit = atof(optarg); break;
                 default: break;
             }
         }
@@ -753,6 +761,12 @@ int gmove(int argc, char *argv[]) {
     R.gpus.resize(opt.gpus);
     for (int g = 0; g < opt.gpus; g++)
         if (pgm_create(&po, g, nullptr, &R.gpus[g].ctx) != PGM_OK) DIE("%s", pgm_last_error(nullptr));
+    if (opt.model_out) {
+        // a k-mer's values would be spread over the devices: the segmented median needs them in one place
+        if (opt.gpus != 1) DIE("%s", "--model needs --gpus 1");
+        if (opt.delimit_files) DIE("%s", "--model cannot be combined with -d (the script splits on ';' and ',' only)");
+        if (pgm_model_begin(R.gpus[0].ctx) != PGM_OK) DIE("%s", pgm_last_error(R.gpus[0].ctx));
+    }
 
     // record loop
     FILE *fp = fopen(move_table, "r");
@@ -789,6 +803,20 @@ int gmove(int argc, char *argv[]) {
     if (!ff) { fprintf(stderr, "Error in opening %s\n", freq.c_str()); exit(EXIT_FAILURE); }
     for (uint32_t s = 0; s < R.n_slots; s++) fprintf(ff, "%s\t%" PRIu64 "\n", kmers[opt.index_start - 1 + s].c_str(), (uint64_t)R.totals[s]);
     fclose(ff);
+    if (opt.model_out) {
+        const pgm_model_row *rows = nullptr;
+        if (pgm_model_finalize(R.gpus[0].ctx, opt.stddev_limit, &rows) != PGM_OK) DIE("%s", pgm_last_error(R.gpus[0].ctx));
+        FILE *fm = fopen(opt.model_out, "w");
+        if (!fm) { fprintf(stderr, "Error in opening %s\n", opt.model_out); exit(EXIT_FAILURE); }
+        for (uint32_t s = 0; s < R.n_slots; s++) {
+            // echo -e "$(basename "$file")\t$mean\t$stddev" with datamash's "%.14Lg" numbers (poregen.sh:82)
+            const char *name = kmers[opt.index_start - 1 + s].c_str();
+            if (rows[s].flags & (PGM_MODEL_EMPTY | PGM_MODEL_RANGE)) fprintf(fm, "%s\t\t\n", name);
+            else if (rows[s].flags & PGM_MODEL_NO_SD) fprintf(fm, "%s\t%.14g\tnan\n", name, (double)rows[s].median_num / 2e8);
+            else fprintf(fm, "%s\t%.14g\t%.14g\n", name, (double)rows[s].median_num / 2e8, rows[s].stddev);
+        }
+        fclose(fm);
+    }
     for (Gpu &g : R.gpus) pgm_destroy(g.ctx);
     slow5_idx_unload(R.sp);
     slow5_close(R.sp);

@@ -109,3 +109,29 @@ def test_cli_usage_errors(cli):
     assert subprocess.run([CLI, "gmove", "-h"], capture_output=True).returncode == 1        # -h is not in the optstring (gmove.cpp:217)
     p = subprocess.run([CLI, "gmove", "--version"], capture_output=True)
     assert p.returncode == 0 and p.stdout.startswith(b"gmove ")
+
+
+def test_cli_model_rows(cli):
+    """--model FILE: the rows calculate_mean_stddev_all (reference scripts/poregen.sh:54-85) would compute from
+    the dump files the same run wrote, several device batches; checked against the script's arithmetic
+    restated on those files' text (oracle_model_row_text; parity of this row is unpinned)."""
+    opts = _o(kmer_size=3, sample_limit=300, scaling=1)
+    cfg = SynthConfig(n_reads=50, median_samples=3000, seed=77)
+    with tempfile.TemporaryDirectory(prefix="pgm_cli_model_") as d:
+        fl, kf = _make_files(cfg, opts, d)
+        model = os.path.join(d, "model.tsv")
+        files = _run_cli(opts, d, fl, kf, extra=["--model", model, "--stddev_limit", "1.05", "--batch-samples", "40000"])
+        lines = open(model).read().splitlines()
+    names = sorted(n for n in files if n != "freq.txt")
+    assert [ln.split("\t")[0] for ln in lines] == names
+    for ln in lines:
+        name, med_s, sd_s = ln.split("\t")
+        n, med, sd, ms, ss = ol.model_row_text(files[name], 1.05)
+        if n == 0:
+            assert med_s == "" and sd_s == ""
+            continue
+        assert med_s == ms
+        if n == 1:
+            assert sd_s == "nan"
+        else:
+            assert abs(float(sd_s) - sd) <= 1e-12 * sd
