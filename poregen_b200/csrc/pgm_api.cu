@@ -37,7 +37,8 @@ struct DBuf {
 
 
 typedef BatchScalars Scalars;  // device -> host summary of one batch (pgm_emit.cuh)
-#define MISC_WORDS 64           // word 0 = k_stats_wide queue, word 1 = k_decode record ticket, words 8.. = look-back scan tickets
+#define MISC_WORDS 160          // word 0 = k_stats_wide queue, 1 = k_decode record ticket, 2 = k_stats ticket, 3 = k_read_prep CTAs done,
+                                // 8..63 = look-back scan tickets, 96..159 = record length classes (k_read_prep)
 
 enum State { ST_IDLE = 0, ST_LOADED, ST_COUNTED, ST_EMITTED };
 
@@ -86,7 +87,7 @@ struct pgm_ctx {
     DBuf zbatch;                       // zeroed every batch: scalars | misc words | scan status | read_has_sel[R] | tile histogram
     size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
     uint32_t sort_ntiles = 0;
-    DBuf sel_start, sel_len, sel_read, sel_src, sel_off, samples;
+    DBuf sel_start, sel_len, sel_read, sel_src, sel_off, samples, rec_packed, rec_order;
     DBuf ev_tlen, ev_toff, text, slot_toff;   // PGM_OUT_TEXT
     DBuf hp_prior, hp_consumed;               // pgm_set_prior_host
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
@@ -224,7 +225,7 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
+                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff};
     for (DBuf *b : host) release_host(*b);
@@ -362,6 +363,8 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->cal, (size_t)R * sizeof(ReadCal)));
     RET(ensure(c, c->rflags, R));
     RET(ensure(c, c->n_pass, (size_t)R * 4));
+    RET(ensure(c, c->rec_packed, (size_t)R * 4 + 4));
+    RET(ensure(c, c->rec_order, (size_t)R * 4 + 4));
     RET(ensure(c, c->ev_base, (size_t)(R + 1) * 4));
     const size_t e4 = (size_t)cap * 4;
     DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read};
@@ -471,8 +474,11 @@ int pgm_count(pgm_ctx *c) {
     if (R) {
         {
             StageTimer t(c, PGM_STAGE_PREP);
-            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &SCALARS(c)->err_flag);
-            c->launches++;
+            PrepOrder po;
+            po.cls_count = MISC(c) + 96; po.packed = P<uint32_t>(c->rec_packed); po.order = P<uint32_t>(c->rec_order);
+            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &SCALARS(c)->err_flag, po);
+            k_order<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(R, po);
+            c->launches += 2;
             if (c->db.mode == PGM_MODE_MOVES_I8) { k_oor_check<<<R, PGM_BLOCK, 0, st>>>(c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags)); c->launches++; }
         }
         {
@@ -489,7 +495,7 @@ int pgm_count(pgm_ctx *c) {
             io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end); io.sc_key = P<uint32_t>(c->sc_key);
             io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
             io.n_pass = P<uint32_t>(c->n_pass);
-            io.ticket = MISC(c) + 1;
+            io.ticket = MISC(c) + 1; io.order = P<uint32_t>(c->rec_order);
             io.hist = HIST(c); io.ntiles_cap = c->sort_ntiles; io.hist_mask = (1u << per) - 1;
             const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
             k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
@@ -654,7 +660,7 @@ int pgm_emit(pgm_ctx *c) {
                 c->launches++;
             }
             StatsIO si;
-            si.rflags = P<uint8_t>(c->rflags); si.read_has_sel = HAS_SEL(c); si.cal = P<ReadCal>(c->cal); si.ticket = MISC(c) + 2;
+            si.rflags = P<uint8_t>(c->rflags); si.read_has_sel = HAS_SEL(c); si.cal = P<ReadCal>(c->cal); si.ticket = MISC(c) + 2; si.order = P<uint32_t>(c->rec_order);
             const uint32_t sgrid = (uint32_t)std::min<uint64_t>(cdiv(R, STATS_WARPS), (uint64_t)c->n_sm * 3);
             k_stats<<<sgrid, STATS_WARPS * 32, STATS_DYN_SMEM, st>>>(d, c->db, si);
             c->launches++;

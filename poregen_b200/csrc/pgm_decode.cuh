@@ -36,6 +36,7 @@ struct DecodeIO {
     uint8_t *sc_code;              // ss: 2-bit base code per event
     int32_t *sc_indel;             // ss: indel positions
     uint32_t *ticket;          // record hand-out
+    const uint32_t *order;     // [R] ticket -> record, longest records first (k_read_prep)
     // tile histogram of the first radix pass: hist[digit * ntiles_cap + tile]
     uint32_t *hist;
     uint32_t ntiles_cap, hist_mask;
@@ -404,7 +405,10 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, Dec
     uint32_t exam = 0;
     for (;;) {
         uint32_t r = 0;
-        if (lane == 0) r = atomicAdd(io.ticket, 1u);
+        if (lane == 0) {
+            r = atomicAdd(io.ticket, 1u);
+            r = (r < b.n_reads) ? io.order[r] : 0xffffffffu;
+        }
         r = __shfl_sync(0xffffffffu, r, 0);
         if (r >= b.n_reads) break;
         uint32_t n_pass = 0;

@@ -8,25 +8,63 @@
 // sets the record-level skip flags that do not need the signal:
 //   host PGM_READ_SKIP (ss: fetched slice < k, gmove.cpp:806-808), fastq_len < 10 in the move-table
 //   paths (gmove.cpp:616-619, 1178-1181), trim >= raw_len (assert gmove.cpp:590, 1147).
-__global__ void __launch_bounds__(PGM_BLOCK) k_read_prep(DevOpts o, DevBatch b, ReadCal *cal, uint8_t *rflags, uint32_t *err_flag) {
+// It also lays down the order in which the one-warp-per-record kernels (k_decode, k_stats) take the records:
+// longest first, so that the last warps to finish hold short records (the kernels' run time is the slowest warp's,
+// and a warp gets only two or three records). Records are counted into 64 length classes with an atomic rank
+// inside the class; k_order turns the class counts into offsets and writes order[].
+#define PREP_CLASSES 64
+struct PrepOrder {
+    uint32_t *cls_count;   // [PREP_CLASSES], zeroed per batch
+    uint32_t *packed;      // [R] class << 26 | rank in class
+    uint32_t *order;       // [R] out
+};
+
+__global__ void __launch_bounds__(PGM_BLOCK) k_read_prep(DevOpts o, DevBatch b, ReadCal *cal, uint8_t *rflags, uint32_t *err_flag, PrepOrder po) {
     const uint32_t r = blockIdx.x * PGM_BLOCK + threadIdx.x;
-    if (r >= b.n_reads) return;
-    const pgm_read rd = b.reads[r];
-    uint32_t f = 0;
-    if (rd.raw_off + rd.raw_len > b.n_raw || rd.align_off + rd.align_len > b.n_align || rd.seq_off + rd.seq_len > b.n_bases) {
-        atomicOr(err_flag, 1u);
-        f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
+    if (r < b.n_reads) {
+        const pgm_read rd = b.reads[r];
+        uint32_t f = 0;
+        if (rd.raw_off + rd.raw_len > b.n_raw || rd.align_off + rd.align_len > b.n_align || rd.seq_off + rd.seq_len > b.n_bases) {
+            atomicOr(err_flag, 1u);
+            f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
+        }
+        if (rd.flags & PGM_READ_SKIP) f |= PGM_RF_SKIPPED;
+        const double scale = __ddiv_rn(rd.range, rd.digitisation);
+        if (!isfinite(scale) || !isfinite(rd.offset)) f |= PGM_RF_BAD_CALIB | PGM_RF_SKIPPED;
+        if (rd.trim >= rd.raw_len) f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
+        if (b.mode != PGM_MODE_SS && rd.fastq_len < 10) f |= PGM_RF_SKIPPED;
+        ReadCal c;
+        c.scale = scale; c.med = 0.0; c.mad = 1.0; c.clo = 0; c.chi = -1;
+        if (!(f & PGM_RF_BAD_CALIB)) pgm_code_interval(rd.offset, scale, o.pa_min, o.pa_max, &c.clo, &c.chi);
+        cal[r] = c;
+        rflags[r] = (uint8_t)f;
+        // class 0 = longest (512-sample steps, everything from 32256 samples up together); skipped records last
+        const uint32_t cls = f ? PREP_CLASSES - 1 : (PREP_CLASSES - 1) - min((uint32_t)PREP_CLASSES - 1, rd.raw_len >> 9);
+        po.packed[r] = (cls << 26) | atomicAdd(&po.cls_count[cls], 1u);
     }
-    if (rd.flags & PGM_READ_SKIP) f |= PGM_RF_SKIPPED;
-    const double scale = __ddiv_rn(rd.range, rd.digitisation);
-    if (!isfinite(scale) || !isfinite(rd.offset)) f |= PGM_RF_BAD_CALIB | PGM_RF_SKIPPED;
-    if (rd.trim >= rd.raw_len) f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
-    if (b.mode != PGM_MODE_SS && rd.fastq_len < 10) f |= PGM_RF_SKIPPED;
-    ReadCal c;
-    c.scale = scale; c.med = 0.0; c.mad = 1.0; c.clo = 0; c.chi = -1;
-    if (!(f & PGM_RF_BAD_CALIB)) pgm_code_interval(rd.offset, scale, o.pa_min, o.pa_max, &c.clo, &c.chi);
-    cal[r] = c;
-    rflags[r] = (uint8_t)f;
+}
+
+// k_order: class counts -> offsets (every CTA redoes the 64-element scan), then each record goes to its place.
+__global__ void __launch_bounds__(PGM_BLOCK) k_order(uint32_t n_reads, PrepOrder po) {
+    __shared__ uint32_t sm_off[PREP_CLASSES];
+    if (threadIdx.x < 32) {
+        const uint32_t lane = threadIdx.x;
+        const uint32_t c0 = po.cls_count[lane], c1 = po.cls_count[lane + 32];
+        uint32_t i0 = c0, i1 = c1;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t0 = __shfl_up_sync(0xffffffffu, i0, d), t1 = __shfl_up_sync(0xffffffffu, i1, d);
+            if (lane >= (uint32_t)d) { i0 += t0; i1 += t1; }
+        }
+        const uint32_t half = __shfl_sync(0xffffffffu, i0, 31);
+        sm_off[lane] = i0 - c0;
+        sm_off[lane + 32] = half + i1 - c1;
+    }
+    __syncthreads();
+    const uint32_t i = blockIdx.x * PGM_BLOCK + threadIdx.x;
+    if (i < n_reads) {
+        const uint32_t p = po.packed[i];
+        po.order[sm_off[p >> 26] + (p & 0x03ffffffu)] = i;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

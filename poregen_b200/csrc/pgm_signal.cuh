@@ -299,6 +299,7 @@ struct StatsIO {
     const uint8_t *rflags, *read_has_sel;
     ReadCal *cal;
     uint32_t *ticket;    // zeroed per batch
+    const uint32_t *order;   // [R] ticket -> record, longest records first (k_read_prep)
 };
 
 #define STATS_WARPS 8
@@ -322,7 +323,10 @@ __global__ void __launch_bounds__(STATS_WARPS * 32) k_stats(DevOpts o, DevBatch 
     const uint32_t sbase = smem_u32(H);
     for (;;) {
         uint32_t r = 0;
-        if (lane == 0) r = atomicAdd(io.ticket, 1u);
+        if (lane == 0) {
+            r = atomicAdd(io.ticket, 1u);
+            r = (r < b.n_reads) ? io.order[r] : 0xffffffffu;
+        }
         r = __shfl_sync(PGM_FULL, r, 0);
         if (r >= b.n_reads) break;
         const pgm_read *rp = b.reads + r;
