@@ -6,6 +6,7 @@
 #   oracle/_ref/libslow5.a      slow5lib + streamvbyte (reference submodule, C99, -O2 as its Makefile)
 #   oracle/_ref/poregen_ref     src/gmove.cpp + poregen.cpp + thread.c, -O2
 #   oracle/_ref/poregen_ref_g   same, flags as shipped by the reference Makefile:4 (-g, no -O)
+#   oracle/_ref/reform_ref      src/reform.cpp (text SAM input only)
 # htslib is not vendored by the reference (Makefile:69-81 downloads 1.17): the
 # stand-in headers in oracle/shim/htslib are used instead (parsing only).
 # No -march=native / -ffast-math: keeps fp64 results FMA-free (x86-64 baseline).
@@ -37,7 +38,17 @@ build_one() { # $1 = output name, rest = CFLAGS
     $CXX "$@" "$OUT/obj/${name}_main.o" "$OUT/obj/${name}_gmove.o" "$OUT/obj/${name}_poregen.o" "$OUT/obj/${name}_thread.o" \
         "$OUT/libslow5.a" -lz -lm -lpthread -o "$OUT/$name"
 }
+# `reform` (src/reform.cpp) against the same stand-in headers: text SAM only (the stand-in cannot open BAM).
+cat > "$OUT/obj/reform_main.cpp" <<'EOM'
+int reform(int argc, char *argv[]);
+int main(int argc, char *argv[]) { return reform(argc - 1, argv + 1); }   /* reform_ref reform [options] file, like main.c */
+EOM
+for f in reform.cpp poregen.cpp thread.c; do
+    $CXX -x c++ -std=c++11 -g -O2 -w -I "$S5/include" -I "$HERE/shim" -c "$REF/src/$f" -o "$OUT/obj/reform_${f%.*}.o"
+done
+$CXX -g -O2 "$OUT/obj/reform_main.cpp" "$OUT/obj/reform_reform.o" "$OUT/obj/reform_poregen.o" "$OUT/obj/reform_thread.o" "$OUT/libslow5.a" \
+    -lz -lm -lpthread -o "$OUT/reform_ref"
 build_one poregen_ref -g -O2
 build_one poregen_ref_g -g
 rm -rf "$OUT/obj"
-echo "build_ref: built $OUT/poregen_ref $OUT/poregen_ref_g $OUT/libslow5.a"
+echo "build_ref: built $OUT/poregen_ref $OUT/poregen_ref_g $OUT/reform_ref $OUT/libslow5.a"

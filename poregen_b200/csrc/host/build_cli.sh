@@ -12,7 +12,7 @@ OUT="$PKG/bin/poregen"
 if [ ! -d "$SLOW5LIB/src" ]; then
     echo "build_cli: $SLOW5LIB not present; keeping prebuilt $OUT (if any)"; exit 0
 fi
-if [ -x "$OUT" ] && [ "$OUT" -nt "$HERE/gmove_cli.cpp" ] && [ "$OUT" -nt "$PKG/../include/pgm_gmove.h" ] && [ "$OUT" -nt "$PKG/libpgm_gmove.so" ]; then
+if [ -x "$OUT" ] && [ "$OUT" -nt "$HERE/gmove_cli.cpp" ] && [ "$OUT" -nt "$HERE/bam_reader.hpp" ] && [ "$OUT" -nt "$HERE/reform.inc" ] && [ "$OUT" -nt "$PKG/../include/pgm_gmove.h" ] && [ "$OUT" -nt "$PKG/libpgm_gmove.so" ]; then
     exit 0
 fi
 CC=${CC:-gcc}; CXX=${CXX:-g++}

@@ -33,6 +33,7 @@
 #include <slow5/slow5.h>
 
 #include "../../../include/pgm_gmove.h"
+#include "bam_reader.hpp"
 
 #define GMOVE_VERSION "0.1.0"   // reference src/poregen.h POREGEN_VERSION
 
@@ -318,6 +319,26 @@ bool parse_sam(char *line, Rec &r) {
     r.fastq_len = (int32_t)r.bases.size();
     return true;
 }
+
+// The same record from a BAM file (bam_reader.hpp), with the reference's checks (gmove.cpp:1092-1127).
+void bam_to_rec(const BamRecord &b, Rec &r) {
+    r.read_id = b.name;
+    if (!b.has_ns) DIE("tag 'ns' is not found. Please check your SAM/BAM file: ");
+    if (!b.has_ts) DIE("tag 'ts' is not found. Please check your SAM/BAM file: ");
+    if (!b.has_mv) DIE("NULL returned for tag mv: ");
+    if (b.mv_subtype != 'c') DIE("tag 'mv' specification is incorrect");
+    if (b.mv.empty()) DIE("mv array length is 0: ");
+    r.signal_len = (uint64_t)b.ns;
+    r.trim = (uint32_t)b.ts;
+    r.check_len = true;
+    r.stride = (uint32_t)b.mv[0];
+    r.align.assign(b.mv.begin() + 1, b.mv.end());
+    r.bases.clear();
+    for (char c : b.seq) r.bases.push_back((c == 'A' || c == 'C' || c == 'G' || c == 'T') ? c : 'N');   // "NACNGNNNT" of gmove.cpp:1128-1134
+    r.fastq_len = (int32_t)r.bases.size();
+}
+
+#include "reform.inc"
 
 // ---------------------------------------------------------------------------------------------------
 // Pinned, growable array for batch data.
@@ -736,9 +757,7 @@ int gmove(int argc, char *argv[]) {
         if (!fastq_file) { fprintf(stderr, ".paf input requires an additional .fastq file\n"); exit(EXIT_FAILURE); }
         if (!fai.load(fastq_file)) { fprintf(stderr, "Error in opening file %s\n", fastq_file); exit(EXIT_FAILURE); }
         R.mode = PGM_MODE_SS;
-    } else if (ext == ".bam") {
-        DIE("BAM (BGZF) input is not readable by this build: convert with `samtools view -h` and pass the .sam");
-    } else if (ext == ".sam") R.mode = PGM_MODE_MOVES_I8;
+    } else if (ext == ".bam" || ext == ".sam") R.mode = PGM_MODE_MOVES_I8;   // gmove.cpp:515-520: both go through the SAM/BAM loop
     else R.mode = PGM_MODE_MOVES_CHAR;
 
     // device contexts
@@ -771,17 +790,29 @@ int gmove(int argc, char *argv[]) {
     // record loop
     FILE *fp = fopen(move_table, "r");
     if (!fp) { fprintf(stderr, "Error in opening file %s\n", move_table); exit(EXIT_FAILURE); }
+    BamReader bam;
+    const bool is_bam = R.mode == PGM_MODE_MOVES_I8 && BamReader::looks_like_bam(move_table);
+    if (is_bam && !bam.open(move_table)) DIE("%s: %s", move_table, bam.err().c_str());
+    BamRecord brec;
     Batch batch;
     char *line = nullptr;
     size_t cap = 0;
     uint64_t est = 0, progress = 0;
     const uint64_t max_records = 1u << 20;
-    while (getline(&line, &cap, fp) != -1) {
+    for (;;) {
         Rec r;
         bool have = true;
-        if (R.mode == PGM_MODE_SS) parse_paf(line, r, fai, opt);
-        else if (R.mode == PGM_MODE_MOVES_I8) have = parse_sam(line, r);
-        else if (!parse_tsv(line, r)) DIE("move table line with fewer than 7 columns");
+        if (is_bam) {
+            const int rc = bam.next(brec);
+            if (rc < 0) DIE("%s: %s", move_table, bam.err().c_str());
+            if (rc == 0) break;
+            bam_to_rec(brec, r);
+        } else {
+            if (getline(&line, &cap, fp) == -1) break;
+            if (R.mode == PGM_MODE_SS) parse_paf(line, r, fai, opt);
+            else if (R.mode == PGM_MODE_MOVES_I8) have = parse_sam(line, r);
+            else if (!parse_tsv(line, r)) DIE("move table line with fewer than 7 columns");
+        }
         if (!have) continue;
         est += r.check_len ? r.signal_len : (uint64_t)r.align.size() * 4;   // PAF: the signal length is only known after slow5_get
         batch.recs.push_back(std::move(r));
@@ -832,9 +863,15 @@ extern "C" int pgm_gmove_main(int argc, char **argv) { return gmove(argc, argv);
 // poregen's dispatcher (reference src/main.c:64-103), gmove only.
 int main(int argc, char *argv[]) {
     const double t0 = realtime();
-    if (argc < 2 || strcmp(argv[1], "gmove") != 0) {
-        fprintf(stderr, "Usage: poregen <command> [options]\n\ncommand:\n         gmove     B200 build of `poregen gmove`\n");
+    const bool is_gmove = argc >= 2 && strcmp(argv[1], "gmove") == 0, is_reform = argc >= 2 && strcmp(argv[1], "reform") == 0;
+    if (!is_gmove && !is_reform) {
+        fprintf(stderr, "Usage: poregen <command> [options]\n\ncommand:\n         gmove     B200 build of `poregen gmove`\n"
+                        "         reform    move table (SAM/BAM) -> per-k-mer TSV or PAF with ss:Z\n");
         return (argc >= 2 && (strcmp(argv[1], "--help") == 0 || strcmp(argv[1], "-h") == 0)) ? 0 : 1;
+    }
+    if (is_reform) {
+        const int ret = reform(argc - 1, argv + 1);
+        return ret;
     }
     const int ret = gmove(argc - 1, argv + 1);
     fprintf(stderr, "\n[%s] Version: %s (B200)\n", __func__, GMOVE_VERSION);

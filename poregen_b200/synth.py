@@ -312,3 +312,46 @@ def write_blow5(batch: ReadBatch, path: str) -> None:
             f.write(fixed)
             f.write(batch.raw[int(r["raw_off"]):int(r["raw_off"]) + n].tobytes())
         f.write(b"5WOLB")
+
+
+def write_bam(batch: ReadBatch, path: str, block: int = 3000):
+    """The SAM records of write_alignment (PGM_MODE_MOVES_I8) as a BAM file: BGZF members of at most `block`
+    uncompressed bytes (small on purpose: records straddle members), unmapped reads with SEQ and the tags
+    mv:B:c, ns:i, ts:i; ns/ts are stored in the smallest integer type like htslib does. Test helper."""
+    import struct
+    import zlib
+    assert batch.mode == capi.PGM_MODE_MOVES_I8
+    codes = {c: i for i, c in enumerate("=ACMGRSVTWYHKDBN")}
+
+    def aux_int(tag, v):
+        if 0 <= v < 256:
+            return tag + b"C" + struct.pack("<B", v)
+        if 0 <= v < 65536:
+            return tag + b"S" + struct.pack("<H", v)
+        return tag + b"I" + struct.pack("<I", v)
+
+    text = b"@HD\tVN:1.6\tSO:unknown\n@PG\tID:synth\tPN:synth\n"
+    raw = bytearray(b"BAM\x01" + struct.pack("<i", len(text)) + text + struct.pack("<i", 0))
+    for i, rid in enumerate(batch.read_ids):
+        r = batch.reads[i]
+        seq = _seq(batch, i)
+        name = rid.encode() + b"\x00"
+        packed = bytearray((len(seq) + 1) // 2)
+        for j, ch in enumerate(seq):
+            packed[j >> 1] |= codes.get(ch, 15) << (4 if (j & 1) == 0 else 0)
+        mv = np.concatenate(([int(r["stride"])], _align(batch, i).astype(np.int8))).astype(np.int8)
+        aux = b"mvBc" + struct.pack("<I", mv.size) + mv.tobytes() + aux_int(b"ns", int(r["raw_len"])) + aux_int(b"ts", int(r["trim"]))
+        body = struct.pack("<iiBBHHHIiii", -1, -1, len(name), 0, 4680, 0, 4, len(seq), -1, -1, 0) + name + bytes(packed) + b"\xff" * len(seq) + aux
+        raw += struct.pack("<i", len(body)) + body
+
+    def member(data: bytes) -> bytes:
+        co = zlib.compressobj(6, zlib.DEFLATED, -15)
+        comp = co.compress(data) + co.flush()
+        bsize = 12 + 6 + len(comp) + 8
+        return (b"\x1f\x8b\x08\x04\x00\x00\x00\x00\x00\xff" + struct.pack("<H", 6) + b"BC" + struct.pack("<HH", 2, bsize - 1) + comp +
+                struct.pack("<II", zlib.crc32(data) & 0xffffffff, len(data)))
+
+    with open(path, "wb") as f:
+        for o in range(0, len(raw), block):
+            f.write(member(bytes(raw[o:o + block])))
+        f.write(member(b""))        # the end-of-file marker block

@@ -135,3 +135,18 @@ def test_cli_model_rows(cli):
             assert sd_s == "nan"
         else:
             assert abs(float(sd_s) - sd) <= 1e-12 * sd
+
+
+def test_cli_reads_bam(cli):
+    """guppy/dorado hand over BAM: the same records as BAM (BGZF, records straddling members) must give the
+    files the text SAM gives, which are pinned to the reference by the digests above (the reference's own
+    BAM case, test_gmove.sh 1.4/2.4, needs htslib)."""
+    label, cfg, opts = next(c for c in parity_cases() if c[0] == "sam_k5_sc1")
+    with tempfile.TemporaryDirectory(prefix="pgm_cli_bam_") as d:
+        fl, kf = _make_files(cfg, opts, d)
+        bam = os.path.join(d, "moves.bam")
+        synth.write_bam(synth.make_batch(cfg), bam, block=2000)
+        sam_files = _run_cli(opts, d, fl, kf, outname="o_sam")
+        bam_files = _run_cli(opts, d, dict(fl, align=bam), kf, outname="o_bam")
+    assert bam_files == sam_files
+    assert_matches_golden(load_golden()[label], digest(bam_files), label)
