@@ -149,4 +149,4 @@ def test_cli_reads_bam(cli):
         sam_files = _run_cli(opts, d, fl, kf, outname="o_sam")
         bam_files = _run_cli(opts, d, dict(fl, align=bam), kf, outname="o_bam")
     assert bam_files == sam_files
-    assert_matches_golden(load_golden()[label], digest(bam_files), label)
+    assert_matches_golden(digest(bam_files), load_golden()["synthetic"][label], label)
