@@ -362,7 +362,7 @@ def run_own_arm(args):
     import copy
     import ctypes as C
     topts = copy.copy(opts)
-    topts.output = capi.PGM_OUT_TEXT
+    topts.output = capi.PGM_OUT_TEXT_ONLY   # what the command line uses: the text, per-slot offsets and counts
     eng.close()
 
     # Batches in flight: while one batch's text travels device -> host, the next one's inputs travel host -> device
@@ -419,7 +419,7 @@ def run_own_arm(args):
     e2e_s = float(t_e2e.item())
     h2d = int(batch.raw.nbytes + batch.align.nbytes + batch.bases.nbytes + batch.reads.nbytes)
     text_bytes = int(C.cast(r.slot_text_off, C.POINTER(C.c_uint64))[NS])
-    d2h = int(text_bytes + r.n_sel_events * 20 + NS * 16 + batch.n_reads + 48)
+    d2h = int(text_bytes + NS * 16 + batch.n_reads + 48)
     examined = int(r.n_events_examined)
 
     tot = torch.tensor([n_samples, examined, int(r.n_sel_events), int(r.n_sel_samples)], dtype=torch.float64, device=f"cuda:{local}")
@@ -456,7 +456,7 @@ def run_own_arm(args):
                 "events_selected_per_step": tot_sel_ev, "samples_selected_per_step": tot_sel_samp,
                 "e2e": {"value": tot_samples / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "events_per_sec": tot_events / e2e_s,
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "output": "dump text (%.8f, formatted on the device), per-event index, per-k-mer counts",
+                        "output": "dump text (%.8f, formatted on the device), per-k-mer text offsets and counts, per-record flags",
                         "batches_in_flight": depth, "host_binding": numa},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -62,6 +62,8 @@ extern "C" {
 #define PGM_OUT_F64 0  /* selected samples as IEEE doubles (bit-exact with the reference vector) */
 #define PGM_OUT_TEXT 1 /* the exact "%.8f," / "%.8f;" text of gmove.cpp:674-678, formatted on the
                           device, INSTEAD of the doubles (pgm_result.samples is NULL)             */
+#define PGM_OUT_TEXT_ONLY 2 /* PGM_OUT_TEXT without the per-event arrays on the host (ev_len, ev_read, ev_start,
+                               ev_text_off stay NULL): all a writer needs unless -d asks for record delimiters */
 
 /* Mirrors the fields of the reference's opt_t that the gmove path reads
  * (src/poregen.h:48-79, defaults src/poregen.cpp:209-237) after gmove()'s own option handling

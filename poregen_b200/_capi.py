@@ -16,7 +16,7 @@ PGM_OK, PGM_ERR_ARG, PGM_ERR_CUDA, PGM_ERR_NOMEM, PGM_ERR_INPUT, PGM_ERR_STATE =
 PGM_MODE_MOVES_CHAR, PGM_MODE_SS, PGM_MODE_MOVES_I8 = 0, 1, 2
 PGM_READ_RNA, PGM_READ_SKIP = 1, 2
 PGM_RF_SKIPPED, PGM_RF_BAD_ALIGN, PGM_RF_BAD_CALIB = 1, 2, 4
-PGM_OUT_F64, PGM_OUT_TEXT = 0, 1
+PGM_OUT_F64, PGM_OUT_TEXT, PGM_OUT_TEXT_ONLY = 0, 1, 2
 PGM_ABI_VERSION = 2
 
 

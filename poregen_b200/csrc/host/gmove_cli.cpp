@@ -769,7 +769,7 @@ int gmove(int argc, char *argv[]) {
     po.kmer_size = opt.kmer_size; po.sig_move_offset = opt.sig_move_offset; po.kmer_start_offset = opt.kmer_start_offset;
     po.signal_print_margin = opt.signal_print_margin; po.sample_limit = opt.sample_limit;
     po.max_dur = (uint32_t)opt.max_dur; po.min_dur = (uint32_t)opt.min_dur; po.kmer_pick_margin = (uint32_t)opt.kmer_pick_margin;
-    po.flag_rna = opt.flag_rna; po.scaling = opt.scaling; po.output = PGM_OUT_TEXT;
+    po.flag_rna = opt.flag_rna; po.scaling = opt.scaling; po.output = opt.delimit_files ? PGM_OUT_TEXT : PGM_OUT_TEXT_ONLY;   // -d needs every event's record
     po.n_slots = R.n_slots; po.index_lo = opt.index_start - 1;
     po.pa_min = opt.pa_min; po.pa_max = opt.pa_max;
     std::string list;

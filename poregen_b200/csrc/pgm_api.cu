@@ -242,7 +242,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     if (opts->kmer_size < 1 || opts->kmer_size > 15) return fail(nullptr, PGM_ERR_ARG, "kmer_size %u outside 1..15", opts->kmer_size);
     if (opts->n_slots < 1) return fail(nullptr, PGM_ERR_ARG, "n_slots must be >= 1");
     if (opts->scaling > 1) return fail(nullptr, PGM_ERR_ARG, "scaling must be 0 or 1");
-    if (opts->output > PGM_OUT_TEXT) return fail(nullptr, PGM_ERR_ARG, "unknown output kind %u", opts->output);
+    if (opts->output > PGM_OUT_TEXT_ONLY) return fail(nullptr, PGM_ERR_ARG, "unknown output kind %u", opts->output);
     const uint64_t n_ids = 1ull << (2 * opts->kmer_size);
     if (!opts->kmer_list && (uint64_t)opts->index_lo + opts->n_slots > n_ids)
         return fail(nullptr, PGM_ERR_ARG, "k-mer window [%u,+%u) exceeds 4^k", opts->index_lo, opts->n_slots);
@@ -383,7 +383,7 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
         RET(ensure(c, c->zbatch, c->hist_off + (size_t)SORT_MAX_BINS * ntiles * 4));
     }
     RET(ensure(c, c->samples, (size_t)c->samples_cap * 8));
-    if (c->opts.output == PGM_OUT_TEXT) {
+    if (c->opts.output != PGM_OUT_F64) {
         RET(ensure(c, c->ev_tlen, e4 + 4));
         RET(ensure(c, c->ev_toff, (size_t)(cap + 1) * 8));
         RET(ensure(c, c->slot_toff, (size_t)(c->opts.n_slots + 1) * 8));
@@ -674,7 +674,7 @@ int pgm_emit(pgm_ctx *c) {
         else k_gather<false><<<c->n_sm * 5, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
         c->launches++;
     }
-    if (c->opts.output == PGM_OUT_TEXT) {
+    if (c->opts.output != PGM_OUT_F64) {
         StageTimer t(c, PGM_STAGE_TEXT);
         TextIO tio = make_text_io(c);
         k_text_len<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(tio);
@@ -720,9 +720,10 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     RET(ensure_host(c, c->h_ev_len, ne * 4 + 4));
     RET(ensure_host(c, c->h_ev_read, ne * 4 + 4));
     RET(ensure_host(c, c->h_ev_start, ne * 4 + 4));
-    const bool as_text = c->opts.output == PGM_OUT_TEXT;
+    const bool as_text = c->opts.output != PGM_OUT_F64;
+    const bool with_events = c->opts.output != PGM_OUT_TEXT_ONLY;   // per-event arrays travel to the host
     if (!as_text) RET(ensure_host(c, c->h_samples, nsamp * 8 + 8));
-    if (ne) {
+    if (ne && with_events) {
         CU(c, cudaMemcpyAsync(c->h_ev_len.p, c->sel_len.p, ne * 4, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_read.p, c->sel_read.p, ne * 4, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_start.p, c->sel_start.p, ne * 4, cudaMemcpyDeviceToHost, st));
@@ -743,7 +744,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
         }
         if (nt) CU(c, cudaMemcpyAsync(c->h_text.p, c->text.p, nt, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_slot_toff.p, c->slot_toff.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
-        CU(c, cudaMemcpyAsync(c->h_ev_toff.p, c->ev_toff.p, (ne + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (with_events) CU(c, cudaMemcpyAsync(c->h_ev_toff.p, c->ev_toff.p, (ne + 1) * 8, cudaMemcpyDeviceToHost, st));
     }
     if (c->model_on && nsamp) {   // K7: this batch's selected samples, as the integers their "%.8f" text spells
         pgm_ctx::ModelBatch mb;
@@ -764,10 +765,10 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     out->n_events_examined = s.examined; out->n_events_pass = s.n_pass;
     out->n_sel_events = ne; out->n_sel_samples = nsamp;
     out->slot_sel = P<uint32_t>(c->h_slot_sel); out->slot_total = P<uint32_t>(c->h_slot_total);
-    out->ev_len = P<uint32_t>(c->h_ev_len); out->ev_read = P<uint32_t>(c->h_ev_read); out->ev_start = P<uint32_t>(c->h_ev_start);
+    if (with_events) { out->ev_len = P<uint32_t>(c->h_ev_len); out->ev_read = P<uint32_t>(c->h_ev_read); out->ev_start = P<uint32_t>(c->h_ev_start); }
     out->samples = as_text ? nullptr : P<double>(c->h_samples); out->read_flags = P<uint8_t>(c->h_rflags);
     out->text = as_text ? P<char>(c->h_text) : nullptr; out->slot_text_off = as_text ? P<uint64_t>(c->h_slot_toff) : nullptr;
-    out->ev_text_off = as_text ? P<uint64_t>(c->h_ev_toff) : nullptr;
+    out->ev_text_off = (as_text && with_events) ? P<uint64_t>(c->h_ev_toff) : nullptr;
     c->state = ST_IDLE;
     return PGM_OK;
 }

@@ -61,7 +61,7 @@ class GmoveEngine:
         cb = batch.to_c()
         r = capi.PgmResult()
         self._chk(self.lib.pgm_process(self._ctx, C.byref(cb), C.byref(r)))
-        return GmoveResult.from_c(r, want_text=self.opts.output == capi.PGM_OUT_TEXT)
+        return GmoveResult.from_c(r, want_text=self.opts.output != capi.PGM_OUT_F64)
 
     def format_doubles(self, vals) -> bytes:
         """Device formatter test hook: the dump text of one event made of `vals`."""
@@ -91,7 +91,7 @@ class GmoveEngine:
     def download(self) -> GmoveResult:
         r = capi.PgmResult()
         self._chk(self.lib.pgm_download(self._ctx, C.byref(r)))
-        return GmoveResult.from_c(r, want_text=self.opts.output == capi.PGM_OUT_TEXT)
+        return GmoveResult.from_c(r, want_text=self.opts.output != capi.PGM_OUT_F64)
 
     def sync(self):
         self._chk(self.lib.pgm_sync(self._ctx))

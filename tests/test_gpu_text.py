@@ -61,3 +61,23 @@ def test_dump_text_equals_oracle(built, label, cfg, opts):
     np.testing.assert_array_equal(res.slot_text_off, ref.slot_text_off)
     assert res.text == ref.text
     assert res.samples.size == 0
+
+
+def test_text_only_output_leaves_event_arrays_on_the_device(built):
+    """PGM_OUT_TEXT_ONLY: the same text and per-slot offsets, no per-event arrays on the host."""
+    from cases import _o
+    from poregen_b200.synth import SynthConfig
+    opts = _o(kmer_size=4, sample_limit=30, scaling=1)
+    batch = synth.make_batch(SynthConfig(n_reads=40, median_samples=3000, seed=55))
+    ref = ol.oracle_run(opts, batch)
+    topts = copy.copy(opts)
+    topts.output = capi.PGM_OUT_TEXT_ONLY
+    with GmoveEngine(topts) as eng:
+        res = eng.process(batch)
+        res2 = eng.process(batch)          # second batch on the carried totals: the buffer of the first one is reused
+    assert res.text == ref.text
+    np.testing.assert_array_equal(res.slot_text_off, ref.slot_text_off)
+    np.testing.assert_array_equal(res.slot_sel, ref.slot_sel)
+    assert res.ev_len.size == 0 and res.ev_read.size == 0 and res.ev_start.size == 0 and res.samples.size == 0
+    ref2 = ol.oracle_run(opts, batch, totals=ref.slot_total.copy())
+    assert res2.text == ref2.text
