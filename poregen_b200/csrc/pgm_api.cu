@@ -2,9 +2,9 @@
 // kernel sequencing. No CPU fallback: every compute entry point needs a live CUDA device.
 //
 // Pipeline of one batch (all on one stream, no host synchronisation until pgm_download):
-//   count: k_read_prep -> [k_oor_check] -> k_decode<COUNT> -> scan(n_pass)
-//   emit : k_decode<EMIT> -> stable radix sort by slot -> k_select_prep -> scans -> k_select
-//          -> scan(sel_len) -> [k_stats] -> k_gather -> totals update -> scalars
+//   count: k_read_prep -> k_order -> [k_oor_check] -> k_decode -> k_scan_records -> k_place
+//   emit : k_quota -> k_scan_hist -> [k_sort_scatter, k_sort_hist, k_scan_hist per extra digit pass] -> k_rank
+//          -> k_scan_sel -> [k_stats_wide] -> [k_stats] -> k_gather -> [k_text_len -> k_scan_text -> k_text_write]
 // Element counts that only the device knows (passing / selected events) stay on the device: grids
 // are sized by capacities derived from the batch and the kernels read the counts themselves.
 #include <cuda_runtime.h>
@@ -57,7 +57,7 @@ struct pgm_ctx {
     uint64_t launches = 0;
 
     // per-context persistent device state
-    DBuf lut, consumed, counts, keep, totals_next, bucket_base, sel_base, gscratch;
+    DBuf lut, consumed, counts, keep, bucket_base, sel_base, gscratch;
     uint32_t lb_ticket = 0;          // look-back scans launched since the last zeroing (each gets its own ticket + status words)
     size_t lb_used = 0, lb_words = 0;   // status words handed out / available in zbatch
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
@@ -79,11 +79,10 @@ struct pgm_ctx {
     uint64_t samples_cap = 0;
 
     // per-record
-    DBuf cal, rflags, n_pass, ev_base, read_has_sel, ss_L, ss_nindel;
+    DBuf cal, rflags, n_pass, ev_base;
     // events / sort / selection
-    DBuf key, ev_start, ev_len, ev_read, key2, val, val2, hist, blk32, blk64;
+    DBuf key, ev_start, ev_len, ev_read, key2, val, val2;
     DBuf sc_start, sc_end, sc_key, sc_code, sc_indel;
-    DBuf rec_flag, rec_agg, rec_pre;   // look-back over records (k_decode)
     DBuf zbatch;                       // zeroed every batch: scalars | misc words | scan status | read_has_sel[R] | tile histogram
     size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
     uint32_t sort_ntiles = 0;
@@ -159,24 +158,6 @@ inline uint32_t *HIST(pgm_ctx *c) { return reinterpret_cast<uint32_t *>(reinterp
 
 inline uint32_t cdiv(uint64_t a, uint64_t b) { return (uint32_t)((a + b - 1) / b); }
 
-// Device-wide exclusive scan. n_cap sizes the grid; n_ptr (nullable) holds the real count.
-template <typename TIn, typename TOut>
-int scan(pgm_ctx *c, const TIn *in, TOut *out, uint64_t n_cap, const uint32_t *n_ptr, bool write_total, DBuf &blk) {
-    if (n_cap == 0) {
-        if (write_total) CU(c, cudaMemsetAsync(out, 0, sizeof(TOut), c->stream));
-        return PGM_OK;
-    }
-    const uint32_t nb = cdiv(n_cap, SCAN_TILE);
-    RET(ensure(c, blk, (size_t)nb * sizeof(TOut)));
-    TOut *bs = reinterpret_cast<TOut *>(blk.p);
-    k_scan_reduce<TIn, TOut><<<nb, PGM_BLOCK, 0, c->stream>>>(in, n_cap, n_ptr, bs);
-    k_scan_top<TOut><<<1, PGM_BLOCK, 0, c->stream>>>(bs, nb, (TOut *)nullptr);
-    k_scan_down<TIn, TOut><<<nb, PGM_BLOCK, 0, c->stream>>>(in, n_cap, n_ptr, bs, out, write_total ? 1 : 0);
-    c->launches += 3;
-    CU(c, cudaGetLastError());
-    return PGM_OK;
-}
-
 uint32_t bit_length(uint32_t x) { uint32_t b = 0; while (x) { b++; x >>= 1; } return b; }
 
 // Brackets a pipeline stage with a CUDA event pair on the context's stream when profiling is on.
@@ -221,11 +202,11 @@ void pgm_destroy(pgm_ctx *c) {
     for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); }
     c->model_log.clear();
     for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
-    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->totals_next, &c->bucket_base, &c->sel_base,
+    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->bucket_base, &c->sel_base,
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
-                   &c->ev_base, &c->read_has_sel, &c->ss_L, &c->ss_nindel, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
-                   &c->key2, &c->val, &c->val2, &c->hist, &c->blk32, &c->blk64, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->rec_flag, &c->rec_agg, &c->rec_pre, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
+                   &c->ev_base, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
+                   &c->key2, &c->val, &c->val2, &c->sc_start, &c->sc_end, &c->sc_code,
+                   &c->sc_indel, &c->sc_key, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff};
     for (DBuf *b : host) release_host(*b);
@@ -310,7 +291,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         d.use_lut = 1; d.lut = P<uint32_t>(c->lut);
     }
     const size_t sb = (size_t)opts->n_slots * 4;
-    DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep, &c->totals_next};
+    DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep};
     for (DBuf *b : slotbufs) if ((rc = ensure(c, *b, sb)) != PGM_OK) return bail(rc);
     if ((rc = ensure(c, c->bucket_base, sb + 4)) != PGM_OK || (rc = ensure(c, c->sel_base, sb + 4)) != PGM_OK) return bail(rc);
     if (cudaMemset(c->consumed.p, 0, sb) != cudaSuccess) { c->err = "memset failed"; return bail(PGM_ERR_CUDA); }
@@ -392,8 +373,6 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->sc_end, (size_t)b->n_align * 4 + 4));
     RET(ensure(c, c->sc_key, (size_t)b->n_align * 4 + 4));
     if (b->mode == PGM_MODE_SS) {
-        RET(ensure(c, c->ss_L, (size_t)R * 4));
-        RET(ensure(c, c->ss_nindel, (size_t)R * 4));
         RET(ensure(c, c->sc_code, (size_t)b->n_align + 4));
         RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4 + 4));
     }

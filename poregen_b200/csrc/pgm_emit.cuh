@@ -90,48 +90,6 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_oor_check(DevBatch b, const ReadC
 // counts[s] = passing events of this batch. keep = clamp(limit - prior, 0, counts): the first
 // `keep` passing events of the slot, in (record, position) order, are the ones the reference
 // would have written (gmove.cpp:650-652, 680-685).
-__global__ void __launch_bounds__(PGM_BLOCK) k_select_prep(uint32_t n_slots, uint32_t limit, const uint32_t *prior, const uint32_t *counts,
-                                                           uint32_t *keep, uint32_t *totals_out) {
-    const uint32_t s = blockIdx.x * PGM_BLOCK + threadIdx.x;
-    if (s >= n_slots) return;
-    const uint32_t p = min(prior[s], limit);
-    const uint32_t k = min(counts[s], limit - p);
-    keep[s] = k;
-    if (totals_out) totals_out[s] = p + k;
-}
-
-struct SelectIO {
-    const uint32_t *n_events;     // device scalar: number of passing events E
-    const uint32_t *skey, *sval;  // sorted (slot, event index)
-    const uint32_t *bucket_base;  // [n_slots+1] exclusive scan of counts
-    const uint32_t *keep;         // [n_slots]
-    const uint32_t *sel_base;     // [n_slots+1] exclusive scan of keep
-    const uint32_t *ev_start, *ev_len, *ev_read;  // [E] record-then-position order
-    uint32_t *sel_start, *sel_len, *sel_read;     // [E_sel] grouped by slot
-    uint32_t *ev_out;             // [E] selected index q of every passing event, or PGM_INVALID
-    uint8_t *read_has_sel;        // [R]
-};
-
-__global__ void __launch_bounds__(PGM_BLOCK) k_select(SelectIO io) {
-    const uint32_t n = *io.n_events;
-    for (uint32_t p = blockIdx.x * PGM_BLOCK + threadIdx.x; p < n; p += gridDim.x * PGM_BLOCK) {
-        const uint32_t slot = io.skey[p];
-        const uint32_t rank = p - io.bucket_base[slot];
-        const uint32_t id = io.sval[p];
-        const bool sel = rank < io.keep[slot];
-        io.ev_out[id] = sel ? io.sel_base[slot] + rank : PGM_INVALID;
-        if (sel) {
-            const uint32_t q = io.sel_base[slot] + rank;
-            const uint32_t rr = io.ev_read[id];
-            io.sel_start[q] = io.ev_start[id];
-            io.sel_len[q] = io.ev_len[id];
-            io.sel_read[q] = rr;
-            io.read_has_sel[rr] = 1;
-        }
-    }
-}
-
-
 // ------------------------------------------------------------------------------------------------
 // k_quota: one launch for everything the quota needs. Per slot s: keep = clamp(limit - prior, 0, counts)
 // and the totals after the batch; a packed look-back scan gives bucket_base = exscan(counts) (where each
