@@ -68,6 +68,8 @@ struct pgm_ctx {
     std::vector<ModelBatch> model_log;
     DBuf model_bad, model_grouped, model_off, model_dst, model_rows;
     std::vector<pgm_model_row> h_model_rows;
+    cudaStream_t aux = nullptr;               // short scans that do not depend on each other run beside the main stream
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     size_t text_written_cap = 0;              // capacity of `text` when pgm_emit formatted into it (0: it did not)
     uint32_t n_ranks = 1, rank = 0;
 
@@ -172,14 +174,15 @@ struct StageTimer {
         cudaEventCreate(&e);
         return e;
     }
-    StageTimer(pgm_ctx *c_, int stage_) : c(c_), stage(stage_), l0(c_->launches) {
+    cudaStream_t s;
+    StageTimer(pgm_ctx *c_, int stage_, cudaStream_t s_ = nullptr) : c(c_), stage(stage_), l0(c_->launches), s(s_ ? s_ : c_->stream) {
         if (!c->prof) return;
         a = get(c); b = get(c);
-        cudaEventRecord(a, c->stream);
+        cudaEventRecord(a, s);
     }
     void stop() {
         if (!a) return;
-        cudaEventRecord(b, c->stream);
+        cudaEventRecord(b, s);
         c->spans.push_back({stage, a, b, (uint32_t)(c->launches - l0)});
         a = nullptr;
     }
@@ -199,6 +202,9 @@ void pgm_destroy(pgm_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->aux) { cudaStreamSynchronize(c->aux); cudaStreamDestroy(c->aux); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); }
     c->model_log.clear();
     for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
@@ -254,6 +260,12 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
             return fail(nullptr, PGM_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
         }
         c->own_stream = true;
+    }
+    if ((e = cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
+        delete c;
+        return fail(nullptr, PGM_ERR_CUDA, "cudaStreamCreate (aux): %s", cudaGetErrorString(e));
     }
     DevOpts &d = c->dopts;
     memset(&d, 0, sizeof d);
@@ -575,6 +587,21 @@ int pgm_emit(pgm_ctx *c) {
     d.mode = c->db.mode;
     const uint32_t *n_ev = P<uint32_t>(c->ev_base) + R;  // device scalar: passing events
     const uint32_t pgrid = (uint32_t)c->n_sm * 4;
+    // The scan of the first digit pass's tile histogram (filled by k_place) does not depend on the quota: it runs on
+    // the auxiliary stream while k_quota runs here; both are a few microseconds of latency, not of bandwidth.
+    const bool sorting = R && c->ev_cap;
+    uint32_t passes = 0, per = 0;
+    if (sorting) {
+        sort_plan(c, &passes, &per);
+        CU(c, cudaEventRecord(c->ev_fork, st));
+        CU(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
+        StageTimer t(c, PGM_STAGE_SORT, c->aux);
+        k_scan_hist<<<cdiv((uint64_t)(1u << per) * c->sort_ntiles, LB_TILE), PGM_BLOCK, 0, c->aux>>>(HIST(c), n_ev, 1u << per, c->sort_ntiles,
+                                                                                                  next_lb(c, cdiv((uint64_t)(1u << per) * c->sort_ntiles, LB_TILE)));
+        c->launches++;
+        t.stop();
+        CU(c, cudaEventRecord(c->ev_join, c->aux));
+    }
     // quota: keep / bucket_base / sel_base / totals after the batch, one launch
     {
         StageTimer t(c, PGM_STAGE_SELECT);
@@ -588,21 +615,22 @@ int pgm_emit(pgm_ctx *c) {
         k_quota<<<cdiv(NS, LB_TILE), PGM_BLOCK, 0, st>>>(q, next_lb(c, cdiv(NS, LB_TILE)));
         c->launches++;
     }
-    if (R && c->ev_cap) {
+    if (sorting) {
         // stable LSD radix sort of (slot, event index); the last pass is fused with the selection (k_rank)
+        CU(c, cudaStreamWaitEvent(st, c->ev_join, 0));
         StageTimer tsort(c, PGM_STAGE_SORT);
-        uint32_t passes, per;
-        sort_plan(c, &passes, &per);
         const uint32_t ntiles = c->sort_ntiles;
         const uint32_t sgrid = ntiles < pgrid ? ntiles : pgrid;
         uint32_t *kin = P<uint32_t>(c->key), *kout = P<uint32_t>(c->key2);
         uint32_t *vin = nullptr, *vout = P<uint32_t>(c->val);
         for (uint32_t p = 0; p < passes; p++) {
             const uint32_t shift = p * per;
-            if (p) { k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, HIST(c), ntiles); c->launches++; }   // pass 0: counted by k_decode
-            k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(HIST(c), n_ev, 1u << per, ntiles,
-                                                                                           next_lb(c, cdiv((uint64_t)(1u << per) * ntiles, LB_TILE)));
-            c->launches++;
+            if (p) {   // pass 0: counted by k_place and scanned on the auxiliary stream above
+                k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, HIST(c), ntiles);
+                k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(HIST(c), n_ev, 1u << per, ntiles,
+                                                                                               next_lb(c, cdiv((uint64_t)(1u << per) * ntiles, LB_TILE)));
+                c->launches += 2;
+            }
             if (p + 1 < passes) {
                 k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, HIST(c), ntiles);
                 c->launches++;
@@ -623,12 +651,22 @@ int pgm_emit(pgm_ctx *c) {
         }
         CU(c, cudaGetLastError());
     }
+    // Sample offsets of the selected events: needed by k_gather, not by the statistics, so with scaling the scan runs
+    // beside k_stats.
+    const bool beside = sorting && c->opts.scaling;
     {
-        StageTimer t(c, PGM_STAGE_SCAN);
-        k_scan_sel<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_len), P<unsigned long long>(c->sel_off),
+        cudaStream_t ss = beside ? c->aux : st;
+        if (beside) {
+            CU(c, cudaEventRecord(c->ev_fork, st));
+            CU(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
+        }
+        StageTimer t(c, PGM_STAGE_SCAN, ss);
+        k_scan_sel<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, ss>>>(P<uint32_t>(c->sel_len), P<unsigned long long>(c->sel_off),
                                                                                P<uint32_t>(c->sel_base) + NS, n_ev, SCALARS(c),
                                                                                next_lb(c, cdiv((uint64_t)c->ev_cap + 1, LB_TILE)));
         c->launches++;
+        t.stop();
+        if (beside) CU(c, cudaEventRecord(c->ev_join, c->aux));
     }
     if (R && c->ev_cap) {
         if (c->opts.scaling) {
@@ -644,6 +682,7 @@ int pgm_emit(pgm_ctx *c) {
             k_stats<<<sgrid, STATS_WARPS * 32, STATS_DYN_SMEM, st>>>(d, c->db, si);
             c->launches++;
         }
+        if (beside) CU(c, cudaStreamWaitEvent(st, c->ev_join, 0));
         StageTimer t(c, PGM_STAGE_GATHER);
         GatherIO g;
         g.sel_src = P<unsigned long long>(c->sel_src); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
