@@ -200,6 +200,9 @@ int pgm_set_prior_host(pgm_ctx *ctx, const uint32_t *prior, const uint32_t *cons
 void *pgm_alloc_pinned(size_t bytes);
 void pgm_free_pinned(void *p);
 int pgm_device_count(void);
+/* Creates the device's CUDA context ahead of time (callable from any thread, before pgm_create): a command line
+ * can hide the few hundred milliseconds behind its own start-up. */
+int pgm_warmup(int device);
 
 /* Forget all per-k-mer totals (start a new run with the same options). */
 int pgm_reset(pgm_ctx *ctx);

@@ -114,7 +114,7 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
-    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize",
+    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup",
 ]
 PGM_N_STAGES = 10
 # pgm_model_row (include/pgm_gmove.h)

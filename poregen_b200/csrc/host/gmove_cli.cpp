@@ -385,7 +385,7 @@ struct Run {
     uint32_t n_slots = 0;
     uint32_t mode = PGM_MODE_MOVES_CHAR;
     uint64_t n_records = 0, n_samples = 0, n_examined = 0, n_selected = 0;
-    double t_read = 0, t_dev = 0, t_write = 0;
+    double t_read = 0, t_dev = 0, t_write = 0, t_create = 0, t_parse = 0, t_start = 0, t_close = 0;
 };
 
 // Fetches the signal of every record of the batch on host threads and lays the batch out for the device:
@@ -619,6 +619,7 @@ const struct option long_options[] = {
 
 // Same contract as the reference's gmove(argc, argv) (src/main.c:43,76): argv[0] is the word "gmove".
 int gmove(int argc, char *argv[]) {
+    const double t_gmove0 = realtime();
     Run R;
     Opt &opt = R.opt;
     const char *kmer_file = nullptr, *fastq_file = nullptr;
@@ -682,6 +683,10 @@ int gmove(int argc, char *argv[]) {
     if (opt.kmer_size <= opt.sig_move_offset) msg("WARNING", "signal move offset value should be less than the kmer length");
     if (opt.kmer_size > 15) DIE("kmer_size above 15 is not supported by the B200 build");
 
+    // CUDA context creation (a few hundred ms) runs beside the host-side start-up: directory, k-mer files, indexes
+    std::thread warm([&opt]() { for (int g = 0; g < opt.gpus; g++) pgm_warmup(g); });
+    struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } warm_join{warm};
+
     int rc = create_dir(output_dir);
     if (rc == -1) { msg("ERROR", "Output directory %s is not empty. Please remove it or specify another directory.", output_dir); return EXIT_FAILURE; }
     if (rc == -2) { msg("ERROR", "Could not create the output dir %s.", output_dir); return EXIT_FAILURE; }
@@ -734,11 +739,25 @@ int gmove(int argc, char *argv[]) {
     // one (empty) file per dumped k-mer, as the reference's fopen(..., "w") loop leaves them (gmove.cpp:460-473);
     // opened and closed one at a time, so 4^9 files do not need 262,144 descriptors
     R.n_slots = opt.index_end - opt.index_start + 1;
-    for (uint32_t i = opt.index_start - 1; i < opt.index_end; i++) {
-        const std::string path = R.dump_dir + "/" + kmers[i];
-        FILE *fp = fopen(path.c_str(), "w");
-        if (!fp) { fprintf(stderr, "Error in opening %dth kmer-file %s\n", i - (opt.index_start - 1) + 1, path.c_str()); exit(EXIT_FAILURE); }
-        fclose(fp);
+    {   // file creation is latency of the file system, not CPU: a few threads take it off the start-up time
+        const uint32_t nt = std::min<uint32_t>(16, R.n_slots);
+        std::atomic<uint32_t> failed{0xffffffffu};
+        std::vector<std::thread> pool;
+        for (uint32_t t = 0; t < nt; t++)
+            pool.emplace_back([&, t]() {
+                for (uint32_t i = opt.index_start - 1 + t; i < opt.index_end; i += nt) {
+                    const std::string path = R.dump_dir + "/" + kmers[i];
+                    FILE *fp = fopen(path.c_str(), "w");
+                    if (!fp) { uint32_t exp = 0xffffffffu; failed.compare_exchange_strong(exp, i); return; }
+                    fclose(fp);
+                }
+            });
+        for (auto &th : pool) th.join();
+        const uint32_t i = failed.load();
+        if (i != 0xffffffffu) {
+            fprintf(stderr, "Error in opening %dth kmer-file %s\n", i - (opt.index_start - 1) + 1, (R.dump_dir + "/" + kmers[i]).c_str());
+            exit(EXIT_FAILURE);
+        }
     }
     R.totals.assign(R.n_slots, 0);
 
@@ -778,6 +797,9 @@ int gmove(int argc, char *argv[]) {
         po.kmer_list = list.data();
     }
     R.gpus.resize(opt.gpus);
+    if (warm.joinable()) warm.join();
+    const double t_c0 = realtime();
+    R.t_start = t_c0 - t_gmove0;
     for (int g = 0; g < opt.gpus; g++)
         if (pgm_create(&po, g, nullptr, &R.gpus[g].ctx) != PGM_OK) DIE("%s", pgm_last_error(nullptr));
     if (opt.model_out) {
@@ -787,7 +809,9 @@ int gmove(int argc, char *argv[]) {
         if (pgm_model_begin(R.gpus[0].ctx) != PGM_OK) DIE("%s", pgm_last_error(R.gpus[0].ctx));
     }
 
+    R.t_create = realtime() - t_c0;
     // record loop
+    const double t_loop0 = realtime();
     FILE *fp = fopen(move_table, "r");
     if (!fp) { fprintf(stderr, "Error in opening file %s\n", move_table); exit(EXIT_FAILURE); }
     BamReader bam;
@@ -828,6 +852,8 @@ int gmove(int argc, char *argv[]) {
     process_batch(R, batch);
     free(line);
     fclose(fp);
+    R.t_parse = realtime() - t_loop0 - R.t_read - R.t_dev - R.t_write;
+    const double t_close0 = realtime();
 
     const std::string freq = std::string(output_dir) + "/freq.txt";
     FILE *ff = fopen(freq.c_str(), "w");
@@ -851,9 +877,10 @@ int gmove(int argc, char *argv[]) {
     for (Gpu &g : R.gpus) pgm_destroy(g.ctx);
     slow5_idx_unload(R.sp);
     slow5_close(R.sp);
+    R.t_close = realtime() - t_close0;
     if (g_verbose > 1 || getenv("PGM_CLI_STATS"))
-        fprintf(stderr, "\n[gmove] %" PRIu64 " records, %" PRIu64 " samples, %" PRIu64 " events examined, %" PRIu64 " selected; read %.3fs device %.3fs write %.3fs\n",
-                R.n_records, R.n_samples, R.n_examined, R.n_selected, R.t_read, R.t_dev, R.t_write);
+        fprintf(stderr, "\n[gmove] %" PRIu64 " records, %" PRIu64 " samples, %" PRIu64 " events examined, %" PRIu64 " selected; start %.3fs create %.3fs parse %.3fs read %.3fs device %.3fs write %.3fs close %.3fs\n",
+                R.n_records, R.n_samples, R.n_examined, R.n_selected, R.t_start, R.t_create, R.t_parse, R.t_read, R.t_dev, R.t_write, R.t_close);
     return 0;
 }
 

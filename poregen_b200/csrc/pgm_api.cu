@@ -552,6 +552,11 @@ int pgm_device_count(void) {
     if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
     return n;
 }
+
+int pgm_warmup(int device) {
+    if (cudaSetDevice(device) != cudaSuccess || cudaFree(nullptr) != cudaSuccess) { cudaGetLastError(); return PGM_ERR_CUDA; }
+    return PGM_OK;
+}
 int pgm_set_gathered(pgm_ctx *c, const uint32_t *all_counts_dev, uint32_t n_ranks, uint32_t rank) {
     if (!c || !all_counts_dev || !n_ranks || rank >= n_ranks) return PGM_ERR_ARG;
     if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_set_gathered belongs between pgm_count and pgm_emit");
