@@ -369,6 +369,8 @@ def run_own_arm(args):
     # and its kernels run (PCIe is full duplex). Each slot is a context with its own stream; every step still does
     # its own upload, its own count/[all-gather]/emit and its own download into host memory inside the timed region.
     class Slot:
+        svb = None      # (aligned batch, stream bytes, stream offsets): upload the compressed signal instead of raw[]
+
         def __init__(self):
             self.stream = torch.cuda.Stream(device=local)
             self.eng = GmoveEngine(topts, device=local, stream=self.stream.cuda_stream)
@@ -380,7 +382,10 @@ def run_own_arm(args):
             e = self.eng
             with torch.cuda.stream(self.stream):
                 e.reset()
-                e.upload(batch)
+                if Slot.svb is not None:
+                    e.upload_svb(*Slot.svb)
+                else:
+                    e.upload(batch)
                 e.count()
                 if world > 1:
                     dist.all_gather_into_tensor(self.all_counts.view(-1), self.counts_t)
@@ -421,6 +426,49 @@ def run_own_arm(args):
     text_bytes = int(C.cast(r.slot_text_off, C.POINTER(C.c_uint64))[NS])
     d2h = int(text_bytes + NS * 16 + batch.n_reads + 48)
     examined = int(r.n_events_examined)
+
+    # ---- the same step fed with the records' svb-zd streams (what a BLOW5 file stores) instead of int16 samples:
+    # k_svb_decode produces raw[] in HBM. Single-GPU runs only (the encoder here is numpy).
+    svb_info = None
+    if world == 1 and not args.no_svb:
+        ab = synth.align_raw(hb, 8)
+        sb, so = synth.svb_streams(ab)
+        p_sb, p_so = pin(sb), pin(so)
+        ab = ReadBatch(ab.mode, ab.raw, batch.align, batch.bases, pin(ab.reads).numpy().view(np.dtype(capi.READ_DTYPE)), ab.read_ids)
+        svb_args = (ab, p_sb.numpy(), p_so.numpy().view(np.uint64))
+        e = slots[0].eng
+        with torch.cuda.stream(slots[0].stream):
+            for _ in range(3):
+                e.upload_svb(*svb_args)
+            e.sync()
+            e.profile_enable(True); e.profile_read()
+            for _ in range(args.steps):
+                e.upload_svb(*svb_args)
+            st_svb = e.profile_read()["svb"]
+            e.profile_enable(False)
+        live = np.zeros(ab.raw.size + 1, np.int32)          # the padding between records is not written by the decoder
+        np.add.at(live, ab.reads["raw_off"].astype(np.int64), 1)
+        np.add.at(live, ab.reads["raw_off"].astype(np.int64) + ab.reads["raw_len"].astype(np.int64), -1)
+        live = np.cumsum(live[:-1]) > 0
+        assert np.array_equal(e.device_raw(ab.raw.size)[live], ab.raw[live]), "k_svb_decode: samples differ from the encoder's input"
+        Slot.svb = svb_args
+        rs = run_e2e(max(depth, args.warmup))
+        barrier()
+        t0 = time.perf_counter()
+        rs = run_e2e(args.steps)
+        barrier()
+        svb_s = (time.perf_counter() - t0) / args.steps
+        Slot.svb = None
+        assert int(rs.n_sel_samples) == int(r.n_sel_samples) and int(C.cast(rs.slot_text_off, C.POINTER(C.c_uint64))[NS]) == text_bytes
+        k_ms = st_svb[0] / max(1, st_svb[1])
+        alg_svb = int(sb.nbytes + 2 * n_samples)
+        pk, _ = measured_peak()
+        svb_info = {"kernel": "k_svb_decode", "ms_per_launch": k_ms, "stream_bytes": int(sb.nbytes), "bytes_per_sample": sb.nbytes / n_samples,
+                    "algorithmic_bytes": alg_svb, "gbs": alg_svb / (k_ms * 1e-3) / 1e9, "frac": alg_svb / (k_ms * 1e-3) / 1e9 / pk,
+                    "e2e": {"value": n_samples / svb_s, "unit": UNIT, "ms_per_step": svb_s * 1e3,
+                            "h2d_bytes_per_step": int(sb.nbytes + so.nbytes + batch.align.nbytes + batch.bases.nbytes + batch.reads.nbytes),
+                            "d2h_bytes_per_step": d2h},
+                    "note": "same C2 step with the records' slow5 svb-zd streams uploaded instead of int16 samples; decoded in HBM"}
 
     tot = torch.tensor([n_samples, examined, int(r.n_sel_events), int(r.n_sel_samples)], dtype=torch.float64, device=f"cuda:{local}")
     if world > 1:
@@ -466,6 +514,8 @@ def run_own_arm(args):
                 "roofline_step": {"algorithmic_bytes": alg_step, "gbs": alg_step / (ms_step * 1e-3) / 1e9,
                                   "frac": alg_step / (ms_step * 1e-3) / 1e9 / peak},
                 "stages": stage_rows, "model_aggregation": model_info, "clocks": clocks}
+        if svb_info:
+            line["svb_signal"] = svb_info
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(args.cpu_reads)
         emit_line(line)
@@ -508,6 +558,7 @@ def main():
     ap.add_argument("--ref-reads", type=int, default=1500, help="--impl reference: records per step")
     ap.add_argument("--cpu-reads", type=int, default=3000, help="cpu_baseline leg: records in the sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-svb", action="store_true", help="skip the compressed-signal (svb-zd) leg")
     ap.add_argument("--e2e-depth", type=int, default=2, help="e2e leg: batches in flight (1 = strictly serial steps)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "own":

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define PGM_ABI_VERSION 2
+#define PGM_ABI_VERSION 3
 
 /* ---- status codes ---- */
 #define PGM_OK 0
@@ -172,6 +172,23 @@ int pgm_emit(pgm_ctx *ctx);   /* stable bucketing, sample_limit, Med-MAD, sample
 int pgm_download(pgm_ctx *ctx, pgm_result *out); /* D2H + stream sync                             */
 int pgm_sync(pgm_ctx *ctx);
 
+/* Compressed signal. Replaces the host-side signal decompression slow5lib runs inside
+ * slow5_get / slow5_rec_parse (slow5lib/src/slow5.c:2876-2905 -> slow5_press.c:1085-1130 ptr_depress_svb_zd ->
+ * thirdparty/streamvbyte/src/streamvbyte_decode.c:57-104 and streamvbyte_zigzag.c:34-40): record i's stream
+ * bytes[off[i] .. off[i+1]) is the raw_signal field of its BLOW5 record exactly as stored when the file's
+ * signal_press is svb-zd (u32 count | (count+3)/4 key bytes | 1..4 data bytes per value). pgm_upload_svb copies
+ * the streams instead of raw[] (host_batch->raw must be NULL; n_raw and reads[].raw_off/raw_len describe the
+ * layout the samples are decoded into on the device - make raw_off a multiple of 8 for 16-byte stores) and
+ * decodes them with one kernel; every later call is the same as after pgm_upload. A stream whose count differs
+ * from raw_len, or that does not consume exactly its bytes (slow5lib's own check, slow5_press.c:1097-1103),
+ * makes pgm_download fail with PGM_ERR_INPUT. */
+typedef struct pgm_svb {
+    uint64_t n_bytes;      /* bytes in bytes[]                                                     */
+    const uint8_t *bytes;  /* concatenated streams (pinned host memory for speed)                  */
+    const uint64_t *off;   /* [n_reads+1] byte offsets into bytes[], ascending                     */
+} pgm_svb;
+int pgm_upload_svb(pgm_ctx *ctx, const pgm_batch *host_batch, const pgm_svb *svb);
+
 /* Multi-GPU quota exchange (north_star: allgather of the 4^k count vector + exclusive scan over
  * ranks). After pgm_count, counts[s] = passing events of slot s in this rank's batch (device
  * uint32[n_slots]). The caller allgathers them and hands back, as DEVICE pointers:
@@ -226,7 +243,8 @@ uint64_t pgm_launch_count(const pgm_ctx *ctx);
 #define PGM_STAGE_GATHER 7       /* k_gather: the selected samples as doubles, in output order     */
 #define PGM_STAGE_MISC 8         /* memsets                                                        */
 #define PGM_STAGE_TEXT 9         /* PGM_OUT_TEXT: k_text_len, k_scan_text (k_text_write runs in pgm_download) */
-#define PGM_N_STAGES 10
+#define PGM_STAGE_SVB 10         /* k_svb_decode (pgm_upload_svb)                                   */
+#define PGM_N_STAGES 11
 int pgm_profile_enable(pgm_ctx *ctx, int on);
 int pgm_profile_read(pgm_ctx *ctx, float *ms, uint32_t *launches);
 const char *pgm_stage_name(int stage);
@@ -255,6 +273,10 @@ int pgm_model_finalize(pgm_ctx *ctx, double stddev_limit, const pgm_model_row **
  * ("%.8f," ... "%.8f;", gmove.cpp:674-678) into text_out[cap]; *len_out = its length (also when it
  * does not fit, in which case nothing is written). */
 int pgm_debug_format(pgm_ctx *ctx, const double *vals, uint32_t n, char *text_out, uint64_t cap, uint64_t *len_out);
+
+/* Test hook: the first n samples of the loaded batch's raw[] as the device holds them (after pgm_upload_svb: as
+ * decoded), and the decoder's verdict (PGM_ERR_INPUT for a malformed stream). Synchronises. */
+int pgm_debug_raw(pgm_ctx *ctx, int16_t *out, uint64_t n);
 
 #ifdef __cplusplus
 }

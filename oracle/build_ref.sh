@@ -7,6 +7,7 @@
 #   oracle/_ref/poregen_ref     src/gmove.cpp + poregen.cpp + thread.c, -O2
 #   oracle/_ref/poregen_ref_g   same, flags as shipped by the reference Makefile:4 (-g, no -O)
 #   oracle/_ref/reform_ref      src/reform.cpp (text SAM input only)
+#   oracle/_ref/libsvbref.so    slow5lib's own svb-zd compress/depress behind two C entry points (svb_ref_wrap.c)
 # htslib is not vendored by the reference (Makefile:69-81 downloads 1.17): the
 # stand-in headers in oracle/shim/htslib are used instead (parsing only).
 # No -march=native / -ffast-math: keeps fp64 results FMA-free (x86-64 baseline).
@@ -48,6 +49,7 @@ for f in reform.cpp poregen.cpp thread.c; do
 done
 $CXX -g -O2 "$OUT/obj/reform_main.cpp" "$OUT/obj/reform_reform.o" "$OUT/obj/reform_poregen.o" "$OUT/obj/reform_thread.o" "$OUT/libslow5.a" \
     -lz -lm -lpthread -o "$OUT/reform_ref"
+$CC -g -O2 -std=c99 -fPIC -shared -I "$S5/include" "$HERE/svb_ref_wrap.c" "$OUT/libslow5.a" -lz -lm -o "$OUT/libsvbref.so"
 build_one poregen_ref -g -O2
 build_one poregen_ref_g -g
 rm -rf "$OUT/obj"

@@ -417,3 +417,31 @@ size_t oracle_model_row_text(const char *text, size_t len, double limit, double 
     free(v);
     return m;
 }
+
+/* ---------- svb-zd signal stream ----------
+ * slow5lib/src/slow5_press.c:1085-1130 (ptr_depress_svb / ptr_depress_svb_zd): u32 count, then
+ * thirdparty/streamvbyte/src/streamvbyte_decode.c:57-104 (keys: 2 bits per value, (count+3)/4 bytes; data:
+ * code+1 little-endian bytes per value, 36-56) and streamvbyte_zigzag.c:19-40 (zig-zag, running sum from 0,
+ * stored as int16). Returns 0, or -1 where slow5lib reports an error (count differs from what the caller expects /
+ * the decoder does not consume exactly nbytes-4 bytes, slow5_press.c:1097-1103). */
+int oracle_svb_zd_decode(const uint8_t *p, size_t nbytes, uint32_t expect, int16_t *out) {
+    if (nbytes < 4) return -1;
+    uint32_t count;
+    memcpy(&count, p, 4);
+    if (count != expect) return -1;
+    const size_t keylen = ((size_t)count + 3) / 4;
+    if (4 + keylen > nbytes) return -1;
+    const uint8_t *keys = p + 4, *data = keys + keylen, *end = p + nbytes;
+    int32_t prev = 0;
+    for (uint32_t i = 0; i < count; i++) {
+        const unsigned code = (keys[i >> 2] >> (2 * (i & 3))) & 3u;
+        if (data + code + 1 > end) return -1;
+        uint32_t v = 0;
+        memcpy(&v, data, code + 1);            /* little endian host, as the reference assumes */
+        data += code + 1;
+        const int32_t d = (int32_t)((v >> 1) ^ (0u - (v & 1u)));
+        prev = (int32_t)((uint32_t)prev + (uint32_t)d);
+        out[i] = (int16_t)prev;
+    }
+    return data == end ? 0 : -1;
+}

@@ -17,7 +17,7 @@ PGM_MODE_MOVES_CHAR, PGM_MODE_SS, PGM_MODE_MOVES_I8 = 0, 1, 2
 PGM_READ_RNA, PGM_READ_SKIP = 1, 2
 PGM_RF_SKIPPED, PGM_RF_BAD_ALIGN, PGM_RF_BAD_CALIB = 1, 2, 4
 PGM_OUT_F64, PGM_OUT_TEXT, PGM_OUT_TEXT_ONLY = 0, 1, 2
-PGM_ABI_VERSION = 2
+PGM_ABI_VERSION = 3
 
 
 class PgmOpts(C.Structure):
@@ -77,6 +77,10 @@ class PgmBatch(C.Structure):
     ]
 
 
+class PgmSvb(C.Structure):
+    _fields_ = [("n_bytes", C.c_uint64), ("bytes", C.c_void_p), ("off", C.c_void_p)]
+
+
 class PgmResult(C.Structure):
     _fields_ = [
         ("n_slots", C.c_uint32),
@@ -114,9 +118,9 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
-    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup",
+    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw",
 ]
-PGM_N_STAGES = 10
+PGM_N_STAGES = 11
 # pgm_model_row (include/pgm_gmove.h)
 MODEL_ROW_DTYPE = [("median", "<f8"), ("stddev", "<f8"), ("median_num", "<i8"), ("n", "<u8"), ("flags", "<u4"), ("pad", "<u4")]
 PGM_MODEL_EMPTY, PGM_MODEL_NO_SD, PGM_MODEL_RANGE, PGM_MODEL_CLAMPED = 1, 2, 4, 8
@@ -149,6 +153,8 @@ def load() -> C.CDLL:
     for name in ("pgm_upload", "pgm_attach_device"):
         getattr(lib, name).argtypes = [C.c_void_p, P(PgmBatch)]
         getattr(lib, name).restype = C.c_int
+    lib.pgm_upload_svb.argtypes = [C.c_void_p, P(PgmBatch), P(PgmSvb)]
+    lib.pgm_upload_svb.restype = C.c_int
     for name in ("pgm_count", "pgm_emit", "pgm_sync", "pgm_reset"):
         getattr(lib, name).argtypes = [C.c_void_p]
         getattr(lib, name).restype = C.c_int
@@ -176,6 +182,8 @@ def load() -> C.CDLL:
     lib.pgm_profile_read.restype = C.c_int
     lib.pgm_stage_name.argtypes = [C.c_int]
     lib.pgm_stage_name.restype = C.c_char_p
+    lib.pgm_debug_raw.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.pgm_debug_raw.restype = C.c_int
     lib.pgm_debug_format.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, P(C.c_uint64)]
     lib.pgm_debug_format.restype = C.c_int
     _lib = lib

@@ -25,6 +25,7 @@
 #include "pgm_sort.cuh"
 #include "pgm_text.cuh"
 #include "pgm_model.cuh"
+#include "pgm_svb.cuh"
 
 namespace {
 
@@ -77,6 +78,9 @@ struct pgm_ctx {
     DevBatch db{};
     bool attached = false;
     DBuf raw, align, bases, reads;
+    DBuf svb_blob, svb_off, svb_words;        // pgm_upload_svb: streams, their offsets, {ticket, error} words
+    bool svb_used = false;
+    DBuf h_svb_err;
     uint32_t ev_cap = 0;
     uint64_t samples_cap = 0;
 
@@ -212,9 +216,9 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed};
+                   &c->sc_indel, &c->sc_key, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed, &c->svb_blob, &c->svb_off, &c->svb_words};
     for (DBuf *b : dev) release(*b);
-    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff};
+    DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff, &c->h_svb_err};
     for (DBuf *b : host) release_host(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     for (auto &sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
@@ -392,15 +396,14 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     return PGM_OK;
 }
 
-int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
-    if (!c || !b) return PGM_ERR_ARG;
-    CU(c, cudaSetDevice(c->device));
+// H2D copies of a host batch; `with_raw` false leaves raw[] to be produced on the device (pgm_upload_svb)
+static int upload_common(pgm_ctx *c, const pgm_batch *b, bool with_raw) {
     RET(prepare_batch(c, b));
     RET(ensure(c, c->raw, (size_t)b->n_raw * 2 + 32));
     RET(ensure(c, c->align, (size_t)b->n_align + 32));
     RET(ensure(c, c->bases, (size_t)b->n_bases + 32));
     RET(ensure(c, c->reads, (size_t)b->n_reads * sizeof(pgm_read)));
-    if (b->n_raw) CU(c, cudaMemcpyAsync(c->raw.p, b->raw, (size_t)b->n_raw * 2, cudaMemcpyHostToDevice, c->stream));
+    if (with_raw && b->n_raw) CU(c, cudaMemcpyAsync(c->raw.p, b->raw, (size_t)b->n_raw * 2, cudaMemcpyHostToDevice, c->stream));
     if (b->n_align) CU(c, cudaMemcpyAsync(c->align.p, b->align, (size_t)b->n_align, cudaMemcpyHostToDevice, c->stream));
     if (b->n_bases) CU(c, cudaMemcpyAsync(c->bases.p, b->bases, (size_t)b->n_bases, cudaMemcpyHostToDevice, c->stream));
     if (b->n_reads) CU(c, cudaMemcpyAsync(c->reads.p, b->reads, (size_t)b->n_reads * sizeof(pgm_read), cudaMemcpyHostToDevice, c->stream));
@@ -408,6 +411,7 @@ int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
     c->db.raw = P<int16_t>(c->raw); c->db.align = P<uint8_t>(c->align); c->db.bases = P<uint8_t>(c->bases); c->db.reads = P<pgm_read>(c->reads);
     c->attached = false;
     c->need_wide = false;
+    c->svb_used = false;
     if (c->opts.scaling) {
         // in-range code span ~ (pa_max - pa_min) / |scale|; anything close to the shared-memory budget goes the wide way
         const double span = c->opts.pa_max - c->opts.pa_min;
@@ -416,6 +420,48 @@ int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
             if (!(span / sc < (double)(SIG_SMEM_BINS - 8))) c->need_wide = true;
         }
     }
+    c->state = ST_LOADED;
+    return PGM_OK;
+}
+
+int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
+    if (!c || !b) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    return upload_common(c, b, true);
+}
+
+int pgm_upload_svb(pgm_ctx *c, const pgm_batch *b, const pgm_svb *svb) {
+    if (!c || !b || !svb) return PGM_ERR_ARG;
+    if (b->raw) return fail(c, PGM_ERR_ARG, "pgm_upload_svb: batch.raw must be NULL (the samples are decoded on the device)");
+    if (b->n_reads && (!svb->off || (svb->n_bytes && !svb->bytes))) return fail(c, PGM_ERR_ARG, "null array in pgm_svb");
+    CU(c, cudaSetDevice(c->device));
+    pgm_batch hb = *b;
+    static const int16_t dummy = 0;
+    if (hb.n_raw) hb.raw = &dummy;     // prepare_batch only checks for presence
+    RET(upload_common(c, &hb, false));
+    c->state = ST_IDLE;
+    const uint32_t R = b->n_reads;
+    RET(ensure(c, c->svb_blob, (size_t)svb->n_bytes + 64));
+    RET(ensure(c, c->svb_off, (size_t)(R + 1) * 8));
+    RET(ensure(c, c->svb_words, 16));
+    RET(ensure_host(c, c->h_svb_err, 16));
+    cudaStream_t st = c->stream;
+    if (svb->n_bytes) CU(c, cudaMemcpyAsync(c->svb_blob.p, svb->bytes, (size_t)svb->n_bytes, cudaMemcpyHostToDevice, st));
+    CU(c, cudaMemsetAsync(c->svb_words.p, 0, 16, st));
+    if (R) {
+        if (svb->off[R] > svb->n_bytes) return fail(c, PGM_ERR_ARG, "pgm_svb.off[n_reads] exceeds n_bytes");
+        CU(c, cudaMemcpyAsync(c->svb_off.p, svb->off, (size_t)(R + 1) * 8, cudaMemcpyHostToDevice, st));
+        StageTimer t(c, PGM_STAGE_SVB);
+        SvbIO io;
+        io.blob = P<uint8_t>(c->svb_blob); io.blob_off = P<unsigned long long>(c->svb_off); io.reads = P<pgm_read>(c->reads);
+        io.raw = P<int16_t>(c->raw); io.n_raw = b->n_raw; io.n_reads = R;
+        io.ticket = P<uint32_t>(c->svb_words); io.err = P<uint32_t>(c->svb_words) + 1;
+        const uint32_t grid = (uint32_t)std::min<uint64_t>(cdiv(R, SVB_WARPS), (uint64_t)c->n_sm * 8);
+        k_svb_decode<<<grid, SVB_WARPS * 32, 0, st>>>(io);
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
+    c->svb_used = true;
     c->state = ST_LOADED;
     return PGM_OK;
 }
@@ -727,6 +773,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     cudaStream_t st = c->stream;
     const uint32_t R = c->db.n_reads, NS = c->opts.n_slots;
     CU(c, cudaMemcpyAsync(c->h_scalars, SCALARS(c), sizeof(Scalars), cudaMemcpyDeviceToHost, st));
+    if (c->svb_used) CU(c, cudaMemcpyAsync(c->h_svb_err.p, P<uint32_t>(c->svb_words) + 1, 4, cudaMemcpyDeviceToHost, st));
     RET(ensure_host(c, c->h_slot_sel, (size_t)NS * 4));
     RET(ensure_host(c, c->h_slot_total, (size_t)NS * 4));
     RET(ensure_host(c, c->h_rflags, R ? R : 1));
@@ -736,6 +783,8 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     CU(c, cudaStreamSynchronize(st));
     const Scalars s = *c->h_scalars;
     if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays");
+    if (c->svb_used && *P<uint32_t>(c->h_svb_err))
+        return fail(c, PGM_ERR_INPUT, "svb-zd stream of a record does not decode to its raw_len samples");
     if (s.n_pass > c->ev_cap || s.n_sel_samples > c->samples_cap)
         return fail(c, PGM_ERR_INPUT, "internal capacity exceeded (events %u/%u, samples %llu/%llu)", s.n_pass, c->ev_cap,
                     s.n_sel_samples, (unsigned long long)c->samples_cap);
@@ -796,7 +845,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     return PGM_OK;
 }
 
-static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode", "scan", "place", "sort", "select", "stats", "gather", "misc", "text"};
+static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode", "scan", "place", "sort", "select", "stats", "gather", "misc", "text", "svb"};
 
 const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }
 
@@ -882,6 +931,19 @@ int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **ro
     CU(c, cudaMemcpyAsync(c->h_model_rows.data(), c->model_rows.p, (size_t)NS * sizeof(pgm_model_row), cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     *rows_out = c->h_model_rows.data();
+    return PGM_OK;
+}
+
+int pgm_debug_raw(pgm_ctx *c, int16_t *out, uint64_t n) {
+    if (!c || (!out && n)) return PGM_ERR_ARG;
+    if (c->state == ST_IDLE) return fail(c, PGM_ERR_STATE, "pgm_debug_raw needs a loaded batch");
+    if (n > c->db.n_raw) return fail(c, PGM_ERR_ARG, "pgm_debug_raw: n exceeds the batch's n_raw");
+    CU(c, cudaSetDevice(c->device));
+    if (n) CU(c, cudaMemcpyAsync(out, c->db.raw, (size_t)n * 2, cudaMemcpyDeviceToHost, c->stream));
+    if (c->svb_used) CU(c, cudaMemcpyAsync(c->h_svb_err.p, P<uint32_t>(c->svb_words) + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    if (c->svb_used && *P<uint32_t>(c->h_svb_err))
+        return fail(c, PGM_ERR_INPUT, "svb-zd stream of a record does not decode to its raw_len samples");
     return PGM_OK;
 }
 

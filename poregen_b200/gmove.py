@@ -78,6 +78,24 @@ class GmoveEngine:
         cb = batch.to_c()
         self._chk(self.lib.pgm_upload(self._ctx, C.byref(cb)))
 
+    def upload_svb(self, batch: ReadBatch, stream_bytes: np.ndarray, stream_off: np.ndarray):
+        """pgm_upload_svb: the records' svb-zd streams travel instead of raw[]; the samples are decoded in HBM."""
+        self._batch_keep = (batch, stream_bytes, stream_off)
+        cb = batch.to_c()
+        cb.raw = None
+        sv = capi.PgmSvb()
+        sv.n_bytes = int(stream_bytes.size)
+        sv.bytes = stream_bytes.ctypes.data
+        sv.off = stream_off.ctypes.data
+        assert stream_bytes.dtype == np.uint8 and stream_off.dtype == np.uint64 and stream_off.size == batch.n_reads + 1
+        self._chk(self.lib.pgm_upload_svb(self._ctx, C.byref(cb), C.byref(sv)))
+
+    def device_raw(self, n: int) -> np.ndarray:
+        """Test hook (pgm_debug_raw): the loaded batch's first n samples as the device holds them."""
+        out = np.empty(n, dtype=np.int16)
+        self._chk(self.lib.pgm_debug_raw(self._ctx, out.ctypes.data, n))
+        return out
+
     def attach_device(self, cbatch: capi.PgmBatch, keep=None):
         self._batch_keep = keep
         self._chk(self.lib.pgm_attach_device(self._ctx, C.byref(cbatch)))

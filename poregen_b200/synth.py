@@ -289,6 +289,50 @@ def write_alignment(batch: ReadBatch, outdir: str) -> dict:
     return res
 
 
+def svb_zd_encode(x: np.ndarray) -> bytes:
+    """One signal as slow5lib stores it under signal_press svb-zd (reference slow5lib/src/slow5_press.c:1034-1083:
+    u32 count, then StreamVByte keys and data of the zig-zag coded differences, thirdparty/streamvbyte/src/
+    streamvbyte_encode.c and streamvbyte_zigzag.c:19-32). numpy, for test and bench inputs."""
+    x = np.ascontiguousarray(x, dtype=np.int16).astype(np.int32)
+    n = x.size
+    d = np.diff(x, prepend=np.int32(0))
+    z = ((d << 1) ^ (d >> 31)).astype(np.uint32)
+    code = (z > 0xFF).astype(np.uint8) + (z > 0xFFFF).astype(np.uint8) + (z > 0xFFFFFF).astype(np.uint8)
+    kc = np.zeros((n + 3) // 4 * 4, dtype=np.uint8)
+    kc[:n] = code
+    kc = kc.reshape(-1, 4)
+    keys = (kc[:, 0] | (kc[:, 1] << 2) | (kc[:, 2] << 4) | (kc[:, 3] << 6)).astype(np.uint8)
+    b4 = z.astype("<u4").view(np.uint8).reshape(-1, 4)
+    keep = np.arange(4, dtype=np.uint8)[None, :] <= code[:, None]
+    return np.uint32(n).tobytes() + keys.tobytes() + b4[keep].tobytes()
+
+
+def svb_streams(batch: ReadBatch):
+    """(bytes uint8[], off uint64[R+1]): every record's signal as its svb-zd stream, concatenated."""
+    parts, off = [], [0]
+    for r in batch.reads:
+        o, n = int(r["raw_off"]), int(r["raw_len"])
+        parts.append(svb_zd_encode(batch.raw[o:o + n]))
+        off.append(off[-1] + len(parts[-1]))
+    blob = np.frombuffer(b"".join(parts), dtype=np.uint8).copy() if parts else np.zeros(0, np.uint8)
+    return blob, np.asarray(off, dtype=np.uint64)
+
+
+def align_raw(batch: ReadBatch, align: int = 8) -> ReadBatch:
+    """The same records with every raw_off rounded up to a multiple of `align` samples (the gaps are zero): the layout
+    a host that assembles batches for pgm_upload_svb picks, so that the decoder's stores are 16-byte aligned."""
+    reads = batch.reads.copy()
+    lens = reads["raw_len"].astype(np.int64)
+    padded = (lens + align - 1) // align * align
+    offs = np.concatenate([[0], np.cumsum(padded)[:-1]]) if lens.size else np.zeros(0, np.int64)
+    raw = np.zeros(int(padded.sum()), np.int16)
+    for r, o in zip(reads, offs):
+        n = int(r["raw_len"])
+        raw[o:o + n] = batch.raw[int(r["raw_off"]):int(r["raw_off"]) + n]
+    reads["raw_off"] = offs.astype(np.uint64)
+    return ReadBatch(batch.mode, raw, batch.align, batch.bases, reads, batch.read_ids)
+
+
 def write_blow5(batch: ReadBatch, path: str) -> None:
     """Uncompressed binary BLOW5 (record_press none, signal_press none), layout as slow5lib
     serialises it (reference slow5lib/src/slow5.c:946-1147 header, :3907-4033 record, EOF marker

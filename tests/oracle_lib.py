@@ -56,7 +56,56 @@ def lib():
         _lib.oracle_model_row.restype = C.c_int
         _lib.oracle_model_row_text.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p, C.c_char_p]
         _lib.oracle_model_row_text.restype = C.c_size_t
+        _lib.oracle_svb_zd_decode.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p]
+        _lib.oracle_svb_zd_decode.restype = C.c_int
     return _lib
+
+
+def svb_zd_decode(stream: bytes, expect: int):
+    """oracle_svb_zd_decode: int16 samples of one svb-zd stream, or None where slow5lib reports an error."""
+    buf = np.frombuffer(stream, dtype=np.uint8)
+    out = np.empty(max(expect, 1), dtype=np.int16)
+    rc = lib().oracle_svb_zd_decode(buf.ctypes.data if buf.size else None, buf.size, expect, out.ctypes.data)
+    return out[:expect] if rc == 0 else None
+
+
+SVBREF_SO = os.path.join(ORACLE_DIR, "_ref", "libsvbref.so")
+_svbref = None
+
+
+def svbref():
+    """slow5lib's own svb-zd compress/depress (oracle/_ref/libsvbref.so, built by oracle/build_ref.sh), or None."""
+    global _svbref
+    if _svbref is None and os.path.exists(SVBREF_SO):
+        L = C.CDLL(SVBREF_SO)
+        L.svbref_compress.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.svbref_compress.restype = C.c_void_p
+        L.svbref_depress.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.svbref_depress.restype = C.c_void_p
+        L.svbref_free.argtypes = [C.c_void_p]
+        _svbref = L
+    return _svbref
+
+
+def svbref_compress(x: np.ndarray) -> bytes:
+    L = svbref()
+    x = np.ascontiguousarray(x, dtype=np.int16)
+    n = C.c_size_t(0)
+    p = L.svbref_compress(x.ctypes.data, x.size, C.byref(n))
+    out = C.string_at(p, n.value)
+    L.svbref_free(p)
+    return out
+
+
+def svbref_depress(stream: bytes):
+    L = svbref()
+    n = C.c_size_t(0)
+    p = L.svbref_depress(stream, len(stream), C.byref(n))
+    if not p:
+        return None
+    out = np.frombuffer(C.string_at(p, n.value), dtype=np.int16).copy()
+    L.svbref_free(p)
+    return out
 
 
 def model_row_text(text: bytes, limit: float):
