@@ -245,6 +245,9 @@ uint64_t pgm_launch_count(const pgm_ctx *ctx);
 #define PGM_STAGE_TEXT 9         /* PGM_OUT_TEXT: k_text_len, k_scan_text (k_text_write runs in pgm_download) */
 #define PGM_STAGE_SVB 10         /* k_svb_decode (pgm_upload_svb)                                   */
 #define PGM_N_STAGES 11
+#define PGM_PROFILE_ONLY(stage) (2 + (stage)) /* pgm_profile_enable(ctx, PGM_PROFILE_ONLY(s)): bracket stage s alone. Every
+                                                  event pair costs a few microseconds of stream time; a timed region that
+                                                  wants one kernel's duration should not pay for ten. */
 int pgm_profile_enable(pgm_ctx *ctx, int on);
 int pgm_profile_read(pgm_ctx *ctx, float *ms, uint32_t *launches);
 const char *pgm_stage_name(int stage);

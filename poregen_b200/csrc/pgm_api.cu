@@ -80,6 +80,7 @@ struct pgm_ctx {
     DBuf raw, align, bases, reads;
     DBuf svb_blob, svb_off, svb_words;        // pgm_upload_svb: streams, their offsets, {ticket, error} words
     bool svb_used = false;
+    uint32_t gather_ctas = 0;                 // resident k_gather CTAs per SM (occupancy query, first pgm_emit)
     DBuf h_svb_err;
     uint32_t ev_cap = 0;
     uint64_t samples_cap = 0;
@@ -104,6 +105,7 @@ struct pgm_ctx {
 
     // optional per-stage event timing
     bool prof = false;
+    int prof_only = -1;      // >= 0: only this stage is bracketed (pgm_profile_enable(ctx, PGM_PROFILE_ONLY(stage)))
     struct Span { int stage; cudaEvent_t a, b; uint32_t launches; };
     std::vector<Span> spans;
     std::vector<cudaEvent_t> ev_pool;
@@ -180,7 +182,7 @@ struct StageTimer {
     }
     cudaStream_t s;
     StageTimer(pgm_ctx *c_, int stage_, cudaStream_t s_ = nullptr) : c(c_), stage(stage_), l0(c_->launches), s(s_ ? s_ : c_->stream) {
-        if (!c->prof) return;
+        if (!c->prof || (c->prof_only >= 0 && c->prof_only != stage)) return;
         a = get(c); b = get(c);
         cudaEventRecord(a, s);
     }
@@ -739,8 +741,16 @@ int pgm_emit(pgm_ctx *c) {
         g.sel_src = P<unsigned long long>(c->sel_src); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
         g.sel_off = P<uint64_t>(c->sel_off); g.n_sel = P<uint32_t>(c->sel_base) + NS; g.cal = P<ReadCal>(c->cal);
         g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
-        if (c->opts.scaling) k_gather<true><<<c->n_sm * 5, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
-        else k_gather<false><<<c->n_sm * 5, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
+        if (!c->gather_ctas) {   // resident CTAs per SM of the instantiation in use (registers and shared memory decide)
+            int nb = 0;
+            const size_t sm = sizeof(GatherStage) * GATHER_WARPS;
+            if (c->opts.scaling) CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gather<true>, GATHER_WARPS * 32, sm));
+            else CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gather<false>, GATHER_WARPS * 32, sm));
+            c->gather_ctas = nb > 0 ? (uint32_t)nb : 1u;
+        }
+        const uint32_t ggrid = (uint32_t)c->n_sm * c->gather_ctas;
+        if (c->opts.scaling) k_gather<true><<<ggrid, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
+        else k_gather<false><<<ggrid, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
         c->launches++;
     }
     if (c->opts.output != PGM_OUT_F64) {
@@ -852,6 +862,7 @@ const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAG
 int pgm_profile_enable(pgm_ctx *c, int on) {
     if (!c) return PGM_ERR_ARG;
     c->prof = on != 0;
+    c->prof_only = (on >= 2 && on - 2 < PGM_N_STAGES) ? on - 2 : -1;
     return PGM_OK;
 }
 

@@ -399,7 +399,10 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 }
 
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PGM_BLOCK) k_decode(DevOpts o, DevBatch b, DecodeIO io) {
+#ifndef DEC_MIN_CTAS
+#define DEC_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(PGM_BLOCK, DEC_MIN_CTAS) k_decode(DevOpts o, DevBatch b, DecodeIO io) {
     __shared__ __align__(16) uint8_t sm_w[DEC_WARPS][DEC_WSM];   // per-warp staging (tokeniser, then evaluation tiles)
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t exam = 0;

@@ -44,8 +44,13 @@ struct ReadCal {
 
 // ---------------------------------------------------------------- pA and the in-range interval
 // TO_PICOAMPS (reference src/poregen.h:30): ((raw)+(offset))*((range)/(digitisation))
+// (double)c for any int32 without the conversion unit: 2^52 + 2^31 + c is exactly representable with the mantissa
+// bits 0x80000000 ^ c, and subtracting the constant back is exact. I2F.F64 shares a narrow pipe; DADD does not.
+__device__ __forceinline__ double pgm_i2d(int c) {
+    return __dsub_rn(__hiloint2double(0x43300000, (int)((uint32_t)c ^ 0x80000000u)), 4503601774854144.0);
+}
 __device__ __forceinline__ double pgm_pa(int c, double offset, double scale) {
-    return __dmul_rn(__dadd_rn((double)c, offset), scale);
+    return __dmul_rn(__dadd_rn(pgm_i2d(c), offset), scale);
 }
 
 // pA(c) is monotone in c (each fp op is monotone), non-decreasing for scale>=0 and non-increasing

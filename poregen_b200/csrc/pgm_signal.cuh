@@ -445,22 +445,30 @@ __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shf
 // arrive by cp.async while this one is converted), the 32 events as structure-of-arrays, and the map from
 // an output position of the batch (window of GATHER_MAP positions) to its event.
 #define GATHER_WARPS 4
-#define GATHER_MAP 1536
+#ifndef GATHER_MIN_CTAS
+#define GATHER_MIN_CTAS 5
+#endif
+#ifndef GATHER_UNROLL
+#define GATHER_UNROLL 3         // group iterations in flight per lane: the dependent shared-memory loads of one hide behind the other
+#endif
+#define GATHER_MAP 512
 #define GATHER_CH 6                         // 16-byte chunks staged per event: covers 41 samples at the worst alignment
 #define GATHER_EV_SAMPLES (GATHER_CH * 8)
+constexpr int kGatherUnroll = GATHER_UNROLL;
 struct __align__(16) GatherEvP {   // 64 bytes, read with four 16-byte shared-memory loads
     double offset, scale;
     double med, mad;
     double rcp;
     int clo; uint32_t nbins;
-    int sidx;                 // index into the staged copy of output position 0 of the batch
-    uint32_t slim;            // positions below this one are staged (rel + staged samples)
-    uint32_t fast, pad;
+    uint32_t gstart;          // first group of the event (numbering inside the batch)
+    uint32_t len;             // samples of the event
+    uint32_t rel;             // output position of its first sample, relative to the batch's first
+    uint32_t packed;          // bits 0-10 index of sample 0 in the staged copy | 11-16 samples staged | 17 fast division | 18 odd start
 };
 struct GatherStage {
     int16_t raw[2][32 * GATHER_EV_SAMPLES];
     GatherEvP ev[32];
-    long long base[32];       // raw[] index of output position 0 of the batch as seen from this event: src - rel
+    long long base[32];       // raw[] index of the event's first sample
     uint8_t map[GATHER_MAP];
 };
 
@@ -477,7 +485,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // (byte map) -> staged raw sample -> double -> coalesced 256-byte stores; every lane converts a sample in every
 // step, whatever the event lengths are.
 template <bool SCALING>
-__global__ void __launch_bounds__(GATHER_WARPS * 32) k_gather(DevOpts o, DevBatch b, GatherIO io) {
+__global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(DevOpts o, DevBatch b, GatherIO io) {
     extern __shared__ __align__(16) uint8_t sm_gather[];
     GatherStage &S = reinterpret_cast<GatherStage *>(sm_gather)[threadIdx.x >> 5];
     const uint32_t n = *io.n_sel;
@@ -524,24 +532,26 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32) k_gather(DevOpts o, DevBatc
     level2(0);
     if (q0 + stride < n) level1(q0 + stride);
     for (uint32_t buf = 0;; buf ^= 1) {
-        // ---- publish the batch
+        // ---- publish the batch. The unit of the walk is a GROUP: four consecutive output positions of ONE event that
+        // start on an even index of samples[] (so a group is two 16-byte stores); an event that starts on an odd index
+        // has an empty first slot. Lane j owns event j: it counts the event's groups, a warp scan numbers them.
         const uint32_t ln = ln2;
         const uint64_t out0 = __shfl_sync(PGM_FULL, (unsigned long long)off2, 0);        // first output position of the batch
         const uint32_t rel = (uint32_t)(off2 - out0);
-        const uint32_t endrel = ln ? rel + ln : 0u;
-        uint32_t total = endrel;
-#pragma unroll
-        for (int d = 16; d; d >>= 1) total = max(total, __shfl_xor_sync(PGM_FULL, total, d));
-        S.base[lane] = (long long)src2 - (long long)rel;
+        const uint32_t par = (uint32_t)(off2 & 1);
+        const uint32_t ng = ln ? (ln + par + 3) >> 2 : 0u;
+        const uint32_t ginc = warp_incl_scan_add(ng);
+        const uint32_t gstart = ginc - ng;
+        const uint32_t total = __shfl_sync(PGM_FULL, ginc, 31);      // groups in the batch
+        S.base[lane] = (long long)src2;
         {
             GatherEvP ev;
             ev.offset = offset2; ev.scale = scale2; ev.med = med2; ev.mad = mad2;
             ev.rcp = SCALING ? __drcp_rn(mad2) : 1.0;
             ev.clo = clo2; ev.nbins = (chi2 >= clo2) ? (uint32_t)(chi2 - clo2 + 1) : 0u;
-            ev.sidx = (int)(lane * GATHER_EV_SAMPLES + (uint32_t)(src2 & 7)) - (int)rel;
-            ev.slim = rel + nst2;
-            ev.fast = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
-            ev.pad = 0;
+            ev.gstart = gstart; ev.len = ln; ev.rel = rel;
+            const uint32_t fast = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
+            ev.packed = (lane * GATHER_EV_SAMPLES + (uint32_t)(src2 & 7)) | (nst2 << 11) | (fast << 17) | (par << 18);
             S.ev[lane] = ev;
         }
         const bool all_staged = __all_sync(PGM_FULL, nst2 == ln);   // no event of the batch longer than its staged copy
@@ -552,35 +562,56 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32) k_gather(DevOpts o, DevBatc
             if (q0 + 2 * stride < n) level1(q0 + 2 * stride);
         }
         const int16_t *staged = S.raw[buf];
-        // ---- walk the batch's output range window by window
+        // ---- walk the batch's groups window by window: lane -> group -> event (byte map) -> four staged samples ->
+        // four independent conversions -> two 16-byte stores
         for (uint32_t w0 = 0; w0 < total; w0 += GATHER_MAP) {
             __syncwarp();
-            const uint32_t lo = max(rel, w0), hi = min(endrel, w0 + GATHER_MAP);
+            const uint32_t lo = max(gstart, w0), hi = min(gstart + ng, w0 + GATHER_MAP);
             for (uint32_t t = lo; t < hi; t++) S.map[t - w0] = (uint8_t)lane;
             __syncwarp();
             const uint32_t wend = min(total, w0 + GATHER_MAP);
-            auto convert = [&](uint32_t p, auto fetch) {
-                const uint32_t e = S.map[p - w0];
-                const uint4 *ep = reinterpret_cast<const uint4 *>(&S.ev[e]);
-                const uint4 a0 = ep[0], a1 = ep[1], a2 = ep[2], a3 = ep[3];
-                SigConv cv;
-                cv.offset = __hiloint2double((int)a0.y, (int)a0.x); cv.scale = __hiloint2double((int)a0.w, (int)a0.z);
-                cv.med = __hiloint2double((int)a1.y, (int)a1.x); cv.mad = __hiloint2double((int)a1.w, (int)a1.z);
-                cv.rcp = __hiloint2double((int)a2.y, (int)a2.x); cv.clo = (int)a2.z; cv.nbins = a2.w;
-                cv.scaling = SCALING; cv.fast_div = a3.z != 0;
-                const int code = fetch(e, (int)a3.x, a3.y);
-                io.samples[out0 + p] = cv(code);
+            auto walk = [&](auto fetch) {
+#pragma unroll kGatherUnroll
+                for (uint32_t g = w0 + lane; g < wend; g += 32) {
+                    const uint32_t e = S.map[g - w0];
+                    const uint4 *ep = reinterpret_cast<const uint4 *>(&S.ev[e]);
+                    const uint4 a0 = ep[0], a1 = ep[1], a2 = ep[2], a3 = ep[3];
+                    SigConv cv;
+                    cv.scaling = SCALING;
+                    cv.offset = __hiloint2double((int)a0.y, (int)a0.x); cv.scale = __hiloint2double((int)a0.w, (int)a0.z);
+                    cv.med = __hiloint2double((int)a1.y, (int)a1.x); cv.mad = __hiloint2double((int)a1.w, (int)a1.z);
+                    cv.rcp = __hiloint2double((int)a2.y, (int)a2.x); cv.clo = (int)a2.z; cv.nbins = a2.w;
+                    cv.fast_div = ((a3.w >> 17) & 1u) != 0;
+                    const uint32_t len = a3.y;
+                    const int sidx = (int)(a3.w & 0x7ffu);
+                    const uint32_t nst = (a3.w >> 11) & 0x3fu;
+                    const int t0 = (int)(4u * (g - a3.x)) - (int)((a3.w >> 18) & 1u);   // event sample in the group's first slot
+                    double o4[4];
+                    bool ok[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        ok[i] = (uint32_t)(t0 + i) < len;
+                        const uint32_t t = ok[i] ? (uint32_t)(t0 + i) : 0u;
+                        o4[i] = cv(fetch(e, sidx, nst, t));
+                    }
+                    double *dst = io.samples + out0 + a3.z + (long long)t0;
+                    if (ok[0] && ok[1]) *reinterpret_cast<double2 *>(dst) = make_double2(o4[0], o4[1]);
+                    else {
+                        if (ok[0]) dst[0] = o4[0];
+                        if (ok[1]) dst[1] = o4[1];
+                    }
+                    if (ok[2] && ok[3]) *reinterpret_cast<double2 *>(dst + 2) = make_double2(o4[2], o4[3]);
+                    else {
+                        if (ok[2]) dst[2] = o4[2];
+                        if (ok[3]) dst[3] = o4[3];
+                    }
+                }
             };
-            if (all_staged) {
-#pragma unroll 2
-                for (uint32_t p = w0 + lane; p < wend; p += 32)
-                    convert(p, [&](uint32_t, int sidx, uint32_t) { return (int)staged[sidx + (int)p]; });
-            } else {   // some event is longer than GATHER_EV_SAMPLES: its tail comes from global memory
-                for (uint32_t p = w0 + lane; p < wend; p += 32)
-                    convert(p, [&](uint32_t e, int sidx, uint32_t slim) {
-                        return (p < slim) ? (int)staged[sidx + (int)p] : (int)b.raw[S.base[e] + (long long)p];
-                    });
-            }
+            if (all_staged) walk([&](uint32_t, int sidx, uint32_t, uint32_t t) { return (int)staged[sidx + (int)t]; });
+            else   // some event is longer than its staged copy: the tail comes from global memory
+                walk([&](uint32_t e, int sidx, uint32_t nst, uint32_t t) {
+                    return (t < nst) ? (int)staged[sidx + (int)t] : (int)b.raw[S.base[e] + (long long)t];
+                });
         }
         if (!more) break;
         q0 += stride;

@@ -146,8 +146,13 @@ class GmoveEngine:
         buf = (C.c_char * (n * 40)).from_address(p.value)
         return np.frombuffer(buf, dtype=np.dtype(capi.MODEL_ROW_DTYPE), count=n).copy()
 
-    def profile_enable(self, on: bool = True):
-        self._chk(self.lib.pgm_profile_enable(self._ctx, 1 if on else 0))
+    def profile_enable(self, on: bool = True, only: Optional[str] = None):
+        """Stage timers on/off; `only` = a stage name: bracket that stage alone (PGM_PROFILE_ONLY)."""
+        mode = 1 if on else 0
+        if on and only is not None:
+            names = [self.lib.pgm_stage_name(i).decode() for i in range(capi.PGM_N_STAGES)]
+            mode = 2 + names.index(only)
+        self._chk(self.lib.pgm_profile_enable(self._ctx, mode))
 
     def profile_read(self) -> dict:
         """{stage name: (ms, launches)} accumulated since the last read (synchronises)."""

@@ -6,3 +6,8 @@ b=synth.make_batch(cfg)
 with GmoveEngine(opts) as e:
     for i in range(2):
         e.upload(b); e.count(); e.emit(); e.sync()
+    if "svb" in sys.argv[1:]:
+        ab = synth.align_raw(b, 8)
+        blob, off = synth.svb_streams(ab)
+        for i in range(2):
+            e.upload_svb(ab, blob, off); e.sync()
