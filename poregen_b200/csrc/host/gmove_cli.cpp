@@ -78,6 +78,7 @@ struct Opt {
     uint64_t batch_samples = 64ull << 20;
     const char *model_out = nullptr;   // --model FILE: kmer<TAB>median<TAB>stddev (scripts/poregen.sh:54-85)
     double stddev_limit = 1e300;
+    int host_signal = 0;          // --host-signal-decode: let slow5lib decompress the signal (default: svb-zd streams go to the GPU)
 };
 
 void print_help(FILE *fp, const Opt &o) {
@@ -110,6 +111,7 @@ void print_help(FILE *fp, const Opt &o) {
     fprintf(fp, "   --batch-samples INT        raw samples per device batch [%" PRIu64 "]\n", o.batch_samples);
     fprintf(fp, "   --model FILE               also write kmer<TAB>median<TAB>stddev per dumped k-mer (calculate_mean_stddev_all of scripts/poregen.sh)\n");
     fprintf(fp, "   --stddev_limit FLOAT       upper clamp of the stddev column [none]\n");
+    fprintf(fp, "   --host-signal-decode       decompress svb-zd signals with slow5lib on the host instead of on the GPU\n");
 }
 
 // 0 created / exists and empty, -1 exists and not empty, -2 cannot create (reference gmove.cpp:126-140)
@@ -365,8 +367,11 @@ struct Batch {
     Pinned<int16_t> raw;
     Pinned<uint8_t> align, bases;
     Pinned<pgm_read> reads;
+    Pinned<uint8_t> svb;          // device signal decode: the records' svb-zd streams instead of raw[]
+    Pinned<uint64_t> svb_off;
+    bool use_svb = false;
     uint64_t samples = 0;
-    void clear() { recs.clear(); raw.clear(); align.clear(); bases.clear(); reads.clear(); samples = 0; }
+    void clear() { recs.clear(); raw.clear(); align.clear(); bases.clear(); reads.clear(); svb.clear(); svb_off.clear(); use_svb = false; samples = 0; }
 };
 
 struct Gpu {
@@ -380,6 +385,7 @@ struct Run {
     std::vector<std::string> kmers;     // full list; dumped range = [index_start-1, index_end)
     std::string dump_dir;
     slow5_file_t *sp = nullptr;
+    bool device_signal = false;         // BLOW5 with signal_press svb-zd: the streams are decoded by k_svb_decode
     std::vector<Gpu> gpus;
     std::vector<uint32_t> totals;       // kmer_frequency_map of the dumped range
     uint32_t n_slots = 0;
@@ -388,9 +394,120 @@ struct Run {
     double t_read = 0, t_dev = 0, t_write = 0, t_create = 0, t_parse = 0, t_start = 0, t_close = 0;
 };
 
+// slow5lib entry points below the public header (declared in slow5lib/src/slow5_extra.h:60 and
+// include/slow5/slow5_press.h:105; both are exported by libslow5.a): the record's bytes as stored, and the
+// record-level decompressor. slow5_get is these two followed by slow5_rec_parse (slow5lib/src/slow5.c:2519-2530).
+extern "C" void *slow5_get_mem(const char *read_id, size_t *n, const slow5_file_t *s5p);
+
+// One BLOW5 record as slow5_rec_parse reads it (slow5lib/src/slow5.c:2801-2905), stopping at raw_signal: with
+// signal_press svb-zd the field holds the compressed stream and len_raw_signal its BYTE length; the sample count
+// is the stream's first word (slow5_press.c:1086-1087).
+struct RawRec {
+    char *mem = nullptr;          // malloc'd by slow5lib
+    const uint8_t *stream = nullptr;
+    uint64_t stream_len = 0;
+    uint32_t n_samples = 0;
+    double digitisation = 0, offset = 0, range = 0;
+};
+
+static bool fetch_raw_record(const Run &R, const char *read_id, RawRec *out) {
+    size_t bytes = 0;
+    char *mem = (char *)slow5_get_mem(read_id, &bytes, R.sp);
+    if (!mem) return false;
+    const enum slow5_press_method rp = R.sp->compress ? R.sp->compress->record_press->method : SLOW5_COMPRESS_NONE;
+    if (rp != SLOW5_COMPRESS_NONE) {
+        size_t nb = 0;
+        char *plain = (char *)slow5_ptr_depress_solo(rp, mem, bytes, &nb);
+        free(mem);
+        if (!plain || !nb) { free(plain); return false; }
+        mem = plain; bytes = nb;
+    }
+    size_t o = 0;
+    uint16_t idlen = 0;
+    if (bytes < 2) { free(mem); return false; }
+    memcpy(&idlen, mem, 2); o = 2 + (size_t)idlen + 4;                 // read_id, read_group
+    if (o + 4 * 8 + 8 > bytes) { free(mem); return false; }
+    double samp = 0;
+    memcpy(&out->digitisation, mem + o, 8); memcpy(&out->offset, mem + o + 8, 8); memcpy(&out->range, mem + o + 16, 8);
+    memcpy(&samp, mem + o + 24, 8);
+    uint64_t len = 0;
+    memcpy(&len, mem + o + 32, 8);
+    o += 40;
+    if (len < 4 || o + len > bytes) { free(mem); return false; }
+    out->mem = mem; out->stream = (const uint8_t *)mem + o; out->stream_len = len;
+    memcpy(&out->n_samples, out->stream, 4);
+    return true;
+}
+
+// Device signal decode: the batch carries every record's svb-zd stream (pgm_upload_svb); nothing is decompressed here.
+void assemble_svb(Run &R, Batch &b) {
+    const size_t n = b.recs.size();
+    std::vector<RawRec> recs(n);
+    int nt = R.opt.threads > 0 ? R.opt.threads : (int)std::thread::hardware_concurrency();
+    nt = std::max(1, std::min<int>(nt, (int)n));
+    std::atomic<size_t> next(0);
+    std::atomic<int> failed(0);
+    auto work = [&]() {
+        for (;;) {
+            const size_t i = next.fetch_add(1);
+            if (i >= n) break;
+            if (!fetch_raw_record(R, b.recs[i].read_id.c_str(), &recs[i])) failed = 1;         // gmove.cpp:582
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; t++) th.emplace_back(work);
+    work();
+    for (auto &t : th) t.join();
+    if (failed) { fprintf(stderr, "Error in when fetching the read\n"); exit(EXIT_FAILURE); }
+    uint64_t nraw = 0, nal = 0, nb = 0, nsv = 0;
+    b.reads.resize(n);
+    b.svb_off.resize(n + 1);
+    for (size_t i = 0; i < n; i++) {
+        const Rec &r = b.recs[i];
+        const RawRec &s = recs[i];
+        if (r.check_len && s.n_samples != r.signal_len)                                         // assert gmove.cpp:589
+            DIE("read %s: signal length %" PRIu64 " in the alignment, %" PRIu64 " in the SLOW5 record", r.read_id.c_str(), r.signal_len, (uint64_t)s.n_samples);
+        pgm_read &d = b.reads.p[i];
+        memset(&d, 0, sizeof d);
+        d.raw_off = nraw; d.raw_len = s.n_samples;
+        d.align_off = nal; d.align_len = (uint32_t)r.align.size();
+        d.seq_off = nb; d.seq_len = (uint32_t)r.bases.size();
+        d.trim = r.trim; d.stride = r.stride; d.fastq_len = r.fastq_len; d.query_start = r.query_start;
+        d.st_k = r.st_k; d.end_k = r.end_k; d.flags = r.flags;
+        d.digitisation = s.digitisation; d.offset = s.offset; d.range = s.range;
+        b.svb_off.p[i] = nsv;
+        nraw += ((uint64_t)s.n_samples + 7) & ~(uint64_t)7;
+        nal += (r.align.size() + 15) & ~(size_t)15;
+        nb += r.bases.size();
+        nsv += s.stream_len;
+    }
+    b.svb_off.p[n] = nsv;
+    b.raw.n = nraw;                                  // layout only: raw[] exists on the device
+    b.svb.resize(nsv); b.align.resize(nal); b.bases.resize(nb);
+    next = 0;
+    auto copy = [&]() {
+        for (;;) {
+            const size_t i = next.fetch_add(1);
+            if (i >= n) break;
+            const pgm_read &d = b.reads.p[i];
+            memcpy(b.svb.p + b.svb_off.p[i], recs[i].stream, (size_t)recs[i].stream_len);
+            memcpy(b.align.p + d.align_off, b.recs[i].align.data(), d.align_len);
+            memcpy(b.bases.p + d.seq_off, b.recs[i].bases.data(), d.seq_len);
+            free(recs[i].mem);
+        }
+    };
+    th.clear();
+    for (int t = 1; t < nt; t++) th.emplace_back(copy);
+    copy();
+    for (auto &t : th) t.join();
+    b.samples = nraw;
+    b.use_svb = true;
+}
+
 // Fetches the signal of every record of the batch on host threads and lays the batch out for the device:
 // records start on 16-byte boundaries of raw[] (the kernels stream aligned 16-byte words).
 void assemble(Run &R, Batch &b) {
+    if (R.device_signal) { assemble_svb(R, b); return; }
     const size_t n = b.recs.size();
     std::vector<slow5_rec_t *> recs(n, nullptr);
     int nt = R.opt.threads > 0 ? R.opt.threads : (int)std::thread::hardware_concurrency();
@@ -535,7 +652,15 @@ void process_batch(Run &R, Batch &b) {
             pb.align += al0; pb.n_align = al1 - al0;
             pb.bases += sq0; pb.n_bases = sq1 - sq0;
         }
-        check(gp.ctx, pgm_upload(gp.ctx, &pb));
+        if (b.use_svb) {   // this GPU's streams, offsets relative to the first of them
+            std::vector<uint64_t> off(pb.n_reads + 1);
+            const uint64_t s0 = b.svb_off.p[gp.r0];
+            for (uint32_t i = 0; i <= pb.n_reads; i++) off[i] = b.svb_off.p[gp.r0 + i] - s0;
+            pgm_svb sv;
+            sv.n_bytes = off[pb.n_reads]; sv.bytes = b.svb.p + s0; sv.off = off.data();
+            pb.raw = nullptr;
+            check(gp.ctx, pgm_upload_svb(gp.ctx, &pb, &sv));   // the offsets are pageable: copied before the call returns
+        } else check(gp.ctx, pgm_upload(gp.ctx, &pb));
         check(gp.ctx, pgm_count(gp.ctx));
         if (G > 1) check(gp.ctx, pgm_counts_host(gp.ctx, counts[g].data()));
     };
@@ -583,7 +708,7 @@ void process_batch(Run &R, Batch &b) {
 
 enum { LO_SCALING = 3, LO_MARGIN, LO_SAMPLE_LIMIT, LO_FILE_LIMIT, LO_KMER_FILE, LO_INDEX_START, LO_INDEX_END, LO_FASTQ, LO_D,
        LO_MAX_DUR, LO_MIN_DUR, LO_PA_MIN, LO_PA_MAX, LO_PICK_MARGIN, LO_RNA, LO_VERBOSE, LO_HELP, LO_VERSION, LO_DEBUG_BREAK,
-       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT };
+       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT, LO_HOSTSIG };
 
 const struct option long_options[] = {
     {"kmer_size", required_argument, 0, 'k'},          // 0
@@ -613,6 +738,7 @@ const struct option long_options[] = {
     {"batch-samples", required_argument, 0, 0},        // 24
     {"model", required_argument, 0, 0},                // 25
     {"stddev_limit", required_argument, 0, 0},         // 26
+    {"host-signal-decode", no_argument, 0, 0},         // 27
     {0, 0, 0, 0}};
 
 }  // namespace
@@ -671,6 +797,7 @@ int gmove(int argc, char *argv[]) {
                 case LO_BATCH: opt.batch_samples = strtoull(optarg, nullptr, 10); break;
                 case LO_MODEL: opt.model_out = optarg; break;
                 case LO_SDLIMIT: opt.stddev_limit = atof(optarg); break;
+                case LO_HOSTSIG: opt.host_signal = 1; break;
                 default: break;
             }
         }
@@ -768,6 +895,8 @@ int gmove(int argc, char *argv[]) {
     R.sp = slow5_open(slow5file, "r");
     if (!R.sp) { fprintf(stderr, "Error in opening file %s\n", slow5file); exit(EXIT_FAILURE); }
     if (slow5_idx_load(R.sp) < 0) { fprintf(stderr, "Error in loading index\n"); exit(EXIT_FAILURE); }
+    R.device_signal = !opt.host_signal && R.sp->format == SLOW5_FORMAT_BINARY && R.sp->compress &&
+                      R.sp->compress->signal_press->method == SLOW5_COMPRESS_SVB_ZD;
 
     const std::string mt(move_table);
     const std::string ext = mt.size() >= 4 ? mt.substr(mt.size() - 4) : std::string();
@@ -782,7 +911,9 @@ int gmove(int argc, char *argv[]) {
     // device contexts
     const int ndev = pgm_device_count();
     if (ndev < 1) DIE("no CUDA device: the gmove hot path has no CPU fallback");
-    if (opt.gpus < 1 || opt.gpus > ndev) DIE("--gpus %d but %d device(s) present", opt.gpus, ndev);
+    // PGM_CLI_SHARE_DEVICES=1 (tests on a one-GPU box): --gpus N contexts are spread over the devices that exist
+    const bool share = getenv("PGM_CLI_SHARE_DEVICES") != nullptr;
+    if (opt.gpus < 1 || (opt.gpus > ndev && !share)) DIE("--gpus %d but %d device(s) present", opt.gpus, ndev);
     pgm_opts po;
     memset(&po, 0, sizeof po);
     po.kmer_size = opt.kmer_size; po.sig_move_offset = opt.sig_move_offset; po.kmer_start_offset = opt.kmer_start_offset;
@@ -801,7 +932,7 @@ int gmove(int argc, char *argv[]) {
     const double t_c0 = realtime();
     R.t_start = t_c0 - t_gmove0;
     for (int g = 0; g < opt.gpus; g++)
-        if (pgm_create(&po, g, nullptr, &R.gpus[g].ctx) != PGM_OK) DIE("%s", pgm_last_error(nullptr));
+        if (pgm_create(&po, g % ndev, nullptr, &R.gpus[g].ctx) != PGM_OK) DIE("%s", pgm_last_error(nullptr));
     if (opt.model_out) {
         // a k-mer's values would be spread over the devices: the segmented median needs them in one place
         if (opt.gpus != 1) DIE("%s", "--model needs --gpus 1");

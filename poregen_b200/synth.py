@@ -333,16 +333,20 @@ def align_raw(batch: ReadBatch, align: int = 8) -> ReadBatch:
     return ReadBatch(batch.mode, raw, batch.align, batch.bases, reads, batch.read_ids)
 
 
-def write_blow5(batch: ReadBatch, path: str) -> None:
-    """Uncompressed binary BLOW5 (record_press none, signal_press none), layout as slow5lib
-    serialises it (reference slow5lib/src/slow5.c:946-1147 header, :3907-4033 record, EOF marker
-    slow5_defs.h:133). Much faster to write and read than ASCII for the CPU-baseline sample."""
+def write_blow5(batch: ReadBatch, path: str, signal_press: str = "none", record_press: str = "none") -> None:
+    """Binary BLOW5 as slow5lib serialises it (reference slow5lib/src/slow5.c:946-1147 header, :3907-4033 record, EOF
+    marker slow5_defs.h:133). Default: nothing compressed (fast to write and read for the CPU-baseline sample).
+    signal_press "svb-zd": raw_signal holds the svb-zd stream and len_raw_signal its byte length (slow5lib's default
+    for new files; on-disk code 1, slow5_press.c:46-66); record_press "zlib": every record is one zlib stream (code 1)."""
     import struct
+    import zlib
+    sp = {"none": 0, "svb-zd": 1}[signal_press]
+    rp = {"none": 0, "zlib": 1}[record_press]
     hdr_txt = ("@asic_id\tsynthetic\n@sample_frequency\t4000\n"
                "#char*\tuint32_t\tdouble\tdouble\tdouble\tdouble\tuint64_t\tint16_t*\n"
                "#read_id\tread_group\tdigitisation\toffset\trange\tsampling_rate\tlen_raw_signal\traw_signal\n").encode()
     with open(path, "wb") as f:
-        head = b"BLOW5\x01" + bytes([0, 2, 0]) + bytes([0]) + struct.pack("<I", 1) + bytes([0])
+        head = b"BLOW5\x01" + bytes([0, 2, 0]) + bytes([rp]) + struct.pack("<I", 1) + bytes([sp])
         f.write(head + b"\0" * (64 - len(head)))
         f.write(struct.pack("<I", len(hdr_txt)))
         f.write(hdr_txt)
@@ -350,11 +354,14 @@ def write_blow5(batch: ReadBatch, path: str) -> None:
             r = batch.reads[i]
             n = int(r["raw_len"])
             rb = rid.encode()
-            fixed = struct.pack("<H", len(rb)) + rb + struct.pack("<IddddQ", 0, float(r["digitisation"]), float(r["offset"]),
-                                                                   float(r["range"]), 4000.0, n)
-            f.write(struct.pack("<Q", len(fixed) + 2 * n))
-            f.write(fixed)
-            f.write(batch.raw[int(r["raw_off"]):int(r["raw_off"]) + n].tobytes())
+            sig = batch.raw[int(r["raw_off"]):int(r["raw_off"]) + n]
+            payload = svb_zd_encode(sig) if sp else sig.tobytes()
+            rec = struct.pack("<H", len(rb)) + rb + struct.pack("<IddddQ", 0, float(r["digitisation"]), float(r["offset"]),
+                                                                 float(r["range"]), 4000.0, len(payload) if sp else n) + payload
+            if rp:
+                rec = zlib.compress(rec)
+            f.write(struct.pack("<Q", len(rec)))
+            f.write(rec)
         f.write(b"5WOLB")
 
 

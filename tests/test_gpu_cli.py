@@ -40,7 +40,7 @@ def _run_cli(opts, d, fl, kf, outname="o", extra=()):
         cmd += ["--fastq", fl["fastq"]]
     out = os.path.join(d, outname)
     cmd += [os.path.join(d, "reads.blow5"), fl["align"], out]
-    p = subprocess.run(cmd, capture_output=True, timeout=300)
+    p = subprocess.run(cmd, capture_output=True, timeout=300, env=dict(os.environ, PGM_CLI_SHARE_DEVICES="1"))
     assert p.returncode == 0, p.stderr.decode()[-3000:]
     files = {}
     for name in os.listdir(os.path.join(out, "dump")):
@@ -150,3 +150,24 @@ def test_cli_reads_bam(cli):
         bam_files = _run_cli(opts, d, dict(fl, align=bam), kf, outname="o_bam")
     assert bam_files == sam_files
     assert_matches_golden(digest(bam_files), load_golden()["synthetic"][label], label)
+
+
+@pytest.mark.parametrize("record_press", ["none", "zlib"])
+def test_cli_decodes_svb_zd_signal_on_the_device(cli, record_press):
+    """BLOW5 files as slow5tools writes them (signal_press svb-zd, records zlib-compressed or not): the command line
+    ships the streams and k_svb_decode unpacks them; the files must equal the reference digests, the host-decoded run
+    (--host-signal-decode: slow5lib decompresses) and a run cut into several batches and two device contexts."""
+    for label in ("tsv_k5_sc1", "ss_rna_k5_sc1"):
+        _, cfg, opts = next(c for c in parity_cases() if c[0] == label)
+        with tempfile.TemporaryDirectory(prefix="pgm_cli_svb_") as d:
+            fl, kf = _make_files(cfg, opts, d)
+            os.remove(os.path.join(d, "reads.blow5"))
+            for f in os.listdir(d):
+                if f.endswith(".idx"):
+                    os.remove(os.path.join(d, f))
+            synth.write_blow5(synth.make_batch(cfg), os.path.join(d, "reads.blow5"), signal_press="svb-zd", record_press=record_press)
+            dev = _run_cli(opts, d, fl, kf, outname="o_dev")
+            host = _run_cli(opts, d, fl, kf, outname="o_host", extra=["--host-signal-decode"])
+            cut = _run_cli(opts, d, fl, kf, outname="o_cut", extra=["--batch-samples", "30000", "--gpus", "2"])
+        assert dev == host and cut == dev
+        assert_matches_golden(digest(dev), load_golden()["synthetic"][label], label)

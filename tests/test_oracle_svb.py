@@ -57,3 +57,23 @@ def test_malformed_streams_are_rejected_like_slow5lib():
     assert ol.svb_zd_decode(enc, 99) is None          # the caller's length disagrees with the stream's
     if ol.svbref() is not None:
         assert ol.svbref_depress(enc[:-1]) is None and ol.svbref_depress(enc + b"\0") is None
+
+
+def test_reference_reads_the_compressed_blow5_the_writer_makes(tmp_path):
+    """The test/bench BLOW5 writer with signal_press svb-zd (+ zlib records) produces files the UNMODIFIED reference
+    (slow5lib inside oracle/_ref/poregen_ref) reads to the same dump as the uncompressed file."""
+    import os
+    from cases import parity_cases
+    if not os.path.exists(ol.REF_BIN):
+        pytest.skip("compiled reference (oracle/_ref) not present")
+    _, cfg, opts = next(c for c in parity_cases() if c[0] == "tsv_k5_sc1")
+    cfg.n_reads = 12
+    batch = synth.make_batch(cfg)
+    outs = []
+    for i, (sp, rp) in enumerate((("none", "none"), ("svb-zd", "none"), ("svb-zd", "zlib"))):
+        d = tmp_path / f"v{i}"
+        d.mkdir()
+        synth.write_blow5(batch, str(d / "reads.blow5"), signal_press=sp, record_press=rp)
+        fl = synth.write_alignment(batch, str(d))
+        outs.append(ol.run_reference(opts, str(d / "reads.blow5"), fl["align"], str(d / "ref"), fastq=fl["fastq"]))
+    assert outs[0] == outs[1] == outs[2] and len(outs[0]) > 1
