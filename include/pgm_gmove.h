@@ -272,6 +272,14 @@ typedef struct pgm_model_row {
 int pgm_model_begin(pgm_ctx *ctx);
 int pgm_model_finalize(pgm_ctx *ctx, double stddev_limit, const pgm_model_row **rows_out);
 
+/* Dwell medians (reference scripts/poregen.sh:33-52, calculate_dwell_times_medians): per dump file, `datamash
+ * median` over the comma counts of its ';'-separated fields = (event length - 1) of every event, plus one 0 for the empty field
+ * behind the last ';'. Uses the log pgm_model_begin started (event lengths are logged beside the values). Returns
+ * twice_median[n_slots] (host memory owned by the context): the sum of the two middle counts (or twice the middle one), so the
+ * median is twice_median / 2 exactly; -1 for a k-mer without events (empty file: datamash prints nothing). Can be called before
+ * or after pgm_model_finalize. */
+int pgm_model_dwell(pgm_ctx *ctx, const int64_t **twice_median_out);
+
 /* Test hook for the device formatter: the text of ONE event made of the n host doubles vals[]
  * ("%.8f," ... "%.8f;", gmove.cpp:674-678) into text_out[cap]; *len_out = its length (also when it
  * does not fit, in which case nothing is written). */

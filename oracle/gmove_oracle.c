@@ -445,3 +445,31 @@ int oracle_svb_zd_decode(const uint8_t *p, size_t nbytes, uint32_t expect, int16
     }
     return data == end ? 0 : -1;
 }
+
+/* ---------- dwell medians ----------
+ * scripts/poregen.sh:33-52 calculate_dwell_times_medians on one dump file's text:
+ *   awk -F';' '{for(i=1;i<=NF;i++) print gsub(",", "", $i)}' | datamash median 1
+ * i.e. the comma count of every ';'-separated field of every line — the file is one line that ends with ';', so the
+ * last field is empty and counts 0 — and the median (mean of the two middle values). Returns the number of values
+ * (0 for an empty file: awk prints nothing); *twice_median = sum of the two middle counts (or twice the middle one).
+ * PARITY UNPINNED like the model rows: datamash is not available; the median of integers has one defensible value. */
+static int u64_cmp(const void *a, const void *b) {
+    const uint64_t x = *(const uint64_t *)a, y = *(const uint64_t *)b;
+    return (x > y) - (x < y);
+}
+size_t oracle_dwell_median_text(const char *text, size_t len, uint64_t *twice_median) {
+    *twice_median = 0;
+    if (len == 0) return 0;
+    size_t nf = 1;
+    for (size_t i = 0; i < len; i++) nf += text[i] == ';';
+    uint64_t *c = (uint64_t *)calloc(nf, sizeof(uint64_t));
+    size_t f = 0;
+    for (size_t i = 0; i < len; i++) {
+        if (text[i] == ';') f++;
+        else if (text[i] == ',') c[f]++;
+    }
+    qsort(c, nf, sizeof(uint64_t), u64_cmp);
+    *twice_median = (nf & 1) ? 2 * c[nf / 2] : c[nf / 2 - 1] + c[nf / 2];
+    free(c);
+    return nf;
+}

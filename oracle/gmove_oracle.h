@@ -45,6 +45,10 @@ int oracle_pick_kmer(const int *indel_pos, size_t n, int left, int k, int margin
 int oracle_model_row(const double *vals, size_t n, double limit, double *median, double *stddev);
 size_t oracle_model_row_text(const char *text, size_t len, double limit, double *median, double *stddev, char *median_str, char *stddev_str);
 
+/* scripts/poregen.sh:33-52 calculate_dwell_times_medians on one dump file's text; returns the number of values, *twice_median =
+ * twice the datamash median of the per-field comma counts. PARITY UNPINNED (datamash absent). */
+size_t oracle_dwell_median_text(const char *text, size_t len, uint64_t *twice_median);
+
 /* slow5lib's svb-zd signal stream -> int16 samples (slow5_press.c:1085-1130 and the streamvbyte scalar decoder).
  * PINNED: tests/test_oracle_svb.py compares it (and the numpy encoder that makes the test inputs) with slow5lib's
  * own slow5_ptr_compress_solo / slow5_ptr_depress_solo compiled into oracle/_ref/libsvbref.so. */

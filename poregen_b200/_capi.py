@@ -118,7 +118,7 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
-    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw",
+    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw", "pgm_model_dwell",
 ]
 PGM_N_STAGES = 11
 # pgm_model_row (include/pgm_gmove.h)
@@ -182,6 +182,8 @@ def load() -> C.CDLL:
     lib.pgm_profile_read.restype = C.c_int
     lib.pgm_stage_name.argtypes = [C.c_int]
     lib.pgm_stage_name.restype = C.c_char_p
+    lib.pgm_model_dwell.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.pgm_model_dwell.restype = C.c_int
     lib.pgm_debug_raw.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.pgm_debug_raw.restype = C.c_int
     lib.pgm_debug_format.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, P(C.c_uint64)]

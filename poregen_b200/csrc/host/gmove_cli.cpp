@@ -76,6 +76,7 @@ struct Opt {
     // extensions
     int gpus = 1, threads = 0;
     uint64_t batch_samples = 64ull << 20;
+    const char *dwell_out = nullptr;   // --dwell FILE: kmer<TAB>median dwell (scripts/poregen.sh:33-52)
     const char *model_out = nullptr;   // --model FILE: kmer<TAB>median<TAB>stddev (scripts/poregen.sh:54-85)
     double stddev_limit = 1e300;
     int host_signal = 0;          // --host-signal-decode: let slow5lib decompress the signal (default: svb-zd streams go to the GPU)
@@ -111,6 +112,7 @@ void print_help(FILE *fp, const Opt &o) {
     fprintf(fp, "   --batch-samples INT        raw samples per device batch [%" PRIu64 "]\n", o.batch_samples);
     fprintf(fp, "   --model FILE               also write kmer<TAB>median<TAB>stddev per dumped k-mer (calculate_mean_stddev_all of scripts/poregen.sh)\n");
     fprintf(fp, "   --stddev_limit FLOAT       upper clamp of the stddev column [none]\n");
+    fprintf(fp, "   --dwell FILE               per-k-mer median of (event length - 1), as calculate_dwell_times_medians prints it\n");
     fprintf(fp, "   --host-signal-decode       decompress svb-zd signals with slow5lib on the host instead of on the GPU\n");
 }
 
@@ -708,7 +710,7 @@ void process_batch(Run &R, Batch &b) {
 
 enum { LO_SCALING = 3, LO_MARGIN, LO_SAMPLE_LIMIT, LO_FILE_LIMIT, LO_KMER_FILE, LO_INDEX_START, LO_INDEX_END, LO_FASTQ, LO_D,
        LO_MAX_DUR, LO_MIN_DUR, LO_PA_MIN, LO_PA_MAX, LO_PICK_MARGIN, LO_RNA, LO_VERBOSE, LO_HELP, LO_VERSION, LO_DEBUG_BREAK,
-       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT, LO_HOSTSIG };
+       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT, LO_HOSTSIG, LO_DWELL };
 
 const struct option long_options[] = {
     {"kmer_size", required_argument, 0, 'k'},          // 0
@@ -739,6 +741,7 @@ const struct option long_options[] = {
     {"model", required_argument, 0, 0},                // 25
     {"stddev_limit", required_argument, 0, 0},         // 26
     {"host-signal-decode", no_argument, 0, 0},         // 27
+    {"dwell", required_argument, 0, 0},                // 28
     {0, 0, 0, 0}};
 
 }  // namespace
@@ -798,6 +801,7 @@ int gmove(int argc, char *argv[]) {
                 case LO_MODEL: opt.model_out = optarg; break;
                 case LO_SDLIMIT: opt.stddev_limit = atof(optarg); break;
                 case LO_HOSTSIG: opt.host_signal = 1; break;
+                case LO_DWELL: opt.dwell_out = optarg; break;
                 default: break;
             }
         }
@@ -933,10 +937,10 @@ int gmove(int argc, char *argv[]) {
     R.t_start = t_c0 - t_gmove0;
     for (int g = 0; g < opt.gpus; g++)
         if (pgm_create(&po, g % ndev, nullptr, &R.gpus[g].ctx) != PGM_OK) DIE("%s", pgm_last_error(nullptr));
-    if (opt.model_out) {
+    if (opt.model_out || opt.dwell_out) {
         // a k-mer's values would be spread over the devices: the segmented median needs them in one place
-        if (opt.gpus != 1) DIE("%s", "--model needs --gpus 1");
-        if (opt.delimit_files) DIE("%s", "--model cannot be combined with -d (the script splits on ';' and ',' only)");
+        if (opt.gpus != 1) DIE("%s", "--model / --dwell need --gpus 1");
+        if (opt.delimit_files) DIE("%s", "--model / --dwell cannot be combined with -d (the scripts split on ';' and ',' only)");
         if (pgm_model_begin(R.gpus[0].ctx) != PGM_OK) DIE("%s", pgm_last_error(R.gpus[0].ctx));
     }
 
@@ -1004,6 +1008,18 @@ int gmove(int argc, char *argv[]) {
             else fprintf(fm, "%s\t%.14g\t%.14g\n", name, (double)rows[s].median_num / 2e8, rows[s].stddev);
         }
         fclose(fm);
+    }
+    if (opt.dwell_out) {
+        const int64_t *tm = nullptr;
+        if (pgm_model_dwell(R.gpus[0].ctx, &tm) != PGM_OK) DIE("%s", pgm_last_error(R.gpus[0].ctx));
+        FILE *fd = fopen(opt.dwell_out, "w");
+        if (!fd) { fprintf(stderr, "Error in opening %s\n", opt.dwell_out); exit(EXIT_FAILURE); }
+        for (uint32_t s = 0; s < R.n_slots; s++) {   // echo -e "$filename\t$median" (poregen.sh:50)
+            const char *name = kmers[opt.index_start - 1 + s].c_str();
+            if (tm[s] < 0) fprintf(fd, "%s\t\n", name);
+            else fprintf(fd, "%s\t%.14g\n", name, (double)tm[s] / 2.0);
+        }
+        fclose(fd);
     }
     for (Gpu &g : R.gpus) pgm_destroy(g.ctx);
     slow5_idx_unload(R.sp);

@@ -64,11 +64,13 @@ struct pgm_ctx {
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
     const uint32_t *gathered = nullptr;       // pgm_set_gathered
     // model aggregation log (pgm_model_begin / pgm_model_finalize): one entry per batch
-    struct ModelBatch { long long *vals; unsigned long long *slot_off; std::vector<unsigned long long> h_slot_off; };
+    struct ModelBatch { long long *vals; unsigned long long *slot_off; std::vector<unsigned long long> h_slot_off;
+                        uint32_t *lens = nullptr, *ev_off = nullptr; std::vector<uint32_t> h_ev_off; };   // event lengths / slot ranges (dwell medians)
     bool model_on = false;
     std::vector<ModelBatch> model_log;
     DBuf model_bad, model_grouped, model_off, model_dst, model_rows;
     std::vector<pgm_model_row> h_model_rows;
+    std::vector<int64_t> h_dwell;
     cudaStream_t aux = nullptr;               // short scans that do not depend on each other run beside the main stream
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     size_t text_written_cap = 0;              // capacity of `text` when pgm_emit formatted into it (0: it did not)
@@ -211,7 +213,7 @@ void pgm_destroy(pgm_ctx *c) {
     if (c->aux) { cudaStreamSynchronize(c->aux); cudaStreamDestroy(c->aux); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
-    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); }
+    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); cudaFree(mb.lens); cudaFree(mb.ev_off); }
     c->model_log.clear();
     for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
     DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->bucket_base, &c->sel_base,
@@ -839,6 +841,13 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
         c->launches += 2;
         CU(c, cudaGetLastError());
         CU(c, cudaMemcpyAsync(mb.h_slot_off.data(), mb.slot_off, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
+        // the events' lengths and slot ranges, for the dwell medians
+        CU(c, cudaMalloc(&mb.lens, (ne ? ne : 1) * 4));
+        CU(c, cudaMalloc(&mb.ev_off, (size_t)(NS + 1) * 4));
+        mb.h_ev_off.resize(NS + 1);
+        if (ne) CU(c, cudaMemcpyAsync(mb.lens, c->sel_len.p, ne * 4, cudaMemcpyDeviceToDevice, st));
+        CU(c, cudaMemcpyAsync(mb.ev_off, c->sel_base.p, (size_t)(NS + 1) * 4, cudaMemcpyDeviceToDevice, st));
+        CU(c, cudaMemcpyAsync(mb.h_ev_off.data(), c->sel_base.p, (size_t)(NS + 1) * 4, cudaMemcpyDeviceToHost, st));
         c->model_log.push_back(std::move(mb));
     }
     CU(c, cudaStreamSynchronize(st));
@@ -882,7 +891,7 @@ int pgm_profile_read(pgm_ctx *c, float *ms, uint32_t *launches) {
 }
 
 static void model_clear(pgm_ctx *c) {
-    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); }
+    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); cudaFree(mb.lens); cudaFree(mb.ev_off); }
     c->model_log.clear();
 }
 
@@ -942,6 +951,53 @@ int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **ro
     CU(c, cudaMemcpyAsync(c->h_model_rows.data(), c->model_rows.p, (size_t)NS * sizeof(pgm_model_row), cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     *rows_out = c->h_model_rows.data();
+    return PGM_OK;
+}
+
+int pgm_model_dwell(pgm_ctx *c, const int64_t **twice_median_out) {
+    if (!c || !twice_median_out) return PGM_ERR_ARG;
+    if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_dwell needs pgm_model_begin first");
+    CU(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint32_t NS = c->opts.n_slots;
+    // per slot: two leading zeros (see k_dwell_group), then every batch's events in file order
+    std::vector<unsigned long long> off(NS + 1, 0);
+    for (uint32_t s = 0; s < NS; s++) {
+        unsigned long long n = 2;
+        for (auto &mb : c->model_log) n += mb.h_ev_off[s + 1] - mb.h_ev_off[s];
+        off[s + 1] = off[s] + n;
+    }
+    const unsigned long long total = off[NS];
+    RET(ensure(c, c->model_off, (size_t)(NS + 1) * 8));
+    RET(ensure(c, c->model_rows, (size_t)NS * sizeof(ModelRowDev)));
+    RET(ensure(c, c->model_grouped, (size_t)total * 8));
+    RET(ensure(c, c->model_dst, (size_t)NS * 8 * (c->model_log.size() + 1)));
+    CU(c, cudaMemcpyAsync(c->model_off.p, off.data(), (size_t)(NS + 1) * 8, cudaMemcpyHostToDevice, st));
+    std::vector<unsigned long long> dst((size_t)NS * c->model_log.size(), 0), cur(NS);
+    for (uint32_t s = 0; s < NS; s++) cur[s] = off[s] + 2;
+    for (size_t bi = 0; bi < c->model_log.size(); bi++)
+        for (uint32_t s = 0; s < NS; s++) {
+            dst[bi * NS + s] = cur[s];
+            cur[s] += c->model_log[bi].h_ev_off[s + 1] - c->model_log[bi].h_ev_off[s];
+        }
+    if (!dst.empty()) CU(c, cudaMemcpyAsync(c->model_dst.p, dst.data(), dst.size() * 8, cudaMemcpyHostToDevice, st));
+    k_dwell_heads<<<cdiv(NS, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<unsigned long long>(c->model_off), NS, P<long long>(c->model_grouped));
+    c->launches++;
+    for (size_t bi = 0; bi < c->model_log.size(); bi++) {
+        k_dwell_group<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(c->model_log[bi].lens, c->model_log[bi].ev_off, P<unsigned long long>(c->model_dst) + bi * NS, NS,
+                                                         P<long long>(c->model_grouped));
+        c->launches++;
+    }
+    k_model_rows<<<NS < (uint32_t)c->n_sm * 8 ? NS : (uint32_t)c->n_sm * 8, PGM_BLOCK, 0, st>>>(P<long long>(c->model_grouped), P<unsigned long long>(c->model_off), NS,
+                                                                                              (double)INFINITY, P<ModelRowDev>(c->model_rows));
+    c->launches++;
+    CU(c, cudaGetLastError());
+    std::vector<pgm_model_row> rows(NS);
+    CU(c, cudaMemcpyAsync(rows.data(), c->model_rows.p, (size_t)NS * sizeof(pgm_model_row), cudaMemcpyDeviceToHost, st));
+    CU(c, cudaStreamSynchronize(st));
+    c->h_dwell.resize(NS);
+    for (uint32_t s = 0; s < NS; s++) c->h_dwell[s] = (off[s + 1] - off[s] > 2) ? rows[s].median_num : -1;   // no event: the file is empty
+    *twice_median_out = c->h_dwell.data();
     return PGM_OK;
 }
 

@@ -39,6 +39,23 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_model_group(const long long *vals
     }
 }
 
+// Dwell medians (reference scripts/poregen.sh:33-52, calculate_dwell_times_medians): per dump file, the comma count of every
+// ';'-separated field — event length - 1, plus a 0 for the empty field behind the last ';' — and `datamash median` over them.
+// The counts of one batch's slot range go behind two leading zeros (the first is the value k_model_rows drops, the second the
+// empty field) and what earlier batches put there; k_model_rows then selects the median exactly like for the level values.
+__global__ void __launch_bounds__(PGM_BLOCK) k_dwell_group(const uint32_t *sel_len, const uint32_t *ev_off, const unsigned long long *dst_off,
+                                                           uint32_t n_slots, long long *grouped) {
+    for (uint32_t s = blockIdx.x; s < n_slots; s += gridDim.x) {
+        const uint32_t a = ev_off[s], n = ev_off[s + 1] - a;
+        const unsigned long long d = dst_off[s];
+        for (uint32_t i = threadIdx.x; i < n; i += PGM_BLOCK) grouped[d + i] = (long long)sel_len[a + i] - 1;
+    }
+}
+__global__ void __launch_bounds__(PGM_BLOCK) k_dwell_heads(const unsigned long long *off, uint32_t n_slots, long long *grouped) {
+    const uint32_t s = blockIdx.x * PGM_BLOCK + threadIdx.x;
+    if (s < n_slots) { grouped[off[s]] = 0; grouped[off[s] + 1] = 0; }
+}
+
 struct ModelRowDev {     // mirrors pgm_model_row (include/pgm_gmove.h)
     double median, stddev;
     long long median_num;          // median = median_num / 2e8, exactly

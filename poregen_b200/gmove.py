@@ -146,6 +146,13 @@ class GmoveEngine:
         buf = (C.c_char * (n * 40)).from_address(p.value)
         return np.frombuffer(buf, dtype=np.dtype(capi.MODEL_ROW_DTYPE), count=n).copy()
 
+    def model_dwell(self) -> np.ndarray:
+        """Twice the per-k-mer dwell median over everything logged since model_begin (scripts/poregen.sh:33-52); -1: no event."""
+        p = C.c_void_p()
+        self._chk(self.lib.pgm_model_dwell(self._ctx, C.byref(p)))
+        buf = (C.c_char * (self.n_slots * 8)).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.int64, count=self.n_slots).copy()
+
     def profile_enable(self, on: bool = True, only: Optional[str] = None):
         """Stage timers on/off; `only` = a stage name: bracket that stage alone (PGM_PROFILE_ONLY)."""
         mode = 1 if on else 0

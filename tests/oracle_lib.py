@@ -56,9 +56,18 @@ def lib():
         _lib.oracle_model_row.restype = C.c_int
         _lib.oracle_model_row_text.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_char_p, C.c_char_p]
         _lib.oracle_model_row_text.restype = C.c_size_t
+        _lib.oracle_dwell_median_text.argtypes = [C.c_char_p, C.c_size_t, C.POINTER(C.c_uint64)]
+        _lib.oracle_dwell_median_text.restype = C.c_size_t
         _lib.oracle_svb_zd_decode.argtypes = [C.c_void_p, C.c_size_t, C.c_uint32, C.c_void_p]
         _lib.oracle_svb_zd_decode.restype = C.c_int
     return _lib
+
+
+def dwell_median_text(text: bytes):
+    """scripts/poregen.sh:33-52 on one dump file's text: (values, twice the median); (0, None) for an empty file."""
+    tm = C.c_uint64(0)
+    n = lib().oracle_dwell_median_text(text, len(text), C.byref(tm))
+    return int(n), (int(tm.value) if n else None)
 
 
 def svb_zd_decode(stream: bytes, expect: int):

@@ -120,10 +120,18 @@ def test_cli_model_rows(cli):
     with tempfile.TemporaryDirectory(prefix="pgm_cli_model_") as d:
         fl, kf = _make_files(cfg, opts, d)
         model = os.path.join(d, "model.tsv")
-        files = _run_cli(opts, d, fl, kf, extra=["--model", model, "--stddev_limit", "1.05", "--batch-samples", "40000"])
+        dwell = os.path.join(d, "dwell.tsv")
+        files = _run_cli(opts, d, fl, kf, extra=["--model", model, "--stddev_limit", "1.05", "--batch-samples", "40000", "--dwell", dwell])
         lines = open(model).read().splitlines()
+        dlines = open(dwell).read().splitlines()
     names = sorted(n for n in files if n != "freq.txt")
     assert [ln.split("\t")[0] for ln in lines] == names
+    # --dwell: calculate_dwell_times_medians (scripts/poregen.sh:33-52) on the files the same run wrote
+    assert [ln.split("\t")[0] for ln in dlines] == names
+    for ln in dlines:
+        name, med_s = ln.split("\t")
+        n, tm = ol.dwell_median_text(files[name])
+        assert med_s == ("" if n == 0 else "%.14g" % (tm / 2.0))
     for ln in lines:
         name, med_s, sd_s = ln.split("\t")
         n, med, sd, ms, ss = ol.model_row_text(files[name], 1.05)

@@ -86,3 +86,45 @@ def test_model_rows_few_values(built):
         rows = eng.model_finalize(1e9)
     _check(rows, _slot_texts(ref), 1e9)
     assert (rows["flags"] & capi.PGM_MODEL_EMPTY).any()
+
+
+def _check_dwell(tm, texts):
+    assert tm.size == len(texts)
+    for s, text in enumerate(texts):
+        n, want = ol.dwell_median_text(text)
+        if n == 0:
+            assert tm[s] == -1, (s, tm[s])
+        else:
+            assert int(tm[s]) == want, (s, int(tm[s]), want, n)
+
+
+@pytest.mark.parametrize("nbatches", [1, 4])
+def test_dwell_medians(built, nbatches):
+    """calculate_dwell_times_medians (reference scripts/poregen.sh:33-52): median of the per-event comma counts (+ the empty last
+    field) of every dump file, from the logged event lengths; one batch and a run cut into four (totals carried)."""
+    opts = _o(kmer_size=4, sample_limit=37, scaling=1)
+    batch = synth.make_batch(SynthConfig(n_reads=64, median_samples=3000, seed=305))
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        eng.model_begin()
+        step = 64 // nbatches
+        for lo in range(0, 64, step):
+            eng.process(batch.slice(lo, lo + step))
+        tm = eng.model_dwell()
+        rows = eng.model_finalize(1e9)          # the level rows are still available afterwards
+        tm2 = eng.model_dwell()
+    _check_dwell(tm, _slot_texts(ref))
+    assert np.array_equal(tm, tm2)
+    _check(rows, _slot_texts(ref), 1e9)
+
+
+def test_dwell_medians_sparse(built):
+    opts = _o(kmer_size=6, sample_limit=2, scaling=0, min_dur=1, max_dur=12)
+    batch = synth.make_batch(SynthConfig(n_reads=6, median_samples=1500, seed=306))
+    ref = ol.oracle_run(opts, batch)
+    with GmoveEngine(opts) as eng:
+        eng.model_begin()
+        eng.process(batch)
+        tm = eng.model_dwell()
+    _check_dwell(tm, _slot_texts(ref))
+    assert (tm == -1).any()          # k-mers without events: the file is empty, datamash prints nothing

@@ -21,3 +21,11 @@ def test_too_few_values():
     assert ol.model_row_text(b"1.50000000;", 1.0)[0] == 0
     n, med, sd, ms, ss = ol.model_row_text(b"1.50000000,-2.25000000;", 1.0)
     assert n == 1 and med == -2.25 and math.isnan(sd)
+
+
+def test_dwell_median_known_answers():
+    """scripts/poregen.sh:33-52 by hand: fields of "1,2,3;4,5;6;" are "1,2,3" "4,5" "6" "" -> comma counts 2,1,0,0 -> median 0.5."""
+    assert ol.dwell_median_text(b"1.0,2.0,3.0;4.0,5.0;6.0;") == (4, 1)
+    assert ol.dwell_median_text(b"") == (0, None)
+    assert ol.dwell_median_text(b"1.0,2.0,3.0;") == (2, 2)            # counts 2 and 0 -> median 1
+    assert ol.dwell_median_text(b"1,2,3,4;1,2,3,4;1,2;1;") == (5, 2)   # counts 3,3,1,0,0 -> median 1
