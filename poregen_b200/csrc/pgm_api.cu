@@ -252,7 +252,8 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         return fail(nullptr, PGM_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
     if (prop.major != 10) return fail(nullptr, PGM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
 
-    if ((e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess ||
+    if ((e = cudaFuncSetAttribute(k_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, RANK_SMEM)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_gather<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_gather<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess)
         return fail(nullptr, PGM_ERR_CUDA, "cudaFuncSetAttribute(k_stats / k_gather): %s", cudaGetErrorString(e));
@@ -700,7 +701,7 @@ int pgm_emit(pgm_ctx *c) {
                 r.ev_start = P<uint32_t>(c->ev_start); r.ev_len = P<uint32_t>(c->ev_len); r.ev_read = P<uint32_t>(c->ev_read);
                 r.sel_start = P<uint32_t>(c->sel_start); r.sel_len = P<uint32_t>(c->sel_len); r.sel_read = P<uint32_t>(c->sel_read);
                 r.sel_src = P<unsigned long long>(c->sel_src); r.reads = c->db.reads; r.read_has_sel = HAS_SEL(c);
-                k_rank<<<sgrid, PGM_BLOCK, 0, st>>>(r);
+                k_rank<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, RANK_SMEM, st>>>(r);
                 c->launches++;
             }
         }

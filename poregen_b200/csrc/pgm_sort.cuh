@@ -131,42 +131,58 @@ struct RankIO {
     uint8_t *read_has_sel;                        // [R]
 };
 
-__global__ void __launch_bounds__(PGM_BLOCK) k_rank(RankIO io) {
-    __shared__ uint32_t wcount[PGM_WARPS][SORT_MAX_BINS];
-    __shared__ uint32_t goff[SORT_MAX_BINS];
+// 512-thread CTAs: a tile's 4096 events are 8 rounds per warp instead of 16 (the rounds of a warp are serial: every one
+// reads the counters the previous one wrote), and the 830 tiles of C2 make 2.8 waves of half-length tiles instead of 1.4 of full ones.
+#define RANK_BLOCK 512
+#define RANK_WARPS (RANK_BLOCK / 32)
+#define RANK_ITEMS (SORT_TILE / RANK_BLOCK)
+#define RANK_SMEM ((RANK_WARPS + 1) * SORT_MAX_BINS * 4)
+__global__ void __launch_bounds__(RANK_BLOCK) k_rank(RankIO io) {
+    extern __shared__ __align__(16) uint32_t sm_rank[];
+    uint32_t(*wcount)[SORT_MAX_BINS] = reinterpret_cast<uint32_t(*)[SORT_MAX_BINS]>(sm_rank);
+    uint32_t *goff = sm_rank + RANK_WARPS * SORT_MAX_BINS;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.bits, mask = bins - 1, shift = io.shift;
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t used_tiles = (n + SORT_TILE - 1) / SORT_TILE;
     for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < PGM_WARPS * bins; i += PGM_BLOCK) wcount[i / bins][i % bins] = 0;
-        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) goff[i] = io.hist_scanned[(size_t)i * io.ntiles_cap + tile];
+        for (uint32_t i = threadIdx.x; i < RANK_WARPS * bins; i += RANK_BLOCK) wcount[i / bins][i % bins] = 0;
+        for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)i * io.ntiles_cap + tile];
         __syncthreads();
-        const uint32_t wbase = tile * SORT_TILE + w * (32 * SORT_ITEMS);
-        uint32_t key[SORT_ITEMS], lrank[SORT_ITEMS];
+        const uint32_t wbase = tile * SORT_TILE + w * (32 * RANK_ITEMS);
+        uint32_t key[RANK_ITEMS], lrank[RANK_ITEMS], peers[RANK_ITEMS];
+        // the matches of all rounds first (they depend on nothing but the keys), then the serial counter updates
 #pragma unroll
-        for (int rd = 0; rd < SORT_ITEMS; rd++) {
+        for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
-            const bool valid = idx < n;
-            key[rd] = valid ? io.keys_in[idx] : 0;
+            key[rd] = (idx < n) ? io.keys_in[idx] : 0;
+        }
+#pragma unroll
+        for (int rd = 0; rd < RANK_ITEMS; rd++) {
+            const bool valid = wbase + rd * 32 + lane < n;
             const uint32_t d = valid ? ((key[rd] >> shift) & mask) : bins;  // invalid lanes form their own group
-            const uint32_t peers = __match_any_sync(0xffffffffu, d);
-            const uint32_t leader = __ffs(peers) - 1;
+            peers[rd] = __match_any_sync(0xffffffffu, d);
+        }
+#pragma unroll
+        for (int rd = 0; rd < RANK_ITEMS; rd++) {
+            const bool valid = wbase + rd * 32 + lane < n;
+            const uint32_t d = (key[rd] >> shift) & mask;
+            const uint32_t leader = __ffs(peers[rd]) - 1;
             uint32_t old = 0;
             if (valid && lane == leader) {
                 old = wcount[w][d];
-                wcount[w][d] = old + __popc(peers);
+                wcount[w][d] = old + __popc(peers[rd]);
             }
             old = __shfl_sync(0xffffffffu, old, leader);
-            lrank[rd] = old + __popc(peers & ((1u << lane) - 1));
+            lrank[rd] = old + __popc(peers[rd] & ((1u << lane) - 1));
             __syncwarp();
         }
         __syncthreads();
-        for (uint32_t b = threadIdx.x; b < bins; b += PGM_BLOCK) {   // exclusive scan over warps, per digit
+        for (uint32_t b = threadIdx.x; b < bins; b += RANK_BLOCK) {   // exclusive scan over warps, per digit
             uint32_t run = 0;
 #pragma unroll
-            for (int ww = 0; ww < PGM_WARPS; ww++) {
+            for (int ww = 0; ww < RANK_WARPS; ww++) {
                 const uint32_t t = wcount[ww][b];
                 wcount[ww][b] = run;
                 run += t;
@@ -174,7 +190,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_rank(RankIO io) {
         }
         __syncthreads();
 #pragma unroll
-        for (int rd = 0; rd < SORT_ITEMS; rd++) {
+        for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
             if (idx < n) {
                 const uint32_t slot = key[rd];
