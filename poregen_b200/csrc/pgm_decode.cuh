@@ -224,6 +224,7 @@ __device__ __forceinline__ int ss_pget(const int32_t *pos, uint32_t n, uint32_t 
 __device__ __forceinline__ bool ss_pick(const int32_t *pos, uint32_t n, int last, int left, int k, int margin, int L, int st_k, bool rna) {
     const int A = (int)((uint32_t)left + (uint32_t)k + (uint32_t)margin);
     const int B = (int)((uint32_t)left - (uint32_t)margin);
+    if (n == 0) return -st_k <= B && last >= A;        // no indel in the record (record-uniform): P = {-st_k}, then `last`
     // u = number of t in [0, n] with P[t] <= B
     uint32_t lo = 0, hi = n + 1;
     while (lo < hi) {
@@ -299,7 +300,7 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
                 base_ch[u] = 0;
                 if (t0 >= ntok) continue;
                 const uint32_t t = t0 + lane;
-                uint32_t ch = 0, num = 0, a = 0, d = 0, cg = 0;
+                uint32_t ch = 0, num = 0, a = 0, d = 0;
                 if (t < ntok) {
                     const int pos = wpos[t];
                     ch = wbuf[16 + pos];
@@ -312,15 +313,17 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
                         nd++;
                     }
                     if (nd == 0 || nd > 9) bad = true;                       // gmove.cpp:834, U7
-                    if (ch == ',') { a = num; cg = 1; }
-                    else if (ch == 'I') { a = num; cg = 0x10000u; }
-                    else { d = num; cg = 0x10000u; }
+                    if (ch == 'D') d = num; else a = num;
                 }
-                uint32_t ta, td, tcg;
+                // raw advance: a warp scan. Deleted bases: a scan only where the round has a 'D'. The ',' and indel
+                // counts are flags: two ballots instead of a scan.
+                uint32_t ta, td = 0;
                 const uint32_t xa = c_raw + warp_excl_scan_add(a, &ta);
-                const uint32_t xd = c_del + warp_excl_scan_add(d, &td);
-                const uint32_t ecg = warp_excl_scan_add(cg, &tcg);
-                const uint32_t xc = c_com + (ecg & 0xffffu), xg = c_ind + (ecg >> 16);
+                uint32_t xd = c_del;
+                if (__any_sync(0xffffffffu, d != 0)) xd += warp_excl_scan_add(d, &td);
+                const uint32_t lt = (1u << lane) - 1u;
+                const uint32_t mcom = __ballot_sync(0xffffffffu, ch == ','), mind = __ballot_sync(0xffffffffu, ch != 0 && ch != ',');
+                const uint32_t xc = c_com + __popc(mcom & lt), xg = c_ind + __popc(mind & lt);
                 if (ch == ',') {
                     const uint64_t ik = (uint64_t)xc + xd;
                     const int64_t si = rna ? (int64_t)rd.seq_len - (int64_t)ik - 1 : (int64_t)ik;
@@ -328,7 +331,7 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
                     if (si >= 0 && si < (int64_t)rd.seq_len) base_ch[u] = __ldg(seq + si);   // consumed after the 8 rounds
                     sc_start[xc] = xa; sc_end[xc] = xa + num;
                 } else if (ch) sc_indel[xg] = (int32_t)xc;
-                c_raw += ta; c_del += td; c_com += tcg & 0xffffu; c_ind += tcg >> 16;
+                c_raw += ta; c_del += td; c_com += __popc(mcom); c_ind += __popc(mind);
             }
 #pragma unroll
             for (int u = 0; u < 8; u++)
