@@ -293,28 +293,47 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
         const int sb = (cb == 0) ? (int)head : -16;                          // first byte a run length may use (chunk coordinates)
         for (uint32_t g0 = 0; g0 < ntok; g0 += 256) {
             uint32_t base_ch[8], ev_idx[8];
+            // run lengths of all 8 rounds first, branch-free: the four bytes in front of the operator come as one
+            // unaligned word from the staged copy (numbers up to 9999; longer ones finish in the rare loop), so the
+            // dependent shared-memory loads of the rounds overlap instead of queueing behind each other's loops
+            uint32_t chs[8], nums[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const uint32_t t = g0 + 32 * u + lane;
+                chs[u] = 0; nums[u] = 0;
+                if (t < ntok) {
+                    const int pos = wpos[t];
+                    const uint32_t bidx = (uint32_t)(16 + pos - 4);
+                    const uint32_t *wb = reinterpret_cast<const uint32_t *>(wbuf) + (bidx >> 2);
+                    const uint32_t v = __funnelshift_r(wb[0], wb[1], (bidx & 3u) * 8u);   // byte 3 = the byte before the operator
+                    chs[u] = wbuf[16 + pos];
+                    const uint32_t d3 = (v >> 24) - '0', d2 = ((v >> 16) & 0xffu) - '0', d1 = ((v >> 8) & 0xffu) - '0', d0 = (v & 0xffu) - '0';
+                    const bool k3 = d3 <= 9u && pos - 1 >= sb, k2 = k3 && d2 <= 9u && pos - 2 >= sb;
+                    const bool k1 = k2 && d1 <= 9u && pos - 3 >= sb, k0 = k1 && d0 <= 9u && pos - 4 >= sb;
+                    uint32_t num = (k3 ? d3 : 0u) + (k2 ? 10u * d2 : 0u) + (k1 ? 100u * d1 : 0u) + (k0 ? 1000u * d0 : 0u);
+                    if (!k3) bad = true;                                     // no digit: gmove.cpp:834
+                    if (k0) {                                                // five digits or more
+                        uint32_t nd = 4, mult = 10000;
+                        for (int q = pos - 5; q >= sb && nd < 10; q--) {
+                            const uint32_t dgt = (uint32_t)wbuf[16 + q] - '0';
+                            if (dgt > 9) break;
+                            if (nd < 9) num += dgt * mult;
+                            mult *= 10;
+                            nd++;
+                        }
+                        if (nd > 9) bad = true;                              // U7
+                    }
+                    nums[u] = num;
+                }
+            }
 #pragma unroll
             for (int u = 0; u < 8; u++) {
                 const uint32_t t0 = g0 + 32 * u;
                 ev_idx[u] = PGM_INVALID;
                 base_ch[u] = 0;
                 if (t0 >= ntok) continue;
-                const uint32_t t = t0 + lane;
-                uint32_t ch = 0, num = 0, a = 0, d = 0;
-                if (t < ntok) {
-                    const int pos = wpos[t];
-                    ch = wbuf[16 + pos];
-                    uint32_t nd = 0, mult = 1;
-                    for (int q = pos - 1; q >= sb && nd < 10; q--) {
-                        const uint32_t dgt = (uint32_t)wbuf[16 + q] - '0';
-                        if (dgt > 9) break;
-                        if (nd < 9) num += dgt * mult;
-                        mult *= 10;
-                        nd++;
-                    }
-                    if (nd == 0 || nd > 9) bad = true;                       // gmove.cpp:834, U7
-                    if (ch == 'D') d = num; else a = num;
-                }
+                const uint32_t ch = chs[u], num = nums[u];
+                const uint32_t a = (ch == 'D') ? 0u : num, d = (ch == 'D') ? num : 0u;
                 // raw advance: a warp scan. Deleted bases: a scan only where the round has a 'D'. The ',' and indel
                 // counts are flags: two ballots instead of a scan.
                 uint32_t ta, td = 0;

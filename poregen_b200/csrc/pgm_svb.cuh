@@ -10,10 +10,12 @@
 // (thirdparty/streamvbyte/src/streamvbyte_zigzag.c:19-40).
 //
 // Both recurrences (byte offset of a value, running sum of differences) are prefix sums. One warp per record walks it
-// in chunks of 256 values, 8 per lane: the lane's 16 key bits give its byte count with three masked adds, one warp
-// scan places the lanes in the chunk's data, the chunk's data bytes (≤ 1 KiB, any alignment) go through shared
-// memory as aligned 16-byte words — the loads of chunk c+1 are issued before chunk c is unpacked — and a second warp
-// scan carries the differences. A lane writes its 8 samples with one 16-byte store when raw_off is a multiple of 8.
+// in steps of 256 values, 8 per lane. Three steps are in flight: step c is unpacked from shared memory, the data bytes
+// of step c+1 (≤ 1 KiB, any alignment) are on their way there as aligned 16-byte cp.async pieces, and step c+2 is
+// placed: its lanes' byte counts come from the 16 key bits with three masked adds and ride in the low half of the ONE
+// warp scan per step whose high half carries step c's difference sums (16 bits of them reach an int16). A lane's
+// 8 byte offsets come from one multiplication on the codes spread to bytes; values of 1-2 bytes (every real signal)
+// unpack without a branch. A lane writes its 8 samples with one 16-byte store when raw_off is a multiple of 8.
 #pragma once
 #include "pgm_device.cuh"
 
@@ -32,12 +34,6 @@ struct SvbIO {
     uint32_t *ticket;                    // zeroed before the launch
     uint32_t *err;                       // |= 1: a stream does not describe raw_len samples
 };
-
-__device__ __forceinline__ uint4 svb_ldg16(const uint8_t *p) {
-    uint4 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-    return v;
-}
 
 // sum of the eight 2-bit fields of x (16 bits)
 __device__ __forceinline__ uint32_t svb_sum2(uint32_t x) {
