@@ -19,6 +19,7 @@
 
 #define DEC_WARPS PGM_WARPS
 #define DEC_WSM 2368   // bytes of shared staging per warp
+#define DEC_SLOT_SMEM 1024   // k-mer tables up to this many slots keep quota state and counts in shared memory
 
 struct DecodeIO {
     // quota state
@@ -424,9 +425,19 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 #ifndef DEC_MIN_CTAS
 #define DEC_MIN_CTAS 4
 #endif
-__global__ void __launch_bounds__(PGM_BLOCK, DEC_MIN_CTAS) k_decode(DevOpts o, DevBatch b, DecodeIO io) {
+__global__ void __launch_bounds__(PGM_BLOCK, DEC_MIN_CTAS) k_decode(DevOpts o, DevBatch b, DecodeIO gio) {
     __shared__ __align__(16) uint8_t sm_w[DEC_WARPS][DEC_WSM];   // per-warp staging (tokeniser, then evaluation tiles)
+    // Small k-mer tables (k <= 5 at full range): the quota state every event looks up and the per-slot counts every passing
+    // event increments live in shared memory for the CTA's lifetime; the counts go to the global vector once, at the end.
+    __shared__ uint32_t sm_cons[DEC_SLOT_SMEM], sm_cnt[DEC_SLOT_SMEM];
     const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    DecodeIO io = gio;
+    const bool local_slots = o.n_slots <= DEC_SLOT_SMEM;
+    if (local_slots) {
+        for (uint32_t s = threadIdx.x; s < o.n_slots; s += PGM_BLOCK) { sm_cons[s] = gio.consumed[s]; sm_cnt[s] = 0; }
+        __syncthreads();
+        io.consumed = sm_cons; io.counts = sm_cnt;
+    }
     uint32_t exam = 0;
     for (;;) {
         uint32_t r = 0;
@@ -451,6 +462,13 @@ __global__ void __launch_bounds__(PGM_BLOCK, DEC_MIN_CTAS) k_decode(DevOpts o, D
     }
     exam = warp_sum_t<uint32_t>(exam);
     if (lane == 0 && exam) atomicAdd(io.examined, (unsigned long long)exam);
+    if (local_slots) {
+        __syncthreads();
+        for (uint32_t s = threadIdx.x; s < o.n_slots; s += PGM_BLOCK) {
+            const uint32_t n = sm_cnt[s];
+            if (n) atomicAdd(gio.counts + s, n);
+        }
+    }
 }
 
 // ev_base = exclusive scan of the per-record totals (one launch, look-back over tiles of 4096 records)
