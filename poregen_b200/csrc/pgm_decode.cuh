@@ -102,12 +102,27 @@ __device__ __forceinline__ Lane16 load_lane16(const uint8_t *abase, uint32_t off
 __device__ __forceinline__ void place_events(const DecodeIO &io, uint32_t r, uint32_t base, uint32_t n_pass, const uint32_t *t_key,
                                              const uint32_t *t_start, const uint32_t *t_len) {
     const uint32_t lane = threadIdx.x & 31;
-    for (uint32_t p = lane; p < n_pass; p += 32) {
-        const uint32_t P = base + p;
-        if (P >= io.ev_cap) break;
-        const uint32_t slot = t_key[p];
-        io.key[P] = slot; io.ev_start[P] = t_start[p]; io.ev_len[P] = t_len[p]; io.ev_read[P] = r;
-        atomicAdd(io.hist + (size_t)(slot & io.hist_mask) * io.ntiles_cap + P / SORT_TILE, 1u);
+    if (base >= io.ev_cap) return;
+    n_pass = min(n_pass, io.ev_cap - base);
+    // a warp makes ~10 trips of 32 events for a record: the loads of four trips are issued before the first store (the
+    // compiler may not move them across the stores itself: the arrays could alias)
+    for (uint32_t p0 = 0; p0 < n_pass; p0 += 128) {
+        uint32_t sl[4], st[4], ln[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t p = p0 + 32 * u + lane;
+            sl[u] = st[u] = ln[u] = 0;
+            if (p < n_pass) { sl[u] = t_key[p]; st[u] = t_start[p]; ln[u] = t_len[p]; }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t p = p0 + 32 * u + lane;
+            if (p < n_pass) {
+                const uint32_t P = base + p;
+                io.key[P] = sl[u]; io.ev_start[P] = st[u]; io.ev_len[P] = ln[u]; io.ev_read[P] = r;
+                atomicAdd(io.hist + (size_t)(sl[u] & io.hist_mask) * io.ntiles_cap + P / SORT_TILE, 1u);
+            }
+        }
     }
 }
 

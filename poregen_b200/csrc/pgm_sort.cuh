@@ -137,7 +137,7 @@ struct RankIO {
 #define RANK_WARPS (RANK_BLOCK / 32)
 #define RANK_ITEMS (SORT_TILE / RANK_BLOCK)
 #define RANK_SMEM ((RANK_WARPS + 1) * SORT_MAX_BINS * 4)
-__global__ void __launch_bounds__(RANK_BLOCK) k_rank(RankIO io) {
+__global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
     extern __shared__ __align__(16) uint32_t sm_rank[];
     uint32_t(*wcount)[SORT_MAX_BINS] = reinterpret_cast<uint32_t(*)[SORT_MAX_BINS]>(sm_rank);
     uint32_t *goff = sm_rank + RANK_WARPS * SORT_MAX_BINS;
@@ -189,26 +189,37 @@ __global__ void __launch_bounds__(RANK_BLOCK) k_rank(RankIO io) {
             }
         }
         __syncthreads();
+        // where every event of the tile goes (or that it is over its quota), then the selected events' rows: all loads of
+        // a level are issued before the first one is used (id -> event row -> record row is a three-deep chain)
+        uint32_t qd[RANK_ITEMS], idv[RANK_ITEMS];
 #pragma unroll
         for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
+            qd[rd] = PGM_INVALID; idv[rd] = 0;
             if (idx < n) {
                 const uint32_t slot = key[rd];
                 const uint32_t d = (slot >> shift) & mask;
                 const uint32_t pos = goff[d] + wcount[w][d] + lrank[rd];
                 const uint32_t rank = pos - io.bucket_base[slot];
-                const uint32_t id = io.vals_in ? io.vals_in[idx] : idx;
-                const bool sel = rank < io.keep[slot];
-                const uint32_t q = io.sel_base[slot] + rank;
-                if (sel) {
-                    const uint32_t rr = io.ev_read[id];
-                    const uint32_t st = io.ev_start[id];
-                    io.sel_start[q] = st;
-                    io.sel_src[q] = io.reads[rr].raw_off + io.reads[rr].trim + st;
-                    io.sel_len[q] = io.ev_len[id];
-                    io.sel_read[q] = rr;
-                    io.read_has_sel[rr] = 1;
-                }
+                idv[rd] = io.vals_in ? io.vals_in[idx] : idx;
+                if (rank < io.keep[slot]) qd[rd] = io.sel_base[slot] + rank;
+            }
+        }
+        uint32_t rrv[RANK_ITEMS], stv[RANK_ITEMS], lnv[RANK_ITEMS];
+#pragma unroll
+        for (int rd = 0; rd < RANK_ITEMS; rd++) {
+            rrv[rd] = stv[rd] = lnv[rd] = 0;
+            if (qd[rd] != PGM_INVALID) { rrv[rd] = io.ev_read[idv[rd]]; stv[rd] = io.ev_start[idv[rd]]; lnv[rd] = io.ev_len[idv[rd]]; }
+        }
+#pragma unroll
+        for (int rd = 0; rd < RANK_ITEMS; rd++) {
+            if (qd[rd] != PGM_INVALID) {
+                const uint32_t q = qd[rd], rr = rrv[rd];
+                io.sel_start[q] = stv[rd];
+                io.sel_src[q] = io.reads[rr].raw_off + io.reads[rr].trim + stv[rd];
+                io.sel_len[q] = lnv[rd];
+                io.sel_read[q] = rr;
+                io.read_has_sel[rr] = 1;
             }
         }
     }
