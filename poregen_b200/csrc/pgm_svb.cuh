@@ -157,7 +157,8 @@ __global__ void __launch_bounds__(SVB_WARPS * 32) k_svb_decode(SvbIO io) {
             const uint32_t inc1 = warp_incl_scan_add(s1);
             posB = issue(1, inc1 - s1, __shfl_sync(0xffffffffu, inc1, 31));
         }
-        uint32_t kq = (nchunks > 2) ? load_keys(2) : 0u;
+        // key bits are requested three steps before they are needed (a step is shorter than a trip to HBM)
+        uint32_t kq = (nchunks > 2) ? load_keys(2) : 0u, kq2 = (nchunks > 3) ? load_keys(3) : 0u, kq3 = (nchunks > 4) ? load_keys(4) : 0u;
         uint32_t bufA = 0, bufC = 2;
         uint32_t prev = 0;                 // running sum of the differences, mod 2^16 (the samples are int16)
         for (uint32_t c = 0; c < nchunks && !overrun; c++) {
@@ -177,7 +178,8 @@ __global__ void __launch_bounds__(SVB_WARPS * 32) k_svb_decode(SvbIO io) {
             const uint32_t nvC = live(c + 2);
             const uint32_t kC = masked(kq, nvC);
             const uint32_t sC = svb_sum2(kC) + nvC;
-            kq = (c + 3 < nchunks) ? load_keys(c + 3) : 0u;
+            kq = kq2; kq2 = kq3;
+            kq3 = (c + 5 < nchunks) ? load_keys(c + 5) : 0u;
             const uint32_t v = ((uint32_t)run << 16) | sC;
             const uint32_t inc = warp_incl_scan_add(v);
             const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31);
