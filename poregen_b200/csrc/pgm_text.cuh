@@ -187,17 +187,40 @@ struct TextIO {
     unsigned long long text_cap;
 };
 
+// One warp per event, two events ahead: the row (length, offset) of event q+2 and the first 32 values of event q+1 are
+// requested before event q is formatted — a warp's events are otherwise a chain of two dependent trips to memory each.
+struct TextAhead {
+    uint32_t q, ln;
+    unsigned long long off, toff;
+};
+template <bool WITH_TOFF>
+__device__ __forceinline__ TextAhead text_row(const TextIO &io, uint32_t q, uint32_t n) {
+    TextAhead r;
+    r.q = q; r.ln = 0; r.off = 0; r.toff = 0;
+    if (q < n) {
+        r.ln = io.sel_len[q]; r.off = io.sel_off[q];
+        if (WITH_TOFF) r.toff = io.ev_toff[q];
+    }
+    return r;
+}
+
 __global__ void __launch_bounds__(PGM_BLOCK) k_text_len(TextIO io) {
     const uint32_t n = *io.n_sel;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t nwarps = gridDim.x * PGM_WARPS;
-    for (uint32_t q = blockIdx.x * PGM_WARPS + (threadIdx.x >> 5); q < n; q += nwarps) {
-        const uint32_t ln = io.sel_len[q];
-        const double *x = io.samples + io.sel_off[q];
-        uint32_t s = 0;
-        for (uint32_t t = lane; t < ln; t += 32) s += fmt8_len(x[t]);
+    const uint32_t q0 = blockIdx.x * PGM_WARPS + (threadIdx.x >> 5);
+    if (q0 >= n) return;
+    TextAhead A = text_row<false>(io, q0, n), B = text_row<false>(io, q0 + nwarps, n);
+    double vA = (lane < A.ln) ? io.samples[A.off + lane] : 0.0;
+    while (A.q < n) {
+        const double vB = (lane < B.ln) ? io.samples[B.off + lane] : 0.0;
+        const TextAhead C = text_row<false>(io, B.q + nwarps, n);
+        const double *x = io.samples + A.off;
+        uint32_t s = (lane < A.ln) ? fmt8_len(vA) : 0u;
+        for (uint32_t t = lane + 32; t < A.ln; t += 32) s += fmt8_len(x[t]);
         s = warp_sum_t<uint32_t>(s);
-        if (lane == 0) io.ev_tlen[q] = s;
+        if (lane == 0) io.ev_tlen[A.q] = s;
+        A = B; vA = vB; B = C;
     }
 }
 
@@ -214,17 +237,23 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_text_write(TextIO io) {
     const uint32_t n = *io.n_sel;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t nwarps = gridDim.x * PGM_WARPS;
-    for (uint32_t q = blockIdx.x * PGM_WARPS + (threadIdx.x >> 5); q < n; q += nwarps) {
-        const uint32_t ln = io.sel_len[q];
-        const double *x = io.samples + io.sel_off[q];
-        unsigned long long pos = io.ev_toff[q];
+    const uint32_t q0 = blockIdx.x * PGM_WARPS + (threadIdx.x >> 5);
+    if (q0 >= n) return;
+    TextAhead A = text_row<true>(io, q0, n), B = text_row<true>(io, q0 + nwarps, n);
+    double vA = (lane < A.ln) ? io.samples[A.off + lane] : 0.0;
+    while (A.q < n) {
+        const double vB = (lane < B.ln) ? io.samples[B.off + lane] : 0.0;
+        const TextAhead C = text_row<true>(io, B.q + nwarps, n);
+        const uint32_t ln = A.ln;
+        const double *x = io.samples + A.off;
+        unsigned long long pos = A.toff;
         for (uint32_t t0 = 0; t0 < ln; t0 += 32) {
             const uint32_t t = t0 + lane;
             Fmt8 f;
             double v = 0.0;
             uint32_t len = 0;
             if (t < ln) {
-                v = x[t];
+                v = t0 ? x[t] : vA;
                 f = fmt8_prepare(v);
                 len = f.big == 1 ? fmt8_big<false>(v, ',', nullptr) : f.len;
             }
@@ -239,6 +268,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_text_write(TextIO io) {
             if (t < ln && at + len <= io.text_cap) fmt8_write(f, v, (t + 1 == ln) ? ';' : ',', io.text + at);   // gmove.cpp:674-678
             pos += tot;
         }
+        A = B; vA = vB; B = C;
     }
 }
 
