@@ -91,6 +91,7 @@ struct pgm_ctx {
     DBuf cal, rflags, n_pass, ev_base;
     // events / sort / selection
     DBuf key, ev_start, ev_len, ev_read, key2, val, val2;
+    DBuf p_start, p_len, p_read;      // two-pass sorts: the event rows in first-pass order (SortPayload)
     DBuf sc_start, sc_end, sc_key, sc_code, sc_indel;
     DBuf zbatch;                       // zeroed every batch: scalars | misc words | scan status | read_has_sel[R] | tile histogram
     size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
@@ -220,7 +221,7 @@ void pgm_destroy(pgm_ctx *c) {
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
                    &c->key2, &c->val, &c->val2, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed, &c->svb_blob, &c->svb_off, &c->svb_words};
+                   &c->sc_indel, &c->sc_key, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed, &c->svb_blob, &c->svb_off, &c->svb_words, &c->p_start, &c->p_len, &c->p_read};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff, &c->h_svb_err};
     for (DBuf *b : host) release_host(*b);
@@ -371,6 +372,11 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     const size_t e4 = (size_t)cap * 4;
     DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read};
     for (DBuf *x : evb) RET(ensure(c, *x, e4));
+    {
+        uint32_t passes, per;
+        sort_plan(c, &passes, &per);
+        if (passes == 2) { RET(ensure(c, c->p_start, e4)); RET(ensure(c, c->p_len, e4)); RET(ensure(c, c->p_read, e4)); }
+    }
     RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
     RET(ensure(c, c->sel_src, (size_t)(cap + 1) * 8));
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
@@ -677,6 +683,7 @@ int pgm_emit(pgm_ctx *c) {
         StageTimer tsort(c, PGM_STAGE_SORT);
         const uint32_t ntiles = c->sort_ntiles;
         const uint32_t sgrid = ntiles < pgrid ? ntiles : pgrid;
+        const bool carry = passes == 2;
         uint32_t *kin = P<uint32_t>(c->key), *kout = P<uint32_t>(c->key2);
         uint32_t *vin = nullptr, *vout = P<uint32_t>(c->val);
         for (uint32_t p = 0; p < passes; p++) {
@@ -688,14 +695,22 @@ int pgm_emit(pgm_ctx *c) {
                 c->launches += 2;
             }
             if (p + 1 < passes) {
-                k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, vout, n_ev, shift, per, HIST(c), ntiles);
+                SortPayload pl;
+                memset(&pl, 0, sizeof pl);
+                if (carry) {   // two passes: the rows travel with the keys, the index does not
+                    pl.s_in = P<uint32_t>(c->ev_start); pl.l_in = P<uint32_t>(c->ev_len); pl.r_in = P<uint32_t>(c->ev_read);
+                    pl.s_out = P<uint32_t>(c->p_start); pl.l_out = P<uint32_t>(c->p_len); pl.r_out = P<uint32_t>(c->p_read);
+                }
+                k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, carry ? nullptr : vout, n_ev, shift, per, HIST(c), ntiles, pl);
                 c->launches++;
                 // ping-pong: keys key<->key2, values val<->val2
                 uint32_t *t = kin; kin = kout; kout = t;
                 vin = vout; vout = (vout == P<uint32_t>(c->val)) ? P<uint32_t>(c->val2) : P<uint32_t>(c->val);
             } else {
                 RankIO r;
-                r.n_events = n_ev; r.keys_in = kin; r.vals_in = vin; r.hist_scanned = HIST(c);
+                r.n_events = n_ev; r.keys_in = kin; r.vals_in = carry ? nullptr : vin; r.hist_scanned = HIST(c);
+                r.p_start = carry ? P<uint32_t>(c->p_start) : nullptr; r.p_len = carry ? P<uint32_t>(c->p_len) : nullptr;
+                r.p_read = carry ? P<uint32_t>(c->p_read) : nullptr;
                 r.ntiles_cap = ntiles; r.shift = shift; r.bits = per;
                 r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
                 r.ev_start = P<uint32_t>(c->ev_start); r.ev_len = P<uint32_t>(c->ev_len); r.ev_read = P<uint32_t>(c->ev_read);
