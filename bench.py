@@ -1,26 +1,35 @@
 #!/usr/bin/env python
 """bench.py — gmove hot-path benchmark (BASELINE.json metric: signal samples/s and events/s).
 
-A "step" is one full pass of the gmove record loop over the whole C2 workload (configs[1]:
-10,000 synthetic RNA004 reads x ~10k samples, ss records, -k 5 --rna --scaling 1
---sample_limit 5000 --min_dur 20 --max_dur 40), starting from empty per-k-mer totals.
+Workload: C3 = BASELINE.json configs[2], the configuration the metric is quoted on and the largest that
+fits one GPU: 100,000 synthetic DNA R10.4.1 move-table reads at 5 kHz (~52,000 samples each, 5.2e9 samples,
+10.4 GB of int16), `gmove -k 9 --sample_limit 1000 --file_limit 262144` (262,144 k-mer files, no scaling).
 
-  value : samples/s, whole job, inputs resident in HBM, timed with CUDA events on the stream the
-          kernels run on, max over ranks.
-  e2e   : the same through the host-buffer C-ABI path (pinned host arrays in, host result out;
-          H2D and D2H inside the timed region).
-  N > 1 : weak scaling. Each rank owns a contiguous range of records (its own C2-sized shard);
-          the only exchange is the all-gather of the per-k-mer count vector + exclusive scan over
-          ranks that fixes every rank's share of sample_limit.
+A "step" is ONE gmove job over all 100,000 reads, from empty per-k-mer totals: the alignment records are streamed
+in blocks of --block-reads consecutive records (what a host that reads a file hands over), block after block,
+with the per-k-mer totals (kmer_frequency_map) carried, so the result is the reference's single loop.
 
-`--impl reference` times the UNMODIFIED reference (oracle/_ref/poregen_ref, single thread: it has
-no other mode) on a bounded prefix of the same workload.
+  value : samples/s, whole job, every block resident in HBM before the timed region; CUDA events on the stream
+          the kernels run on; max over ranks.
+  e2e   : the same job through the host-buffer C ABI: every block uploaded from pinned host memory and the dump
+          TEXT (what the reference fprintf's) of every block downloaded to host memory inside the timed region.
+  N > 1 : STRONG scaling of the same job. Blocks are dealt to the ranks round-robin: round j = blocks
+          [jN, jN+N), rank g takes block jN+g - contiguous record ranges inside every round. Per round one NCCL
+          all-gather of the per-k-mer counts + the exclusive scan over ranks (fused in k_quota) fixes every
+          rank's share of sample_limit; totals are carried from round to round.
+  c2    : resident figure of configs[1] (round 1's workload) for comparison, N=1 only.
+
+`--impl reference` times the UNMODIFIED reference (oracle/_ref/poregen_ref, single thread: it has no other
+mode) on a bounded prefix of the same generator's reads.
 """
 from __future__ import annotations
 
 import argparse
+import copy
+import ctypes as C
 import json
 import os
+import resource
 import shutil
 import subprocess
 import sys
@@ -34,66 +43,210 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "gmove signal samples/sec (events/sec alongside)"
 UNIT = "samples/s"
+C3_READS = 100000
 
 
-def workload_desc(n_reads):
-    return {"workload": "C2 synthetic RNA004 ss records: gmove -k 5 --rna --scaling 1 --sample_limit 5000 --min_dur 20 --max_dur 40 --file_limit 5000",
-            "reads_per_gpu": n_reads, "median_samples_per_read": 10000,
-            "l2": "inputs (200 MB int16 per step) exceed the 126 MB L2; no explicit flush"}
+def workload_desc(reads, block, world):
+    return {"workload": "C3 synthetic DNA R10.4.1 5 kHz move-table reads: gmove -k 9 --sample_limit 1000 --file_limit 262144 "
+                        "(262,144 k-mer buckets, no scaling)",
+            "reads": reads, "median_samples_per_read": 50000, "block_reads": block,
+            "parallelism": f"read-range blocks dealt round-robin x{world}, one count all-gather per round",
+            "l2": "inputs (10.4 GB int16 per step) exceed the 126 MB L2; no explicit flush"}
 
 
 # ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the unmodified reference binary on a prefix of the same reads
+# ------------------------------------------------------------------------------------------------
+def _raise_nofile():
+    soft, hard = resource.getrlimit(resource.RLIMIT_NOFILE)
+    want = hard if hard != resource.RLIM_INFINITY else 1 << 20
+    for target in (want, 1 << 20, 300000):
+        try:
+            resource.setrlimit(resource.RLIMIT_NOFILE, (min(target, want) if hard != resource.RLIM_INFINITY else target, hard))
+            break
+        except (ValueError, OSError):
+            continue
+    return resource.getrlimit(resource.RLIMIT_NOFILE)[0]
+
+
+def reference_sample(n_reads):
+    """(cfg, opts, batch, scaled) for the first n_reads reads of C3. --sample_limit is scaled with the prefix
+    (1000 * n_reads / 100000) so the same share of the events (~65 %) is written as in the whole job: with the
+    full limit a 1 % prefix never reaches the quota and the reference would format MORE text per sample than it
+    does on the real job."""
+    import dataclasses
+    from poregen_b200 import synth, workloads
+    cfg, opts = workloads.c3(n_reads=C3_READS)
+    batch = synth.make_moves_fast(cfg, 0, n_reads)
+    limit = max(1, round(opts.sample_limit * n_reads / C3_READS))
+    return cfg, dataclasses.replace(opts, sample_limit=limit), batch
+
+
+class RefFiles:
+    """BLOW5 + move-table TSV of a batch in a temp dir; runs the reference (windowed over the k-mer index range
+    when the fd limit is below 4^k: one FILE* per k-mer, reference src/gmove.cpp:460-473)."""
+
+    def __init__(self, opts, batch):
+        from poregen_b200 import synth
+        self.opts, self.batch = opts, batch
+        # tmpfs when it has room (the fastest file system for the reference's 262,144 fopen()s), else the default temp dir
+        base = None
+        try:
+            st = os.statvfs("/dev/shm")
+            if st.f_bavail * st.f_frsize > (8 << 30):
+                base = "/dev/shm"
+        except OSError:
+            pass
+        self.dir = tempfile.mkdtemp(prefix="pgm_ref_", dir=base)
+        self.blow5 = os.path.join(self.dir, "reads.blow5")
+        synth.write_blow5(batch, self.blow5)
+        self.files = synth.write_alignment(batch, self.dir)
+        nofile = _raise_nofile()
+        n = opts.index_end - opts.index_start + 1
+        per = max(1, min(n, nofile - 64))
+        self.windows = [(a, min(a + per - 1, opts.index_end)) for a in range(opts.index_start, opts.index_end + 1, per)]
+        self.n = 0
+
+    def run_reference(self, binary):
+        """One reference job (all windows); returns (seconds, [out dirs])."""
+        import dataclasses
+        import oracle_lib as ol
+        outs, total = [], 0.0
+        for (a, b) in self.windows:
+            o = dataclasses.replace(self.opts, index_start=a, index_end=b)
+            out = os.path.join(self.dir, f"ref{self.n}")
+            self.n += 1
+            cmd = [binary, "gmove"] + ol.cli_args(o) + [self.blow5, self.files["align"], out]
+            t0 = time.perf_counter()
+            p = subprocess.run(cmd, capture_output=True)
+            total += time.perf_counter() - t0
+            if p.returncode != 0:
+                raise RuntimeError(f"reference failed rc={p.returncode}: {p.stderr.decode()[-500:]}")
+            outs.append(out)
+        return total, outs
+
+    def close(self):
+        shutil.rmtree(self.dir, ignore_errors=True)
+
+
 def run_reference_arm(args):
-    """Times oracle/_ref/poregen_ref on a bounded prefix of C2 (file form). Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from poregen_b200 import synth, workloads
+    import __graft_entry__ as g
+    g.build()
     import oracle_lib as ol
-    kind = "reference"
-    binary = ol.REF_BIN
-    if not os.path.exists(binary):
-        kind = "port"
+    kind = "reference" if os.path.exists(ol.REF_BIN) else "port"
+    nofile = _raise_nofile()
     n_reads = args.ref_reads
-    cfg, opts = workloads.c2(n_reads=n_reads)
-    batch = synth.make_batch(cfg)
+    if kind == "reference" and nofile < 262144 + 64:
+        n_reads = max(50, n_reads // (262144 // max(1, nofile - 64) + 1))   # every window is a full pass over the reads
+    cfg, opts, batch = reference_sample(n_reads)
     n_samples = int(batch.reads["raw_len"].astype("int64").sum())
-    d = tempfile.mkdtemp(prefix="pgm_ref_")
     times = []
-    examined = None
-    try:
-        if kind == "reference":
-            synth.write_blow5(batch, os.path.join(d, "reads.blow5"))
-            fl = synth.write_alignment(batch, d)
-            for i in range(args.warmup + args.steps):
-                out = os.path.join(d, f"out{i}")
-                t0 = time.perf_counter()
-                ol.run_reference(opts, os.path.join(d, "reads.blow5"), fl["align"], out, fastq=fl["fastq"])
-                dt = time.perf_counter() - t0
-                shutil.rmtree(out, ignore_errors=True)
-                if i >= args.warmup:
+    if kind == "reference":
+        rf = RefFiles(opts, batch)
+        try:
+            ref_warm = min(args.warmup, 1)      # one pass warms the page cache and the SLOW5 index; a step costs tens of seconds
+            for i in range(ref_warm + args.steps):
+                dt, outs = rf.run_reference(ol.REF_BIN)
+                for o in outs:
+                    shutil.rmtree(o, ignore_errors=True)
+                if i >= ref_warm:
                     times.append(dt)
-        else:
-            for i in range(args.warmup + args.steps):
-                t0 = time.perf_counter()
-                ol.oracle_run(opts, batch)
-                dt = time.perf_counter() - t0
-                if i >= args.warmup:
-                    times.append(dt)
-        examined = int(ol.oracle_run(opts, batch).n_events_examined)
-    finally:
-        shutil.rmtree(d, ignore_errors=True)
+            windows = len(rf.windows)
+        finally:
+            rf.close()
+        what = (f"unmodified reference binary (-O2, 1 thread: it has no other mode), file to file (BLOW5 read, TSV parse, "
+                f"262,144 dump files written) in {windows} k-mer index window(s) (RLIMIT_NOFILE {nofile})")
+    else:
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            ol.oracle_run(opts, batch)
+            if i >= args.warmup:
+                times.append(time.perf_counter() - t0)
+        what = "CPU oracle port (oracle/gmove_oracle.c), in memory, incl. text formatting"
+    examined = int(ol.oracle_run(opts, batch).n_events_examined)
     t = sum(times) / len(times)
     val = n_samples / t
-    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": workload_desc(n_reads),
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT,
+            "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": workload_desc(C3_READS, args.block_reads, args.gpus),
             "events_per_sec": examined / t,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind,
-                             "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples) per step; "
-                                       "reference binary built -O2, end to end incl. BLOW5 read and dump/ text output"},
+                             "sample": f"first {n_reads} of the 100,000 C3 reads ({n_samples} samples) per step, --sample_limit "
+                                       f"{opts.sample_limit} (1000 scaled with the prefix so the same share of events is written); {what}"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit_line(line)
+
+
+def cpu_baseline_leg(n_reads):
+    """The reference on a bounded prefix (~10-30 s of one host core), and this build's command line on the same files."""
+    import oracle_lib as ol
+    nofile = _raise_nofile()
+    if nofile < 262144 + 64:
+        n_reads = max(50, n_reads // (262144 // max(1, nofile - 64) + 1))
+    cfg, opts, batch = reference_sample(n_reads)
+    n_samples = int(batch.reads["raw_len"].astype("int64").sum())
+    if not os.path.exists(ol.REF_BIN):
+        t0 = time.perf_counter()
+        ol.oracle_run(opts, batch)
+        dt = time.perf_counter() - t0
+        return {"value": n_samples / dt, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": f"first {n_reads} C3 reads ({n_samples} samples, {dt:.1f} s), --sample_limit {opts.sample_limit}: CPU oracle port, in memory"}
+    rf = RefFiles(opts, batch)
+    try:
+        dt, outs = rf.run_reference(ol.REF_BIN)
+        out = {"value": n_samples / dt, "unit": UNIT, "cores": 1, "kind": "reference", "seconds": dt,
+               "sample": f"first {n_reads} of the 100,000 C3 reads ({n_samples} samples, {dt:.1f} s), --sample_limit {opts.sample_limit} "
+                         f"(1000 scaled with the prefix): unmodified reference binary (-O2), file to file, {len(rf.windows)} index window(s)"}
+        cli = _cli_leg(rf, outs, n_samples)
+        if cli:
+            out["same_files_through_cli"] = cli
+    finally:
+        rf.close()
+    return out
+
+
+def _cli_leg(rf, ref_outs, n_samples):
+    """`poregen gmove` of this build on the SAME files the reference just processed (file to file: BLOW5 decode on
+    host threads, device batches, dump/ written), its phase breakdown (PGM_CLI_STATS), and a byte comparison."""
+    import oracle_lib as ol
+    cli = os.path.join(ROOT, "poregen_b200", "bin", "poregen")
+    if not os.path.exists(cli):
+        return None
+    out_dir = os.path.join(rf.dir, "cli_out")
+    cmd = [cli, "gmove"] + ol.cli_args(rf.opts) + [rf.blow5, rf.files["align"], out_dir]
+    best, stats = None, None
+    env = dict(os.environ, PGM_CLI_STATS="1")
+    for i in range(2):   # the first run pays the SLOW5 index and a cold CUDA context
+        shutil.rmtree(out_dir, ignore_errors=True)
+        t0 = time.perf_counter()
+        p = subprocess.run(cmd, capture_output=True, env=env)
+        dt = time.perf_counter() - t0
+        if p.returncode != 0:
+            return {"error": p.stderr.decode()[-300:]}
+        if best is None or dt < best:
+            best = dt
+            stats = [ln for ln in p.stderr.decode().splitlines() if "pgm" in ln.lower() and ("s" in ln)][-3:]
+    # byte comparison: freq.txt of every window concatenated == ours; every non-empty dump file identical
+    same = True
+    try:
+        ours = open(os.path.join(out_dir, "freq.txt"), "rb").read()
+        ref = b"".join(open(os.path.join(o, "freq.txt"), "rb").read() for o in ref_outs)
+        same = ours == ref
+        checked = 0
+        for o in ref_outs:
+            d = os.path.join(o, "dump")
+            for name in sorted(os.listdir(d))[::97]:      # every 97th file of 262,144: ~2,700 files
+                if open(os.path.join(d, name), "rb").read() != open(os.path.join(out_dir, "dump", name), "rb").read():
+                    same = False
+                checked += 1
+    except OSError:
+        same, checked = False, 0
+    return {"value": n_samples / best, "unit": UNIT, "seconds": best, "identical_to_reference": same, "dump_files_compared": checked,
+            "phases": stats, "note": "process start to exit, incl. CUDA context creation"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -141,7 +294,6 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-# ------------------------------------------------------------------------------------------------
 class _DevArr:
     def __init__(self, ptr, n, typestr="<i4"):
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
@@ -149,14 +301,15 @@ class _DevArr:
 
 def bind_near_gpu(local):
     """Pin this process to the cores of the NUMA node its GPU hangs off, BEFORE any pinned buffer is allocated
-    (first touch then places the staging memory next to the GPU's PCIe root). With eight ranks streaming
-    0.5 GB per step each through host memory, remote placement is what the end-to-end number would measure.
-    Returns a description for the JSON line; silently does nothing where sysfs does not say."""
+    (first touch then places the staging memory next to the GPU's PCIe root). Returns a description for the JSON
+    line, or the reason it did nothing."""
     try:
         import torch
         p = torch.cuda.get_device_properties(local)
         bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
         base = "/sys/bus/pci/devices/" + bdf
+        if not os.path.exists(base + "/numa_node"):
+            return {"bound": False, "why": f"{base}/numa_node absent"}
         node = int(open(base + "/numa_node").read())
         cpus = set()
         for part in open(base + "/local_cpulist").read().strip().split(","):
@@ -166,12 +319,14 @@ def bind_near_gpu(local):
             elif part:
                 cpus.add(int(part))
         cpus &= os.sched_getaffinity(0)
-        if node < 0 or not cpus:
-            return None
+        if node < 0:
+            return {"bound": False, "why": "numa_node = -1 (single-node host or no affinity exposed)", "gpu": bdf}
+        if not cpus:
+            return {"bound": False, "why": "no local cpu in this process's affinity mask", "gpu": bdf, "numa_node": node}
         os.sched_setaffinity(0, cpus)
-        return {"gpu": bdf, "numa_node": node, "cpus": len(cpus)}
-    except Exception:
-        return None
+        return {"bound": True, "gpu": bdf, "numa_node": node, "cpus": len(cpus)}
+    except Exception as e:   # noqa: BLE001
+        return {"bound": False, "why": repr(e)[:120]}
 
 
 def measured_peak():
@@ -189,70 +344,42 @@ def ncu_traffic(stage):
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(stage)
+            return json.load(open(p)).get("c3", {}).get(stage)
         except Exception:
             return None
     return None
 
 
-def cpu_baseline_leg(n_reads):
-    """Reference (or oracle port) on a bounded prefix of C2, ~10-30 s of one host core."""
-    from poregen_b200 import synth, workloads
-    import oracle_lib as ol
-    cfg, opts = workloads.c2(n_reads=n_reads)
-    batch = synth.make_batch(cfg)
-    n_samples = int(batch.reads["raw_len"].astype("int64").sum())
-    if os.path.exists(ol.REF_BIN):
-        d = tempfile.mkdtemp(prefix="pgm_cpu_")
-        try:
-            synth.write_blow5(batch, os.path.join(d, "reads.blow5"))
-            fl = synth.write_alignment(batch, d)
-            t0 = time.perf_counter()
-            ref_files = ol.run_reference(opts, os.path.join(d, "reads.blow5"), fl["align"], os.path.join(d, "out"), fastq=fl["fastq"])
-            dt = time.perf_counter() - t0
-            cli = _cli_leg(opts, d, fl, ref_files, n_samples)
-        finally:
-            shutil.rmtree(d, ignore_errors=True)
-        kind = "reference"
-        what = "unmodified reference binary (-O2), end to end incl. BLOW5 read and dump/ text output"
-    else:
-        t0 = time.perf_counter()
-        ol.oracle_run(opts, batch)
-        dt = time.perf_counter() - t0
-        kind = "port"
-        what = "CPU oracle port (oracle/gmove_oracle.c), in memory, incl. text formatting"
-    out = {"value": n_samples / dt, "unit": UNIT, "cores": 1, "kind": kind,
-           "sample": f"first {n_reads} reads of the C2 generator ({n_samples} samples, {dt:.1f} s): {what}"}
-    if kind == "reference" and cli:
-        out["same_files_through_cli"] = cli
-    return out
+def stage_bytes(mode_scaling, T, NB, R, NS, S_act, E_pass, E_sel, S_sel):
+    """Algorithmic bytes per stage."""
+    return {"prep": 120 * R, "decode": T + NB + 88 * R + 16 * E_pass, "place": 32 * E_pass + 8 * R,
+            "sort": 16 * E_pass + 12 * E_sel, "select": 16 * NS, "stats": (2 * S_act + 48 * R) if mode_scaling else 0,
+            "gather": 2 * S_sel + 8 * S_sel + 20 * E_sel, "scan": 12 * E_sel, "misc": 8 * NS, "text": 0}
 
 
-def _cli_leg(opts, d, fl, ref_files, n_samples):
-    """The C++ command line of this build on the SAME files the reference just processed (file to file:
-    BLOW5 decode on host threads, device batches, dump/ written). Also checks the bytes."""
-    import oracle_lib as ol
-    cli = os.path.join(ROOT, "poregen_b200", "bin", "poregen")
-    if not os.path.exists(cli):
-        return None
-    cmd = [cli, "gmove"] + ol.cli_args(opts) + ["--fastq", fl["fastq"], os.path.join(d, "reads.blow5"), fl["align"], os.path.join(d, "cli_out")]
-    best = None
-    for i in range(2):   # the first run pays CUDA context creation and the SLOW5 index
-        shutil.rmtree(os.path.join(d, "cli_out"), ignore_errors=True)
-        t0 = time.perf_counter()
-        p = subprocess.run(cmd, capture_output=True)
-        dt = time.perf_counter() - t0
-        if p.returncode != 0:
-            return {"error": p.stderr.decode()[-300:]}
-        best = dt if best is None else min(best, dt)
-    same = True
-    for name, data in ref_files.items():
-        path = os.path.join(d, "cli_out", name if name == "freq.txt" else os.path.join("dump", name))
-        if not os.path.exists(path) or open(path, "rb").read() != data:
-            same = False
-            break
-    return {"value": n_samples / best, "unit": UNIT, "seconds": best, "identical_to_reference": same,
-            "note": "process start to exit, incl. CUDA context creation (~0.3-0.5 s)"}
+# ------------------------------------------------------------------------------------------------
+def pcie_calibration(local, nbytes=1 << 30):
+    """Plain pinned cudaMemcpyAsync in both directions at once on this rank's GPU (all ranks run it together):
+    what the e2e step can reach at best. Returns (h2d GB/s, d2h GB/s) measured concurrently."""
+    import torch
+    dev = torch.device("cuda", local)
+    h_in = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    h_out = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    d_in = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    d_out = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    res = []
+    for rep in range(3):
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(s1):
+            a0.record(); d_in.copy_(h_in, non_blocking=True); a1.record()
+        with torch.cuda.stream(s2):
+            b0.record(); h_out.copy_(d_out, non_blocking=True); b1.record()
+        torch.cuda.synchronize()
+        res.append((nbytes / a0.elapsed_time(a1) / 1e6, nbytes / b0.elapsed_time(b1) / 1e6))
+    return max(r[0] for r in res), max(r[1] for r in res)
 
 
 def run_own_arm(args):
@@ -261,7 +388,6 @@ def run_own_arm(args):
     import torch.distributed as dist
     import __graft_entry__ as g
     from poregen_b200 import _capi as capi, synth, workloads
-    from poregen_b200.batch import ReadBatch
     from poregen_b200.gmove import GmoveEngine
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -278,60 +404,82 @@ def run_own_arm(args):
     if world > 1:
         dist.barrier()
     capi.load()
+    dev = torch.device("cuda", local)
 
-    cfg, opts = workloads.c2(n_reads=args.reads, seed=0xC2 + rank)
-    hb = synth.make_batch(cfg)
-    # pinned host copies: the e2e path reads its inputs from pinned memory
-    pin = lambda a: torch.from_numpy(np.array(a, copy=True).view(np.uint8).reshape(-1)).pin_memory()
-    p_raw, p_align, p_bases, p_reads = pin(hb.raw), pin(hb.align), pin(hb.bases), pin(hb.reads)
-    batch = ReadBatch(hb.mode, p_raw.numpy().view(np.int16), p_align.numpy(), p_bases.numpy(),
-                      p_reads.numpy().view(np.dtype(capi.READ_DTYPE)), hb.read_ids)
-    n_samples = int(batch.reads["raw_len"].astype(np.int64).sum())
-    # a real (non-default) stream: handle 0 would make the library create a private stream that
-    # torch's events could not bracket
+    cfg, opts = workloads.c3(n_reads=args.reads)
+    B = args.block_reads
+    n_blocks = (args.reads + B - 1) // B
+    rounds = (n_blocks + world - 1) // world
+    my_blocks = [j * world + rank for j in range(rounds)]            # may run past n_blocks in the last round: an empty block
+    t_gen0 = time.perf_counter()
+    keep_alive = []
+
+    def pinned(nbytes):
+        t = torch.empty(max(1, nbytes), dtype=torch.uint8, pin_memory=True)
+        keep_alive.append(t)
+        return t.numpy()[:nbytes]
+
+    host_blocks, dev_blocks, n_samples_mine = [], [], 0
+    for b in my_blocks:
+        lo, hi = b * B, min(args.reads, (b + 1) * B)
+        if lo >= hi:
+            host_blocks.append(None); dev_blocks.append(None)
+            continue
+        hb = synth.make_moves_fast(cfg, lo, hi - lo, alloc=pinned)
+        p_reads = pinned(hb.reads.nbytes)
+        p_reads[:] = hb.reads.view(np.uint8).reshape(-1)
+        hb.reads = p_reads.view(np.dtype(capi.READ_DTYPE))
+        host_blocks.append(hb)
+        n_samples_mine += int(hb.reads["raw_len"].astype(np.int64).sum())
+        d = {k: torch.from_numpy(np.ascontiguousarray(getattr(hb, k)).view(np.uint8).reshape(-1)).to(dev) for k in ("raw", "align", "bases", "reads")}
+        cb = hb.to_c()
+        cb.raw, cb.align, cb.bases, cb.reads = d["raw"].data_ptr(), d["align"].data_ptr(), d["bases"].data_ptr(), d["reads"].data_ptr()
+        dev_blocks.append((cb, d))
+    gen_s = time.perf_counter() - t_gen0
+
     stream = torch.cuda.Stream(device=local)
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     eng = GmoveEngine(opts, device=local, stream=stream.cuda_stream)
     NS = eng.n_slots
-    limit = opts.sample_limit
-
-    counts_t = None
+    counts_t = all_counts = None
     if world > 1:
-        counts_t = torch.as_tensor(_DevArr(eng.counts_ptr(), NS), device=f"cuda:{local}")
-        all_counts = torch.empty((world, NS), dtype=torch.int32, device=f"cuda:{local}")
+        counts_t = torch.as_tensor(_DevArr(eng.counts_ptr(), NS), device=dev)
+        all_counts = torch.empty((world, NS), dtype=torch.int32, device=dev)
+    empty_batch = capi.PgmBatch()    # a rank without a block in the last round still joins the all-gather
 
-    def step_resident():
+    def job_resident(summaries=None):
         eng.reset()
-        eng.count()
-        if world > 1:
-            dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
-            eng.set_gathered(all_counts.data_ptr(), world, rank)   # lower-rank / all-rank sums inside k_quota
-        eng.emit()
+        for j in range(rounds):
+            blk = dev_blocks[j]
+            eng.attach_device(blk[0] if blk else empty_batch)
+            eng.count()
+            if world > 1:
+                dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
+                eng.set_gathered(all_counts.data_ptr(), world, rank)
+            eng.emit()
+            if summaries is not None:
+                s = eng.summary()
+                summaries.append((int(s.n_events_examined), int(s.n_events_pass), int(s.n_sel_events), int(s.n_sel_samples)))
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- resident (kernel-only) timing
-    eng.upload(batch)
-    for _ in range(args.warmup):
-        step_resident()
+    # ---- resident timing
+    for _ in range(args.warmup - 1):
+        job_resident()
+    summ = []
+    job_resident(summ)                      # last warm-up pass also collects the per-block counters for the byte model
     barrier()
-    res0 = eng.download()               # result of the last warm-up step: counts for the byte model
-    eng.upload(batch)
-    barrier()
-    # Stage table: an UNTIMED pass of the same K steps with every stage bracketed by an event pair (the pairs cost
-    # ~40 us of stream time per step, so they stay out of the timed region).
     eng.profile_enable(True)
     eng.profile_read()
-    for _ in range(args.steps):
-        step_resident()
+    for _ in range(args.steps):             # UNTIMED pass with every stage bracketed -> stage table
+        job_resident()
     stages = eng.profile_read()
     dom = max(stages, key=lambda k: stages[k][0])
-    # Timed region: only the dominant kernel keeps its event pair (roofline.achieved comes from these K launches).
-    eng.profile_enable(True, only=dom)
+    eng.profile_enable(True, only=dom)      # timed region: only the dominant kernel keeps its event pair
     eng.profile_read()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -341,7 +489,7 @@ def run_own_arm(args):
     barrier()
     e0.record(stream)
     for _ in range(args.steps):
-        step_resident()
+        job_resident()
     e1.record(stream)
     barrier()
     ms_total = e0.elapsed_time(e1)
@@ -349,191 +497,154 @@ def run_own_arm(args):
     dom_timed = eng.profile_read()[dom]
     eng.profile_enable(False)
     clocks = sampler.stop() if rank == 0 else None
-    t_res = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{local}")
+    t_res = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
     ms_step = float(t_res.item()) / args.steps
-
-    # ---- K7 (model rows of the whole batch; scripts/poregen.sh:54-85), timed once around pgm_model_finalize
-    eng.model_begin()
-    eng.reset()
-    eng.upload(batch); eng.count(); eng.emit()
-    eng.download()
-    torch.cuda.synchronize()
-    tm0 = time.perf_counter()
-    rows = eng.model_finalize(1e300)
-    model_ms = (time.perf_counter() - tm0) * 1e3
-    model_info = {"ms": model_ms, "values": int(rows["n"].sum()), "rows": int(rows.size),
-                  "note": "pgm_model_finalize on this rank's C2 batch: median by int64 radix selection + exact 128-bit variance per k-mer, incl. the rows' download"}
-
-    # ---- end to end: pinned host buffers in, the dump TEXT (what the reference fprintf's, formatted on the
-    # device) out to host memory, every step. A second context with PGM_OUT_TEXT does this leg.
-    import copy
-    import ctypes as C
-    topts = copy.copy(opts)
-    topts.output = capi.PGM_OUT_TEXT_ONLY   # what the command line uses: the text, per-slot offsets and counts
     eng.close()
 
-    # Batches in flight: while one batch's text travels device -> host, the next one's inputs travel host -> device
-    # and its kernels run (PCIe is full duplex). Each slot is a context with its own stream; every step still does
-    # its own upload, its own count/[all-gather]/emit and its own download into host memory inside the timed region.
-    class Slot:
-        svb = None      # (aligned batch, stream bytes, stream offsets): upload the compressed signal instead of raw[]
+    # ---- end to end: every block from pinned host memory in, its dump TEXT out to host memory
+    topts = copy.copy(opts)
+    topts.output = capi.PGM_OUT_TEXT_ONLY
+    teng = GmoveEngine(topts, device=local, stream=stream.cuda_stream)
+    if world > 1:
+        counts_t = torch.as_tensor(_DevArr(teng.counts_ptr(), NS), device=dev)
+    text_bytes = [0]
 
-        def __init__(self):
-            self.stream = torch.cuda.Stream(device=local)
-            self.eng = GmoveEngine(topts, device=local, stream=self.stream.cuda_stream)
+    def job_e2e():
+        teng.reset()
+        tb = 0
+        for j in range(rounds):
+            hb = host_blocks[j]
+            if hb is not None:
+                teng.upload(hb)
+            else:
+                teng.attach_device(empty_batch)
+            teng.count()
             if world > 1:
-                self.counts_t = torch.as_tensor(_DevArr(self.eng.counts_ptr(), NS), device=f"cuda:{local}")
-                self.all_counts = torch.empty((world, NS), dtype=torch.int32, device=f"cuda:{local}")
-
-        def submit(self):
-            e = self.eng
-            with torch.cuda.stream(self.stream):
-                e.reset()
-                if Slot.svb is not None:
-                    e.upload_svb(*Slot.svb)
-                else:
-                    e.upload(batch)
-                e.count()
-                if world > 1:
-                    dist.all_gather_into_tensor(self.all_counts.view(-1), self.counts_t)
-                    e.set_gathered(self.all_counts.data_ptr(), world, rank)
-                e.emit()
-
-        def collect(self):
+                dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
+                teng.set_gathered(all_counts.data_ptr(), world, rank)
+            teng.emit()
             r = capi.PgmResult()
-            self.eng._chk(self.eng.lib.pgm_download(self.eng._ctx, C.byref(r)))
-            return r
+            teng._chk(teng.lib.pgm_download(teng._ctx, C.byref(r)))
+            tb += int(C.cast(r.slot_text_off, C.POINTER(C.c_uint64))[NS])
+        text_bytes[0] = tb
 
-    depth = max(1, args.e2e_depth)
-    slots = [Slot() for _ in range(depth)]
-    eng = slots[0].eng
-
-    def run_e2e(k):
-        r = None
-        for i in range(min(depth, k)):
-            slots[i % depth].submit()
-        for i in range(k):
-            sl = slots[i % depth]
-            r = sl.collect()
-            if i + depth < k:
-                sl.submit()
-        return r
-
-    r = run_e2e(max(depth, args.warmup))
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    job_e2e()
     barrier()
     t0 = time.perf_counter()
-    r = run_e2e(args.steps)
+    for _ in range(e2e_steps):
+        job_e2e()
     barrier()
-    e2e_s = (time.perf_counter() - t0) / args.steps
-    t_e2e = torch.tensor([e2e_s], dtype=torch.float64, device=f"cuda:{local}")
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    t_e2e = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     e2e_s = float(t_e2e.item())
-    h2d = int(batch.raw.nbytes + batch.align.nbytes + batch.bases.nbytes + batch.reads.nbytes)
-    text_bytes = int(C.cast(r.slot_text_off, C.POINTER(C.c_uint64))[NS])
-    d2h = int(text_bytes + NS * 16 + batch.n_reads + 48)
-    examined = int(r.n_events_examined)
+    teng.close()
+    h2d = sum(int(hb.raw.nbytes + hb.align.nbytes + hb.bases.nbytes + hb.reads.nbytes) for hb in host_blocks if hb is not None)
+    d2h = int(text_bytes[0] + sum((NS + 1) * 8 + 2 * NS * 4 + hb.n_reads + 48 for hb in host_blocks if hb is not None))
+    pc_h2d, pc_d2h = pcie_calibration(local)
 
-    # ---- the same step fed with the records' svb-zd streams (what a BLOW5 file stores) instead of int16 samples:
-    # k_svb_decode produces raw[] in HBM. Single-GPU runs only (the encoder here is numpy).
-    svb_info = None
-    if world == 1 and not args.no_svb:
-        ab = synth.align_raw(hb, 8)
-        sb, so = synth.svb_streams(ab)
-        p_sb, p_so = pin(sb), pin(so)
-        ab = ReadBatch(ab.mode, ab.raw, batch.align, batch.bases, pin(ab.reads).numpy().view(np.dtype(capi.READ_DTYPE)), ab.read_ids)
-        svb_args = (ab, p_sb.numpy(), p_so.numpy().view(np.uint64))
-        e = slots[0].eng
-        with torch.cuda.stream(slots[0].stream):
-            for _ in range(3):
-                e.upload_svb(*svb_args)
-            e.sync()
-            e.profile_enable(True); e.profile_read()
-            for _ in range(args.steps):
-                e.upload_svb(*svb_args)
-            st_svb = e.profile_read()["svb"]
-            e.profile_enable(False)
-        live = np.zeros(ab.raw.size + 1, np.int32)          # the padding between records is not written by the decoder
-        np.add.at(live, ab.reads["raw_off"].astype(np.int64), 1)
-        np.add.at(live, ab.reads["raw_off"].astype(np.int64) + ab.reads["raw_len"].astype(np.int64), -1)
-        live = np.cumsum(live[:-1]) > 0
-        assert np.array_equal(e.device_raw(ab.raw.size)[live], ab.raw[live]), "k_svb_decode: samples differ from the encoder's input"
-        Slot.svb = svb_args
-        rs = run_e2e(max(depth, args.warmup))
-        barrier()
-        t0 = time.perf_counter()
-        rs = run_e2e(args.steps)
-        barrier()
-        svb_s = (time.perf_counter() - t0) / args.steps
-        Slot.svb = None
-        assert int(rs.n_sel_samples) == int(r.n_sel_samples) and int(C.cast(rs.slot_text_off, C.POINTER(C.c_uint64))[NS]) == text_bytes
-        k_ms = st_svb[0] / max(1, st_svb[1])
-        alg_svb = int(sb.nbytes + 2 * n_samples)
-        pk, _ = measured_peak()
-        svb_info = {"kernel": "k_svb_decode", "ms_per_launch": k_ms, "stream_bytes": int(sb.nbytes), "bytes_per_sample": sb.nbytes / n_samples,
-                    "algorithmic_bytes": alg_svb, "gbs": alg_svb / (k_ms * 1e-3) / 1e9, "frac": alg_svb / (k_ms * 1e-3) / 1e9 / pk,
-                    "e2e": {"value": n_samples / svb_s, "unit": UNIT, "ms_per_step": svb_s * 1e3,
-                            "h2d_bytes_per_step": int(sb.nbytes + so.nbytes + batch.align.nbytes + batch.bases.nbytes + batch.reads.nbytes),
-                            "d2h_bytes_per_step": d2h},
-                    "note": "same C2 step with the records' slow5 svb-zd streams uploaded instead of int16 samples; decoded in HBM"}
-
-    tot = torch.tensor([n_samples, examined, int(r.n_sel_events), int(r.n_sel_samples)], dtype=torch.float64, device=f"cuda:{local}")
+    sm = np.array(summ, dtype=np.float64).sum(axis=0) if summ else np.zeros(4)
+    tot = torch.tensor([n_samples_mine, sm[0], sm[1], sm[2], sm[3], h2d, d2h, pc_h2d, pc_d2h], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot)
-    tot_samples, tot_events, tot_sel_ev, tot_sel_samp = [float(x) for x in tot.tolist()]
+    tot_samples, tot_events, tot_pass, tot_sel_ev, tot_sel_samp, tot_h2d, tot_d2h, sum_h2d_gbs, sum_d2h_gbs = [float(x) for x in tot.tolist()]
 
     if rank == 0:
-        # ---- byte model per stage (this rank), DESIGN.md "Kernels and their algorithmic bytes"
-        rd = batch.reads
-        T = int(rd["align_len"].astype(np.int64).sum()); NB = int(rd["seq_len"].astype(np.int64).sum()); R = batch.n_reads
-        E_pass, E_sel, S_sel = int(res0.n_events_pass), int(res0.ev_len.size), int(res0.samples.size)
-        act = np.unique(res0.ev_read)
-        S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
-        alg = {"prep": 120 * R, "decode": T + NB + 88 * R + 16 * E_pass, "place": 32 * E_pass + 8 * R,
-               "sort": 16 * E_pass + 12 * E_sel, "select": 16 * NS, "stats": (2 * S_act + 48 * R) if opts.scaling else 0,
-               "gather": 2 * S_sel + 8 * S_sel + 20 * E_sel,
-               "scan": 12 * E_sel, "misc": 8 * NS, "text": 0}
-        alg_step = 2 * n_samples + T + NB + 24 * R + 8 * S_sel + 12 * E_sel + 4 * NS
+        T = sum(int(hb.reads["align_len"].astype(np.int64).sum()) for hb in host_blocks if hb is not None)
+        NB = sum(int(hb.reads["seq_len"].astype(np.int64).sum()) for hb in host_blocks if hb is not None)
+        R = sum(hb.n_reads for hb in host_blocks if hb is not None)
+        nblk = sum(1 for hb in host_blocks if hb is not None)
+        E_pass, E_sel, S_sel = int(sm[1]), int(sm[2]), int(sm[3])
+        alg = stage_bytes(opts.scaling, T, NB, R, NS * nblk, 0, E_pass, E_sel, S_sel)
+        alg_step = 2 * n_samples_mine + T + NB + 24 * R + 8 * S_sel + 12 * E_sel + 4 * NS * nblk
         peak, peak_src = measured_peak()
         stage_rows = {}
         for name, (ms, ln) in stages.items():
             per = ms / args.steps
-            stage_rows[name] = {"ms_per_step": per, "launches_per_step": ln / args.steps,
-                                "algorithmic_bytes": alg.get(name, 0),
+            stage_rows[name] = {"ms_per_step": per, "launches_per_step": ln / args.steps, "algorithmic_bytes": alg.get(name, 0),
                                 "gbs": (alg.get(name, 0) / (per * 1e-3) / 1e9) if per > 0 else None}
-        # the dominant kernel's duration as measured INSIDE the timed region (its own event pair only)
+        dom_launches = max(1.0, stage_rows[dom]["launches_per_step"])
         dom_per_launch_ms = dom_timed[0] / max(1, dom_timed[1])
-        achieved = stage_rows[dom]["algorithmic_bytes"] / max(1.0, stage_rows[dom]["launches_per_step"]) / (dom_per_launch_ms * 1e-3) / 1e9
+        alg_per_launch = stage_rows[dom]["algorithmic_bytes"] / dom_launches
+        achieved = alg_per_launch / (dom_per_launch_ms * 1e-3) / 1e9
+        pcie_need_s = max(tot_h2d / world / (sum_h2d_gbs / world * 1e9), tot_d2h / world / (sum_d2h_gbs / world * 1e9))
         line = {"metric": METRIC, "value": tot_samples / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic", "config": dict(workload_desc(args.reads), parallelism=f"read-range x{world}"),
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic", "config": workload_desc(args.reads, B, world),
                 "events_per_sec": tot_events / (ms_step * 1e-3),
+                "events_examined_per_step": tot_events, "events_pass_per_step": tot_pass,
                 "events_selected_per_step": tot_sel_ev, "samples_selected_per_step": tot_sel_samp,
                 "e2e": {"value": tot_samples / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "events_per_sec": tot_events / e2e_s,
-                        "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "h2d_bytes_per_step": int(tot_h2d), "d2h_bytes_per_step": int(tot_d2h), "steps": e2e_steps,
                         "output": "dump text (%.8f, formatted on the device), per-k-mer text offsets and counts, per-record flags",
-                        "batches_in_flight": depth, "host_binding": numa},
+                        "pcie_peak_gbs": {"h2d": sum_h2d_gbs, "d2h": sum_d2h_gbs, "how": "pinned cudaMemcpyAsync, 1 GiB, both directions at once, all ranks at once (sum over ranks)"},
+                        "frac_of_pcie": pcie_need_s / e2e_s, "host_binding": numa},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": ncu_traffic(dom), "peak_source": peak_src,
-                             "algorithmic_bytes_per_launch": stage_rows[dom]["algorithmic_bytes"] / max(1.0, stage_rows[dom]["launches_per_step"]),
-                             "ms_per_launch": dom_per_launch_ms},
+                             "algorithmic_bytes_per_launch": alg_per_launch, "ms_per_launch": dom_per_launch_ms,
+                             "launches_per_step": dom_launches, "note": "rank 0's share of the job; per-launch = average over the blocks of a step"},
                 "roofline_step": {"algorithmic_bytes": alg_step, "gbs": alg_step / (ms_step * 1e-3) / 1e9,
-                                  "frac": alg_step / (ms_step * 1e-3) / 1e9 / peak},
+                                  "frac": alg_step / (ms_step * 1e-3) / 1e9 / peak, "note": "rank 0's share / step time"},
                 "stages": stage_rows, "stages_note": "per-stage times from an untimed pass of the same steps with all stage timers on; the timed region brackets only the roofline kernel",
-                "model_aggregation": model_info, "clocks": clocks}
-        if svb_info:
-            line["svb_signal"] = svb_info
+                "setup": {"generate_and_upload_s": gen_s}, "clocks": clocks}
+        if world == 1 and not args.no_c2:
+            line["c2"] = c2_leg(args, local, stream)
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline_leg(args.cpu_reads)
         emit_line(line)
-    for sl in slots:
-        sl.eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def c2_leg(args, local, stream):
+    """configs[1] (round 1's bench workload), resident: 10,000 RNA004 ss records, -k 5 --rna --scaling 1 --sample_limit 5000
+    --min_dur 20 --max_dur 40. One batch per step."""
+    import numpy as np
+    import torch
+    from poregen_b200 import synth, workloads
+    from poregen_b200.gmove import GmoveEngine
+    cfg, opts = workloads.c2()
+    hb = synth.make_batch(cfg)
+    n_samples = int(hb.reads["raw_len"].astype(np.int64).sum())
+    with GmoveEngine(opts, device=local, stream=stream.cuda_stream) as eng:
+        eng.upload(hb)
+
+        def step():
+            eng.reset(); eng.count(); eng.emit()
+        for _ in range(3):
+            step()
+        res = eng.download()
+        eng.upload(hb)
+        eng.profile_enable(True); eng.profile_read()
+        for _ in range(args.steps):
+            step()
+        stages = eng.profile_read()
+        eng.profile_enable(False)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(args.steps):
+            step()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.steps
+    rd = hb.reads
+    T = int(rd["align_len"].astype(np.int64).sum()); NB = int(rd["seq_len"].astype(np.int64).sum()); R = hb.n_reads
+    act = np.unique(res.ev_read)
+    S_act = int((rd["raw_len"][act].astype(np.int64) - rd["trim"][act].astype(np.int64)).sum())
+    alg = stage_bytes(1, T, NB, R, res.n_slots, S_act, res.n_events_pass, res.ev_len.size, res.samples.size)
+    alg_step = 2 * n_samples + T + NB + 24 * R + 8 * res.samples.size + 12 * res.ev_len.size + 4 * res.n_slots
+    peak, _ = measured_peak()
+    rows = {k: {"ms": v[0] / args.steps, "gbs": alg.get(k, 0) / (v[0] / args.steps * 1e-3) / 1e9 if v[0] > 0 else None} for k, v in stages.items() if v[0] > 0}
+    return {"workload": "C2 synthetic RNA004 ss records (10,000 reads): -k 5 --rna --scaling 1 --sample_limit 5000 --min_dur 20 --max_dur 40",
+            "value": n_samples / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+            "roofline_step": {"algorithmic_bytes": alg_step, "frac": alg_step / (ms * 1e-3) / 1e9 / peak}, "stages": rows}
 
 
 _JSON_FD = None
@@ -561,15 +672,16 @@ def main():
     protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
-    ap.add_argument("--reads", type=int, default=10000, help="records per GPU (C2 = 10000)")
-    ap.add_argument("--ref-reads", type=int, default=1500, help="--impl reference: records per step")
-    ap.add_argument("--cpu-reads", type=int, default=3000, help="cpu_baseline leg: records in the sample")
+    ap.add_argument("--reads", type=int, default=C3_READS, help="records of the whole job (C3 = 100000)")
+    ap.add_argument("--block-reads", type=int, default=3125, help="consecutive records handed over per call (per rank and round)")
+    ap.add_argument("--ref-reads", type=int, default=1000, help="--impl reference: records per step (prefix of the same reads)")
+    ap.add_argument("--cpu-reads", type=int, default=2000, help="cpu_baseline leg: records in the sample")
+    ap.add_argument("--e2e-steps", type=int, default=3, help="steps of the end-to-end leg (each moves ~55 GB over PCIe)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-svb", action="store_true", help="skip the compressed-signal (svb-zd) leg")
-    ap.add_argument("--e2e-depth", type=int, default=2, help="e2e leg: batches in flight (1 = strictly serial steps)")
+    ap.add_argument("--no-c2", action="store_true", help="skip the C2 comparison leg")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "own":
         args.warmup = 3

@@ -171,6 +171,10 @@ int pgm_count(pgm_ctx *ctx);  /* decode + filters + per-slot counts of passing e
 int pgm_emit(pgm_ctx *ctx);   /* stable bucketing, sample_limit, Med-MAD, sample gather/format    */
 int pgm_download(pgm_ctx *ctx, pgm_result *out); /* D2H + stream sync                             */
 int pgm_sync(pgm_ctx *ctx);
+/* The counters of pgm_result (n_events_examined / n_events_pass / n_sel_events / n_sel_samples) of the batch pgm_emit
+ * just finished, without moving any array to the host (every pointer of *out is NULL). Synchronises; the batch stays
+ * emitted, so pgm_download can still follow. For callers that keep the result in HBM (benchmarks, K7). */
+int pgm_summary(pgm_ctx *ctx, pgm_result *out);
 
 /* Compressed signal. Replaces the host-side signal decompression slow5lib runs inside
  * slow5_get / slow5_rec_parse (slow5lib/src/slow5.c:2876-2905 -> slow5_press.c:1085-1130 ptr_depress_svb_zd ->

@@ -118,7 +118,7 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
-    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw", "pgm_model_dwell",
+    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw", "pgm_model_dwell", "pgm_summary",
 ]
 PGM_N_STAGES = 11
 # pgm_model_row (include/pgm_gmove.h)
@@ -160,6 +160,8 @@ def load() -> C.CDLL:
         getattr(lib, name).restype = C.c_int
     lib.pgm_download.argtypes = [C.c_void_p, P(PgmResult)]
     lib.pgm_download.restype = C.c_int
+    lib.pgm_summary.argtypes = [C.c_void_p, P(PgmResult)]
+    lib.pgm_summary.restype = C.c_int
     lib.pgm_counts_device.argtypes = [C.c_void_p, P(C.c_void_p)]
     lib.pgm_counts_device.restype = C.c_int
     lib.pgm_totals_device.argtypes = [C.c_void_p, P(C.c_void_p)]

@@ -880,6 +880,21 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     return PGM_OK;
 }
 
+int pgm_summary(pgm_ctx *c, pgm_result *out) {
+    if (!c || !out) return PGM_ERR_ARG;
+    if (c->state != ST_EMITTED) return fail(c, PGM_ERR_STATE, "pgm_summary needs pgm_emit first");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemcpyAsync(c->h_scalars, SCALARS(c), sizeof(Scalars), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    const Scalars s = *c->h_scalars;
+    memset(out, 0, sizeof *out);
+    out->n_slots = c->opts.n_slots; out->n_reads = c->db.n_reads;
+    out->n_events_examined = s.examined; out->n_events_pass = s.n_pass;
+    out->n_sel_events = s.n_sel; out->n_sel_samples = s.n_sel_samples;
+    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays");
+    return PGM_OK;
+}
+
 static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode", "scan", "place", "sort", "select", "stats", "gather", "misc", "text", "svb"};
 
 const char *pgm_stage_name(int stage) { return (stage >= 0 && stage < PGM_N_STAGES) ? kStageNames[stage] : "?"; }

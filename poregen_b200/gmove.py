@@ -111,6 +111,12 @@ class GmoveEngine:
         self._chk(self.lib.pgm_download(self._ctx, C.byref(r)))
         return GmoveResult.from_c(r, want_text=self.opts.output != capi.PGM_OUT_F64)
 
+    def summary(self) -> capi.PgmResult:
+        """pgm_summary: the emitted batch's counters only (nothing but 48 bytes leaves the device)."""
+        r = capi.PgmResult()
+        self._chk(self.lib.pgm_summary(self._ctx, C.byref(r)))
+        return r
+
     def sync(self):
         self._chk(self.lib.pgm_sync(self._ctx))
 

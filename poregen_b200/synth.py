@@ -406,3 +406,88 @@ def write_bam(batch: ReadBatch, path: str, block: int = 3000):
         for o in range(0, len(raw), block):
             f.write(member(bytes(raw[o:o + block])))
         f.write(member(b""))        # the end-of-file marker block
+
+
+# ---------------------------------------------------------------------------------------------
+# Fast counter-based generator for the big move-table shapes (C3 / C5): synth_fast.c, built by
+# __graft_entry__.build() as libpgm_synth.so. Every read is a function of (seed, global read index).
+# ---------------------------------------------------------------------------------------------
+_FAST_LIB = None
+
+
+def _fast_lib():
+    global _FAST_LIB
+    if _FAST_LIB is None:
+        import ctypes as C
+        here = os.path.dirname(os.path.abspath(__file__))
+        path = os.path.join(here, "libpgm_synth.so")
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} missing: run __graft_entry__.build() first")
+        _FAST_LIB = C.CDLL(path)
+    return _FAST_LIB
+
+
+def make_moves_fast(cfg: SynthConfig, read_lo: int = 0, n_reads: Optional[int] = None, alloc=None) -> ReadBatch:
+    """Reads [read_lo, read_lo + n_reads) of the move-table workload `cfg` describes (cfg.n_reads = the whole
+    job). `alloc(nbytes)` returns a uint8 numpy array to put the big arrays in (e.g. pinned memory)."""
+    import ctypes as C
+    assert cfg.mode in (capi.PGM_MODE_MOVES_CHAR, capi.PGM_MODE_MOVES_I8)
+    lib = _fast_lib()
+    n = cfg.n_reads - read_lo if n_reads is None else n_reads
+    hi = read_lo + n
+    alloc = alloc or (lambda nbytes: np.empty(nbytes, np.uint8))
+    # per-read scalars: prefixes of fixed streams, so a read does not depend on how the job is cut
+    ln = np.random.default_rng([cfg.seed, 1]).lognormal(np.log(cfg.median_samples), cfg.sigma_len, hi)[read_lo:]
+    target = np.clip(ln, cfg.min_samples, cfg.max_samples)
+    nb = np.maximum((target / (cfg.stride * cfg.mean_dwell_strides)).astype(np.int64), 12).astype(np.uint32)
+    offset = np.random.default_rng([cfg.seed, 2]).integers(cfg.offset_lo, cfg.offset_hi + 1, hi)[read_lo:].astype(np.int32)
+    offset[offset == 0] = 1
+    tail = np.random.default_rng([cfg.seed, 3]).integers(0, cfg.stride, hi)[read_lo:].astype(np.int64)
+    scale = cfg.range_ / cfg.digitisation
+    q = 1.0 - 1.0 / cfg.mean_dwell_strides
+    thr = np.array([min(2 ** 32 - 1, int(q ** j * 2 ** 32)) for j in range(1, cfg.max_dwell_strides)], np.uint32)
+    level = np.rint(np.random.default_rng([cfg.seed, 4]).normal(cfg.level_mean, cfg.level_sd, 4096) / scale).astype(np.int32)
+
+    class P(C.Structure):
+        _fields_ = [("seed", C.c_uint64), ("stride", C.c_uint32), ("n_thr", C.c_uint32), ("dwell_thr", C.c_void_p),
+                    ("level", C.c_void_p), ("filler", C.c_int32), ("lo_code", C.c_int32), ("hi_code", C.c_int32),
+                    ("spike_thr", C.c_uint32), ("noise_num", C.c_int32), ("moves_char", C.c_uint32)]
+    p = P(cfg.seed, cfg.stride, thr.size, thr.ctypes.data, level.ctypes.data, int(round(cfg.level_mean / scale)),
+          int(round(15.0 / scale)), int(round(230.0 / scale)), int(cfg.spike_frac * 2 ** 32),
+          int(round(cfg.noise_sd / scale / 37837.2 * 2 ** 20)), 1 if cfg.mode == capi.PGM_MODE_MOVES_CHAR else 0)
+    moves = np.zeros(n, np.uint64)
+    lib.pgm_synth_moves_len(C.byref(p), C.c_uint64(read_lo), C.c_uint32(n), C.c_void_p(nb.ctypes.data), C.c_void_p(moves.ctypes.data))
+    moves = moves.astype(np.int64)
+    raw_len = moves * cfg.stride + tail
+    padded = (raw_len + 7) // 8 * 8
+    raw_off = np.zeros(n + 1, np.int64); np.cumsum(padded, out=raw_off[1:])
+    al_off = np.zeros(n + 1, np.int64); np.cumsum(moves, out=al_off[1:])
+    sq_off = np.zeros(n + 1, np.int64); np.cumsum(nb.astype(np.int64), out=sq_off[1:])
+    raw = alloc(int(raw_off[-1]) * 2).view(np.int16)
+    align = alloc(int(al_off[-1]))
+    bases = alloc(int(sq_off[-1]))
+    u64 = lambda a: np.ascontiguousarray(a, dtype=np.uint64)
+    ro, rc, ao, so = u64(raw_off[:-1]), u64(padded), u64(al_off[:-1]), u64(sq_off[:-1])
+    lib.pgm_synth_moves_fill(C.byref(p), C.c_uint64(read_lo), C.c_uint32(n), C.c_void_p(nb.ctypes.data), C.c_void_p(offset.ctypes.data),
+                             C.c_void_p(ro.ctypes.data), C.c_void_p(rc.ctypes.data), C.c_void_p(ao.ctypes.data), C.c_void_p(so.ctypes.data),
+                             C.c_void_p(raw.ctypes.data), C.c_void_p(align.ctypes.data), C.c_void_p(bases.ctypes.data))
+    reads = np.zeros(n, np.dtype(capi.READ_DTYPE))
+    reads["raw_off"] = raw_off[:-1]; reads["raw_len"] = raw_len
+    reads["align_off"] = al_off[:-1]; reads["align_len"] = moves
+    reads["seq_off"] = sq_off[:-1]; reads["seq_len"] = nb; reads["fastq_len"] = nb
+    reads["digitisation"] = cfg.digitisation; reads["offset"] = offset.astype(np.float64); reads["range"] = cfg.range_
+    reads["stride"] = cfg.stride
+    ids = [f"read_{cfg.seed & 0xffff:04x}_{i:07d}" for i in range(read_lo, hi)]
+    return ReadBatch(cfg.mode, raw, align, bases, reads, ids)
+
+
+def rebase(batch: ReadBatch, lo: int, hi: int) -> ReadBatch:
+    """Records [lo, hi) as a self-contained batch: views of the big arrays from the first record's data on, offsets
+    rebased (the records of a generated batch lie in order). What a host that streams a file in pieces hands over."""
+    rd = batch.reads[lo:hi].copy()
+    r0, a0, s0 = int(rd["raw_off"][0]), int(rd["align_off"][0]), int(rd["seq_off"][0])
+    last = rd[-1]
+    r1 = (int(last["raw_off"]) + int(last["raw_len"]) + 7) // 8 * 8
+    a1, s1 = int(last["align_off"]) + int(last["align_len"]), int(last["seq_off"]) + int(last["seq_len"])
+    rd["raw_off"] -= r0; rd["align_off"] -= a0; rd["seq_off"] -= s0
+    return ReadBatch(batch.mode, batch.raw[r0:min(r1, batch.raw.size)], batch.align[a0:a1], batch.bases[s0:s1], rd, batch.read_ids[lo:hi])
