@@ -171,7 +171,7 @@ int pgm_count(pgm_ctx *ctx);  /* decode + filters + per-slot counts of passing e
 int pgm_emit(pgm_ctx *ctx);   /* stable bucketing, sample_limit, Med-MAD, sample gather/format    */
 int pgm_download(pgm_ctx *ctx, pgm_result *out); /* D2H + stream sync                             */
 int pgm_sync(pgm_ctx *ctx);
-/* The counters of pgm_result (n_events_examined / n_events_pass / n_sel_events / n_sel_samples) of the batch pgm_emit
+/* The four counters of a pgm_result: n_events_examined, n_events_pass, n_sel_events, n_sel_samples of the batch pgm_emit
  * just finished, without moving any array to the host (every pointer of *out is NULL). Synchronises; the batch stays
  * emitted, so pgm_download can still follow. For callers that keep the result in HBM (benchmarks, K7). */
 int pgm_summary(pgm_ctx *ctx, pgm_result *out);
