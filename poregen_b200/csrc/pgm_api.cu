@@ -545,8 +545,13 @@ int pgm_count(pgm_ctx *c) {
             io.n_pass = P<uint32_t>(c->n_pass);
             io.ticket = MISC(c) + 1; io.order = P<uint32_t>(c->rec_order);
             io.hist = HIST(c); io.ntiles_cap = c->sort_ntiles; io.hist_mask = (1u << per) - 1;
-            const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
-            k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            if (c->db.mode == PGM_MODE_SS) {
+                const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
+                k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
+            } else {   // move tables: one CTA per record at a time
+                const uint32_t full = (uint32_t)c->n_sm * 3;
+                k_decode_moves<<<R < full ? R : full, DM_THREADS, 0, st>>>(d, c->db, io);
+            }
             c->launches++;
             t.stop();
             StageTimer t2(c, PGM_STAGE_PLACE);

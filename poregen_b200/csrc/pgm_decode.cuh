@@ -437,6 +437,183 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_decode_moves: the move-table decoder (PGM_MODE_MOVES_CHAR / _I8), one CTA per record at a time.
+// Same semantics as decode_moves_record above (reference gmove.cpp:620-690, 1182-1252); the work is laid out
+// for long records (C3: 8,700 moves, 4,200 events per record):
+//   * a step is DM_CHUNK move bytes, eight per thread (one aligned 8-byte load); a block scan numbers the set
+//     moves, a second one carries the position of the last set move in front of a thread's bytes;
+//   * the bases the step's events need are one contiguous window of the sequence: staged once as 2-bit codes in
+//     shared memory; a thread's events are consecutive, so its k-mer id ROLLS (one code per event);
+//   * every event is evaluated ONCE; the quota look-ups of a thread's (up to eight) events are issued together;
+//     passing events are kept in registers until a third block scan gives their place in the record's
+//     temporary (position order).
+#define DM_THREADS 256
+#define DM_WARPS (DM_THREADS / 32)
+#define DM_PER 8
+#define DM_CHUNK (DM_THREADS * DM_PER)
+
+__global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBatch b, DecodeIO gio) {
+    __shared__ uint8_t sm_codes[DM_CHUNK + 32];
+    __shared__ uint32_t sm_cnt_w[DM_WARPS], sm_pass_w[DM_WARPS];
+    __shared__ int sm_last_w[DM_WARPS];
+    __shared__ uint32_t sm_rec;
+    __shared__ uint32_t sm_cons[DEC_SLOT_SMEM], sm_cnt[DEC_SLOT_SMEM];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    DecodeIO io = gio;
+    const bool local_slots = o.n_slots <= DEC_SLOT_SMEM;
+    if (local_slots) {
+        for (uint32_t s = tid; s < o.n_slots; s += DM_THREADS) { sm_cons[s] = gio.consumed[s]; sm_cnt[s] = 0; }
+        io.consumed = sm_cons; io.counts = sm_cnt;
+    }
+    const uint32_t one8 = (b.mode == PGM_MODE_MOVES_CHAR) ? 0x31313131u : 0x01010101u;
+    const uint32_t idmask = (o.k >= 16) ? 0xffffffffu : ((1u << (2 * o.k)) - 1u);
+    uint32_t my_exam = 0;
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) {
+            const uint32_t t = atomicAdd(io.ticket, 1u);
+            sm_rec = (t < b.n_reads) ? io.order[t] : 0xffffffffu;
+        }
+        __syncthreads();
+        const uint32_t r = sm_rec;
+        if (r >= b.n_reads) break;
+        if (io.rflags[r] != 0) { if (tid == 0) io.n_pass[r] = 0; continue; }
+        const pgm_read rd = b.reads[r];
+        const uint8_t *mv = b.align + rd.align_off;
+        const uint8_t *seq = b.bases + rd.seq_off;
+        const uint32_t M = rd.align_len;
+        const uint64_t n_sig = (uint64_t)rd.raw_len - rd.trim;
+        const uint32_t head = (uint32_t)((uintptr_t)mv & 7);
+        const uint8_t *abase = mv - head;
+        const uint32_t span = head + M;
+        uint32_t *t_key = io.sc_key + rd.align_off, *t_start = io.sc_start + rd.align_off, *t_len = io.sc_end + rd.align_off;
+        uint32_t ones_carry = 0, pbase = 0;
+        int last_carry = -1;
+        for (uint32_t cb = 0; cb < span; cb += DM_CHUNK) {
+            const uint32_t off = cb + DM_PER * tid;
+            uint2 x = make_uint2(0u, 0u);
+            if (off < span) x = __ldg(reinterpret_cast<const uint2 *>(abase + off));   // a word with one valid byte lies inside the allocation
+            const int p0 = (int)off - (int)head;                                       // string position of the thread's byte 0
+            const uint32_t lo = (off < head) ? min((uint32_t)DM_PER, head - off) : 0u;
+            const uint32_t hi = (off >= span) ? 0u : min((uint32_t)DM_PER, span - off);
+            uint32_t bits = byte_nibble(byte_is_zero(x.x ^ one8)) | (byte_nibble(byte_is_zero(x.y ^ one8)) << 4);
+            bits &= (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+            const uint32_t cnt = __popc(bits);
+            const int lastpos = bits ? p0 + 31 - __clz(bits) : -1;
+            // block scans: set moves in front of the thread (sum), last set position in front of it (max)
+            const uint32_t inc_cnt = warp_incl_scan_add(cnt);
+            const int inc_last = warp_incl_scan_max(lastpos);
+            int ex_last_w = __shfl_up_sync(0xffffffffu, inc_last, 1);
+            if (lane == 0) ex_last_w = -1;
+            if (lane == 31) { sm_cnt_w[wid] = inc_cnt; sm_last_w[wid] = inc_last; }
+            __syncthreads();
+            uint32_t wbase_cnt = 0, tot_cnt = 0;
+            int wbase_last = -1, tot_last = -1;
+#pragma unroll
+            for (int w = 0; w < DM_WARPS; w++) {
+                const uint32_t c = sm_cnt_w[w];
+                const int l = sm_last_w[w];
+                if ((uint32_t)w < wid) { wbase_cnt += c; wbase_last = max(wbase_last, l); }
+                tot_cnt += c; tot_last = max(tot_last, l);
+            }
+            const uint32_t li0 = wbase_cnt + inc_cnt - cnt;                           // set moves of the step in front of the thread
+            const int ex_last = max(last_carry, max(wbase_last, ex_last_w));
+            // ---- the bases of the step's events as codes. The set move with `rank` set moves of the record in front of it
+            // closes event rank-1, examined when rank > m, labelled with the k-mer at base s_off + rank - m - 1.
+            const int64_t w0 = (int64_t)o.s_off + (int64_t)ones_carry - (int64_t)o.m - 1;   // base of the step's first set move
+            const uint32_t nwin = tot_cnt ? tot_cnt + o.k - 1 : 0u;
+            for (uint32_t i = tid; i < nwin; i += DM_THREADS) {
+                const int64_t sp = w0 + i;
+                uint32_t c = 0xFF;
+                if (sp >= 0 && sp < (int64_t)rd.seq_len) c = pgm_base_code(__ldg(seq + sp), o.fourth, false);   // U4: beyond the sequence = no match
+                sm_codes[i] = (uint8_t)c;
+            }
+            __syncthreads();
+            // ---- the thread's events (its own set bits: consecutive events, consecutive bases)
+            uint32_t ev_slot[DM_PER], ev_s2[DM_PER], ev_len[DM_PER];
+            uint32_t cand = 0;                       // bit i: byte i closes an event that passed everything but the quota
+            if (bits) {
+                uint32_t id = 0, run = 0;            // run = consecutive valid codes ending at the newest one (saturates at k)
+                for (uint32_t t = 0; t + 1 < o.k; t++) {
+                    const uint32_t c = sm_codes[li0 + t];
+                    id = ((id << 2) | (c & 3u)) & idmask;
+                    run = (c == 0xFF) ? 0u : min(run + 1u, o.k);
+                }
+                uint32_t j = 0;
+                int prev = ex_last;
+#pragma unroll
+                for (int i = 0; i < DM_PER; i++) {
+                    ev_slot[i] = 0; ev_s2[i] = 0; ev_len[i] = 0;
+                    if ((bits >> i) & 1u) {
+                        const uint32_t c = sm_codes[li0 + j + o.k - 1];
+                        id = ((id << 2) | (c & 3u)) & idmask;
+                        run = (c == 0xFF) ? 0u : min(run + 1u, o.k);
+                        const uint32_t rank = ones_carry + li0 + j;
+                        const int p = p0 + i;
+                        if (rank > o.m) {
+                            my_exam++;
+                            const uint32_t start = (uint32_t)((uint64_t)(uint32_t)prev * rd.stride);
+                            const uint32_t end = (uint32_t)((uint64_t)(uint32_t)p * rd.stride);
+                            const uint32_t dur = end - start;
+                            const uint32_t sl = (run >= o.k) ? pgm_slot_of(o, id) : PGM_INVALID;
+                            const uint32_t a = (start < o.margin) ? 0u : start - o.margin;                 // U2
+                            const uint32_t e1 = end + o.margin;
+                            const uint32_t e2 = ((uint64_t)e1 > n_sig) ? (uint32_t)n_sig : e1;
+                            if (!(dur > o.max_dur) && !(dur < o.min_dur) && sl != PGM_INVALID && a < e2) {   // gmove.cpp:641-662, U3
+                                cand |= 1u << i;
+                                ev_slot[i] = sl; ev_s2[i] = a; ev_len[i] = e2 - a;
+                            }
+                        }
+                        prev = p;
+                        j++;
+                    }
+                }
+            }
+            // quota look-ups of all candidates together (gmove.cpp:650-652), then the survivors
+            uint32_t cons[DM_PER];
+#pragma unroll
+            for (int i = 0; i < DM_PER; i++) cons[i] = ((cand >> i) & 1u) ? io.consumed[ev_slot[i]] : 0xffffffffu;
+            uint32_t okmask = 0;
+#pragma unroll
+            for (int i = 0; i < DM_PER; i++)
+                if (((cand >> i) & 1u) && cons[i] < o.limit) { okmask |= 1u << i; atomicAdd(io.counts + ev_slot[i], 1u); }
+            const uint32_t np = __popc(okmask);
+            const uint32_t inc_p = warp_incl_scan_add(np);
+            if (lane == 31) sm_pass_w[wid] = inc_p;
+            __syncthreads();
+            uint32_t wbase_p = 0, tot_p = 0;
+#pragma unroll
+            for (int w = 0; w < DM_WARPS; w++) {
+                const uint32_t c = sm_pass_w[w];
+                if ((uint32_t)w < wid) wbase_p += c;
+                tot_p += c;
+            }
+            uint32_t wr = pbase + wbase_p + inc_p - np;
+#pragma unroll
+            for (int i = 0; i < DM_PER; i++)
+                if ((okmask >> i) & 1u) { t_key[wr] = ev_slot[i]; t_start[wr] = ev_s2[i]; t_len[wr] = ev_len[i]; wr++; }
+            pbase += tot_p;
+            ones_carry += tot_cnt;
+            last_carry = max(last_carry, tot_last);
+        }
+        if (tid == 0) {
+            const bool bad = ones_carry <= o.m;                                        // U1
+            io.n_pass[r] = bad ? 0u : pbase;
+            if (bad) io.rflags[r] |= (PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED);
+        }
+    }
+    my_exam = warp_sum_t<uint32_t>(my_exam);
+    if (lane == 0 && my_exam) atomicAdd(io.examined, (unsigned long long)my_exam);
+    if (local_slots) {
+        __syncthreads();
+        for (uint32_t s = tid; s < o.n_slots; s += DM_THREADS) {
+            const uint32_t n = sm_cnt[s];
+            if (n) atomicAdd(gio.counts + s, n);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 #ifndef DEC_MIN_CTAS
 #define DEC_MIN_CTAS 4
 #endif
