@@ -10,9 +10,16 @@ PKG="$(cd "$HERE/../.." && pwd)"
 SLOW5LIB="${SLOW5LIB:-/root/reference/slow5lib}"
 OUT="$PKG/bin/poregen"
 if [ ! -d "$SLOW5LIB/src" ]; then
+    # no sources to rebuild from (the GPU box): the prebuilt binary must match the sources that travelled with it
+    SRC_HASH="$(cat "$HERE/gmove_cli.cpp" "$HERE/bam_reader.hpp" "$HERE/reform.inc" "$PKG/../include/pgm_gmove.h" | sha256sum | cut -c1-64)"
+    if [ -x "$OUT" ] && [ "$("$OUT" --build-info 2>/dev/null || true)" != "$SRC_HASH" ]; then
+        echo "build_cli: $OUT is STALE (built from other sources than the tree holds) and $SLOW5LIB is absent: cannot rebuild" >&2; exit 3
+    fi
     echo "build_cli: $SLOW5LIB not present; keeping prebuilt $OUT (if any)"; exit 0
 fi
-if [ -x "$OUT" ] && [ "$OUT" -nt "$HERE/gmove_cli.cpp" ] && [ "$OUT" -nt "$HERE/bam_reader.hpp" ] && [ "$OUT" -nt "$HERE/reform.inc" ] && [ "$OUT" -nt "$PKG/../include/pgm_gmove.h" ] && [ "$OUT" -nt "$PKG/libpgm_gmove.so" ]; then
+SRC_HASH="$(cat "$HERE/gmove_cli.cpp" "$HERE/bam_reader.hpp" "$HERE/reform.inc" "$PKG/../include/pgm_gmove.h" | sha256sum | cut -c1-64)"
+CLILIB="$PKG/libporegen_gmove_cli.so"
+if [ -x "$OUT" ] && [ -f "$CLILIB" ] && [ "$("$OUT" --build-info 2>/dev/null || true)" = "$SRC_HASH" ] && [ "$OUT" -nt "$PKG/libpgm_gmove.so" ]; then
     exit 0
 fi
 CC=${CC:-gcc}; CXX=${CXX:-g++}
@@ -27,6 +34,10 @@ if [ ! -f "$DEPS/libslow5.a" ]; then
     done
     ar rcs "$DEPS/libslow5.a" "$DEPS"/obj/*.o
 fi
-$CXX -O2 -g -std=c++17 -Wall -I "$SLOW5LIB/include" "$HERE/gmove_cli.cpp" "$DEPS/libslow5.a" \
+$CXX -O2 -g -std=c++17 -Wall -DPGM_SRC_HASH="\"$SRC_HASH\"" -I "$SLOW5LIB/include" "$HERE/gmove_cli.cpp" "$DEPS/libslow5.a" \
     -L "$PKG" -lpgm_gmove -Wl,-rpath,'$ORIGIN/..' -lz -lpthread -o "$OUT"
-echo "build_cli: built $OUT"
+# the same code as a library exporting gmove(int, char**) / reform(int, char**) (include/pgm_gmove_cli.h): what the
+# reference's own main.o links against
+$CXX -O2 -g -std=c++17 -Wall -fPIC -shared -DPGM_NO_MAIN -DPGM_SRC_HASH="\"$SRC_HASH\"" -I "$SLOW5LIB/include" "$HERE/gmove_cli.cpp" "$DEPS/libslow5.a" \
+    -L "$PKG" -lpgm_gmove -Wl,-rpath,'$ORIGIN' -lz -lpthread -o "$CLILIB"
+echo "build_cli: built $OUT and $CLILIB"

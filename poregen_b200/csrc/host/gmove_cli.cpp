@@ -746,8 +746,28 @@ const struct option long_options[] = {
 
 }  // namespace
 
+// The library under this command line must be the one its structures were compiled against (include/pgm_gmove.h):
+// a stale binary next to a fresh libpgm_gmove.so would otherwise corrupt pgm_read / pgm_opts / pgm_result silently.
+static void check_abi() {
+    if (pgm_abi_version() != PGM_ABI_VERSION)
+        DIE("libpgm_gmove.so speaks ABI v%d, this command line was built for v%d: rebuild it (poregen_b200/csrc/host/build_cli.sh)", pgm_abi_version(), PGM_ABI_VERSION);
+}
+
+#ifndef PGM_SRC_HASH
+#define PGM_SRC_HASH "unknown"
+#endif
+// sha256 over the command line's sources at build time (build_cli.sh); tests compare it with the sources they see
+extern "C" const char *pgm_cli_build_info(void) { return PGM_SRC_HASH; }
+
+// poregen reform (reference src/main.c:47,80), same contract as gmove below.
+int reform(int argc, char *argv[]) {
+    check_abi();
+    return reform_impl(argc, argv);
+}
+
 // Same contract as the reference's gmove(argc, argv) (src/main.c:43,76): argv[0] is the word "gmove".
 int gmove(int argc, char *argv[]) {
+    check_abi();
     const double t_gmove0 = realtime();
     Run R;
     Opt &opt = R.opt;
@@ -1032,12 +1052,14 @@ int gmove(int argc, char *argv[]) {
 }
 
 extern "C" int pgm_gmove_main(int argc, char **argv) { return gmove(argc, argv); }
+extern "C" int pgm_reform_main(int argc, char **argv) { return reform(argc, argv); }
 
 #ifndef PGM_NO_MAIN
 // poregen's dispatcher (reference src/main.c:64-103), gmove only.
 int main(int argc, char *argv[]) {
     const double t0 = realtime();
     const bool is_gmove = argc >= 2 && strcmp(argv[1], "gmove") == 0, is_reform = argc >= 2 && strcmp(argv[1], "reform") == 0;
+    if (argc >= 2 && strcmp(argv[1], "--build-info") == 0) { printf("%s\n", pgm_cli_build_info()); return 0; }
     if (!is_gmove && !is_reform) {
         fprintf(stderr, "Usage: poregen <command> [options]\n\ncommand:\n         gmove     B200 build of `poregen gmove`\n"
                         "         reform    move table (SAM/BAM) -> per-k-mer TSV or PAF with ss:Z\n");

@@ -2,8 +2,8 @@
 // kernel sequencing. No CPU fallback: every compute entry point needs a live CUDA device.
 //
 // Pipeline of one batch (all on one stream, no host synchronisation until pgm_download):
-//   count: k_read_prep -> k_order -> [k_oor_check] -> k_decode -> k_scan_records -> k_place
-//   emit : k_quota -> k_scan_hist -> [k_sort_scatter, k_sort_hist, k_scan_hist per extra digit pass] -> k_rank
+//   count: k_read_prep -> k_order -> [k_oor_check] -> k_decode | k_decode_moves -> k_scan_records -> k_tile_hist
+//   emit : k_quota || k_scan_hist -> k_rank (tables of one digit) | k_msd_scatter -> k_msd_rank (two digits)
 //          -> k_scan_sel -> [k_stats_wide] -> [k_stats] -> k_gather -> [k_text_len -> k_scan_text -> k_text_write]
 // Element counts that only the device knows (passing / selected events) stay on the device: grids
 // are sized by capacities derived from the batch and the kernels read the counts themselves.
@@ -38,7 +38,7 @@ struct DBuf {
 
 
 typedef BatchScalars Scalars;  // device -> host summary of one batch (pgm_emit.cuh)
-#define MISC_WORDS 160          // word 0 = k_stats_wide queue, 1 = k_decode record ticket, 2 = k_stats ticket, 3 = k_read_prep CTAs done,
+#define MISC_WORDS 160          // word 0 = k_stats_wide queue, 1 = k_decode record ticket, 2 = k_stats ticket, 3 = k_read_prep CTAs done, 4 = k_msd_rank bucket ticket,
                                 // 8..63 = look-back scan tickets, 96..159 = record length classes (k_read_prep)
 
 enum State { ST_IDLE = 0, ST_LOADED, ST_COUNTED, ST_EMITTED };
@@ -89,14 +89,18 @@ struct pgm_ctx {
 
     // per-record
     DBuf cal, rflags, n_pass, ev_base;
-    // events / sort / selection
-    DBuf key, ev_start, ev_len, ev_read, key2, val, val2;
-    DBuf p_start, p_len, p_read;      // two-pass sorts: the event rows in first-pass order (SortPayload)
-    DBuf sc_start, sc_end, sc_key, sc_code, sc_indel;
+    // events / sort / selection (rows: pgm_sort.cuh)
+    DBuf rows_tmp;                    // per-record temporaries of the decoders
+    DBuf rows_a;                      // two-digit tables: the batch split by the high digit
+    DBuf sel;                         // selected events, grouped by slot
+    DBuf rec_src0;                    // [R] index in raw[] of every record's sample 0
+    DBuf sc_start, sc_end, sc_code, sc_indel;   // ss decoder scratch
+    uint32_t tmp_shift = 0;           // rows_tmp index = align_off >> tmp_shift
     DBuf zbatch;                       // zeroed every batch: scalars | misc words | scan status | read_has_sel[R] | tile histogram
     size_t has_sel_off = 0, hist_off = 0;   // byte offsets inside zbatch
     uint32_t sort_ntiles = 0;
-    DBuf sel_start, sel_len, sel_read, sel_src, sel_off, samples, rec_packed, rec_order;
+    DBuf sel_start, sel_len, sel_read;   // structure-of-arrays form of `sel`, made by pgm_download for the host (k_unpack_sel)
+    DBuf sel_off, samples, rec_packed, rec_order;
     DBuf ev_tlen, ev_toff, text, slot_toff;   // PGM_OUT_TEXT
     DBuf hp_prior, hp_consumed;               // pgm_set_prior_host
     bool need_wide = true;  // some record may have an in-range code span above SIG_SMEM_BINS
@@ -219,9 +223,8 @@ void pgm_destroy(pgm_ctx *c) {
     for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
     DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->bucket_base, &c->sel_base,
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
-                   &c->ev_base, &c->key, &c->ev_start, &c->ev_len, &c->ev_read,
-                   &c->key2, &c->val, &c->val2, &c->sc_start, &c->sc_end, &c->sc_code,
-                   &c->sc_indel, &c->sc_key, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->sel_src, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed, &c->svb_blob, &c->svb_off, &c->svb_words, &c->p_start, &c->p_len, &c->p_read};
+                   &c->ev_base, &c->rows_tmp, &c->rows_a, &c->sel, &c->rec_src0, &c->sc_start, &c->sc_end, &c->sc_code,
+                   &c->sc_indel, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed, &c->svb_blob, &c->svb_off, &c->svb_words};
     for (DBuf *b : dev) release(*b);
     DBuf *host[] = {&c->h_slot_sel, &c->h_slot_total, &c->h_ev_len, &c->h_ev_read, &c->h_ev_start, &c->h_samples, &c->h_rflags, &c->h_text, &c->h_slot_toff, &c->h_ev_toff, &c->h_svb_err};
     for (DBuf *b : host) release_host(*b);
@@ -253,7 +256,11 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         return fail(nullptr, PGM_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
     if (prop.major != 10) return fail(nullptr, PGM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
 
+    if (bit_length(opts->n_slots - 1) > 2 * MSD_MAX_LO_BITS)
+        return fail(nullptr, PGM_ERR_ARG, "n_slots %u needs more than two digits of %d bits", opts->n_slots, MSD_MAX_LO_BITS);
     if ((e = cudaFuncSetAttribute(k_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, RANK_SMEM)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_msd_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((RANK_WARPS + 1) * (1u << MSD_MAX_LO_BITS) * 4))) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_msd_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MSD_RANK_SMEM(MSD_MAX_LO_BITS))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_gather<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_gather<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess)
@@ -340,11 +347,16 @@ int pgm_sync(pgm_ctx *c) {
     return PGM_OK;
 }
 
-// radix pass layout for the slot keys: `passes` passes of `per` bits
-static void sort_plan(const pgm_ctx *c, uint32_t *passes, uint32_t *per) {
-    const uint32_t bits = bit_length(c->opts.n_slots - 1);
-    *passes = bits ? (bits + SORT_MAX_BITS - 1) / SORT_MAX_BITS : 1;
-    *per = bits ? (bits + *passes - 1) / *passes : 1;
+// digits of the slot: tables up to 2^SORT_MAX_BITS slots are ranked in one pass (hi_bits = 0), larger ones are split
+// by the high digit first (pgm_sort.cuh). `first` = bits of the digit the tile histogram counts.
+struct SortPlan { uint32_t bits, hi_bits, lo_bits, first_bits, first_shift; };
+static SortPlan sort_plan(const pgm_ctx *c) {
+    SortPlan p;
+    p.bits = bit_length(c->opts.n_slots - 1);
+    if (p.bits == 0) p.bits = 1;
+    if (p.bits <= SORT_MAX_BITS) { p.hi_bits = 0; p.lo_bits = p.bits; p.first_bits = p.bits; p.first_shift = 0; }
+    else { p.hi_bits = (p.bits + 1) / 2; p.lo_bits = p.bits - p.hi_bits; p.first_bits = p.hi_bits; p.first_shift = p.lo_bits; }
+    return p;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -370,25 +382,22 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     RET(ensure(c, c->rec_order, (size_t)R * 4 + 4));
     RET(ensure(c, c->ev_base, (size_t)(R + 1) * 4));
     const size_t e4 = (size_t)cap * 4;
-    DBuf *evb[] = {&c->key, &c->ev_start, &c->ev_len, &c->ev_read, &c->key2, &c->val, &c->val2, &c->sel_start, &c->sel_len, &c->sel_read};
-    for (DBuf *x : evb) RET(ensure(c, *x, e4));
-    {
-        uint32_t passes, per;
-        sort_plan(c, &passes, &per);
-        if (passes == 2) { RET(ensure(c, c->p_start, e4)); RET(ensure(c, c->p_len, e4)); RET(ensure(c, c->p_read, e4)); }
-    }
+    const SortPlan sp = sort_plan(c);
+    RET(ensure(c, c->rec_src0, (size_t)R * 8 + 8));
+    // rows_tmp: one 16-byte row per possible passing event of a record, at the record's alignment offset (ss: half of it)
+    c->tmp_shift = (b->mode == PGM_MODE_SS) ? 1u : 0u;
+    RET(ensure(c, c->rows_tmp, (((size_t)b->n_align >> c->tmp_shift) + R + 1) * 16));
+    RET(ensure(c, c->sel, (size_t)cap * 16 + 16));
+    if (sp.hi_bits) RET(ensure(c, c->rows_a, (size_t)cap * 16 + 16));
     RET(ensure(c, c->sel_off, (size_t)(cap + 1) * 8));
-    RET(ensure(c, c->sel_src, (size_t)(cap + 1) * 8));
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
     c->sort_ntiles = ntiles;
-    {   // per-batch zero region: scalars | misc words | look-back status words | read_has_sel[R] | tile histogram
-        uint32_t passes, per;
-        sort_plan(c, &passes, &per);
+    {   // per-batch zero region: scalars | misc words | look-back status words | read_has_sel[R]; then (not zeroed) the tile histogram
         c->lb_words = (size_t)R / LB_TILE + c->opts.n_slots / LB_TILE + 2 * ((size_t)cap / LB_TILE) + 12 +
-                      passes * (((size_t)ntiles << per) / LB_TILE + 2);
+                      (((size_t)ntiles << sp.first_bits) / LB_TILE + 2);
         c->has_sel_off = (ZB_STATUS_OFF + c->lb_words * 8 + 255) & ~(size_t)255;
         c->hist_off = (c->has_sel_off + (size_t)R + 255) & ~(size_t)255;
-        RET(ensure(c, c->zbatch, c->hist_off + (size_t)SORT_MAX_BINS * ntiles * 4));
+        RET(ensure(c, c->zbatch, c->hist_off + ((size_t)ntiles << sp.first_bits) * 4));
     }
     RET(ensure(c, c->samples, (size_t)c->samples_cap * 8));
     if (c->opts.output != PGM_OUT_F64) {
@@ -396,10 +405,9 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
         RET(ensure(c, c->ev_toff, (size_t)(cap + 1) * 8));
         RET(ensure(c, c->slot_toff, (size_t)(c->opts.n_slots + 1) * 8));
     }
-    RET(ensure(c, c->sc_start, (size_t)b->n_align * 4 + 4));
-    RET(ensure(c, c->sc_end, (size_t)b->n_align * 4 + 4));
-    RET(ensure(c, c->sc_key, (size_t)b->n_align * 4 + 4));
     if (b->mode == PGM_MODE_SS) {
+        RET(ensure(c, c->sc_start, (size_t)b->n_align * 4 + 4));
+        RET(ensure(c, c->sc_end, (size_t)b->n_align * 4 + 4));
         RET(ensure(c, c->sc_code, (size_t)b->n_align + 4));
         RET(ensure(c, c->sc_indel, (size_t)b->n_align * 4 + 4));
     }
@@ -499,19 +507,25 @@ static LbBuf next_lb(pgm_ctx *c, size_t tiles) {
     return st;
 }
 
+static EvSource ev_source(pgm_ctx *c) {
+    EvSource s;
+    s.rows_tmp = P<uint4>(c->rows_tmp); s.ev_base = P<uint32_t>(c->ev_base); s.reads = c->db.reads;
+    s.n_reads = c->db.n_reads; s.shift = c->tmp_shift;
+    return s;
+}
+
 int pgm_count(pgm_ctx *c) {
     if (!c) return PGM_ERR_ARG;
     if (c->state != ST_LOADED) return fail(c, PGM_ERR_STATE, "pgm_count needs pgm_upload/pgm_attach_device first");
     CU(c, cudaSetDevice(c->device));
     const uint32_t R = c->db.n_reads;
     cudaStream_t st = c->stream;
-    uint32_t passes, per;
-    sort_plan(c, &passes, &per);
+    const SortPlan sp = sort_plan(c);
     {
         StageTimer t(c, PGM_STAGE_MISC);
         CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
-        // scalars, tickets, scan status, read_has_sel[R] and the tiles of the first radix pass's histogram
-        CU(c, cudaMemsetAsync(c->zbatch.p, 0, c->hist_off + ((size_t)c->sort_ntiles << per) * 4, st));
+        // scalars, tickets, scan status, read_has_sel[R] (the tile histogram behind them is written whole by k_tile_hist)
+        CU(c, cudaMemsetAsync(c->zbatch.p, 0, c->hist_off, st));
         c->lb_ticket = 0;
         c->lb_used = 0;
         if (!R) CU(c, cudaMemsetAsync(P<uint32_t>(c->ev_base), 0, 4, st));
@@ -524,7 +538,8 @@ int pgm_count(pgm_ctx *c) {
             StageTimer t(c, PGM_STAGE_PREP);
             PrepOrder po;
             po.cls_count = MISC(c) + 96; po.packed = P<uint32_t>(c->rec_packed); po.order = P<uint32_t>(c->rec_order);
-            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &SCALARS(c)->err_flag, po);
+            k_read_prep<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(d, c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags), &SCALARS(c)->err_flag, po,
+                                                                  P<unsigned long long>(c->rec_src0));
             k_order<<<cdiv(R, PGM_BLOCK), PGM_BLOCK, 0, st>>>(R, po);
             c->launches += 2;
             if (c->db.mode == PGM_MODE_MOVES_I8) { k_oor_check<<<R, PGM_BLOCK, 0, st>>>(c->db, P<ReadCal>(c->cal), P<uint8_t>(c->rflags)); c->launches++; }
@@ -537,14 +552,13 @@ int pgm_count(pgm_ctx *c) {
             io.counts = P<uint32_t>(c->counts);
             io.ev_base = P<uint32_t>(c->ev_base);
             io.ev_cap = c->ev_cap;
-            io.key = P<uint32_t>(c->key); io.ev_start = P<uint32_t>(c->ev_start); io.ev_len = P<uint32_t>(c->ev_len); io.ev_read = P<uint32_t>(c->ev_read);
             io.rflags = P<uint8_t>(c->rflags);
             io.examined = &SCALARS(c)->examined;
-            io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end); io.sc_key = P<uint32_t>(c->sc_key);
+            io.rows_tmp = P<uint4>(c->rows_tmp); io.tmp_shift = c->tmp_shift;
+            io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end);
             io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
             io.n_pass = P<uint32_t>(c->n_pass);
             io.ticket = MISC(c) + 1; io.order = P<uint32_t>(c->rec_order);
-            io.hist = HIST(c); io.ntiles_cap = c->sort_ntiles; io.hist_mask = (1u << per) - 1;
             if (c->db.mode == PGM_MODE_SS) {
                 const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
                 k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
@@ -556,8 +570,12 @@ int pgm_count(pgm_ctx *c) {
             t.stop();
             StageTimer t2(c, PGM_STAGE_PLACE);
             k_scan_records<<<cdiv(R, LB_TILE), PGM_BLOCK, 0, st>>>(io.n_pass, io.ev_base, R, next_lb(c, cdiv(R, LB_TILE)));
-            k_place<<<cdiv(R, DEC_WARPS), PGM_BLOCK, 0, st>>>(c->db, io);
-            c->launches += 2;
+            c->launches++;
+            if (c->ev_cap) {   // tile histogram of the first digit, over the dense (record, position) order
+                const uint32_t grid = std::min<uint32_t>(c->sort_ntiles, (uint32_t)c->n_sm * 8);
+                k_tile_hist<<<grid, PGM_BLOCK, 0, st>>>(ev_source(c), P<uint32_t>(c->ev_base) + R, sp.first_shift, sp.first_bits, HIST(c), c->sort_ntiles);
+                c->launches++;
+            }
         }
         CU(c, cudaGetLastError());
     }
@@ -637,7 +655,7 @@ int pgm_set_prior(pgm_ctx *c, const uint32_t *prior_dev, const uint32_t *consume
 
 static TextIO make_text_io(pgm_ctx *c) {
     TextIO t;
-    t.samples = P<double>(c->samples); t.sel_len = P<uint32_t>(c->sel_len); t.sel_off = P<unsigned long long>(c->sel_off);
+    t.samples = P<double>(c->samples); t.sel = P<uint4>(c->sel); t.sel_off = P<unsigned long long>(c->sel_off);
     t.n_sel = P<uint32_t>(c->sel_base) + c->opts.n_slots;
     t.ev_tlen = P<uint32_t>(c->ev_tlen); t.ev_toff = P<unsigned long long>(c->ev_toff);
     t.text = P<char>(c->text); t.text_cap = c->text.cap;
@@ -653,18 +671,17 @@ int pgm_emit(pgm_ctx *c) {
     DevOpts d = c->dopts;
     d.mode = c->db.mode;
     const uint32_t *n_ev = P<uint32_t>(c->ev_base) + R;  // device scalar: passing events
-    const uint32_t pgrid = (uint32_t)c->n_sm * 4;
-    // The scan of the first digit pass's tile histogram (filled by k_place) does not depend on the quota: it runs on
-    // the auxiliary stream while k_quota runs here; both are a few microseconds of latency, not of bandwidth.
+    // The scan of the tile histogram (k_tile_hist) does not depend on the quota: it runs on the auxiliary stream while
+    // k_quota runs here; both are a few microseconds of latency, not of bandwidth.
     const bool sorting = R && c->ev_cap;
-    uint32_t passes = 0, per = 0;
+    const SortPlan sp = sort_plan(c);
+    const uint32_t first_bins = 1u << sp.first_bits;
     if (sorting) {
-        sort_plan(c, &passes, &per);
         CU(c, cudaEventRecord(c->ev_fork, st));
         CU(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
         StageTimer t(c, PGM_STAGE_SORT, c->aux);
-        k_scan_hist<<<cdiv((uint64_t)(1u << per) * c->sort_ntiles, LB_TILE), PGM_BLOCK, 0, c->aux>>>(HIST(c), n_ev, 1u << per, c->sort_ntiles,
-                                                                                                  next_lb(c, cdiv((uint64_t)(1u << per) * c->sort_ntiles, LB_TILE)));
+        k_scan_hist<<<cdiv((uint64_t)first_bins * c->sort_ntiles, LB_TILE), PGM_BLOCK, 0, c->aux>>>(HIST(c), n_ev, first_bins, c->sort_ntiles,
+                                                                                               next_lb(c, cdiv((uint64_t)first_bins * c->sort_ntiles, LB_TILE)));
         c->launches++;
         t.stop();
         CU(c, cudaEventRecord(c->ev_join, c->aux));
@@ -683,47 +700,32 @@ int pgm_emit(pgm_ctx *c) {
         c->launches++;
     }
     if (sorting) {
-        // stable LSD radix sort of (slot, event index); the last pass is fused with the selection (k_rank)
+        // stable bucketing by slot fused with the selection (pgm_sort.cuh)
         CU(c, cudaStreamWaitEvent(st, c->ev_join, 0));
         StageTimer tsort(c, PGM_STAGE_SORT);
         const uint32_t ntiles = c->sort_ntiles;
-        const uint32_t sgrid = ntiles < pgrid ? ntiles : pgrid;
-        const bool carry = passes == 2;
-        uint32_t *kin = P<uint32_t>(c->key), *kout = P<uint32_t>(c->key2);
-        uint32_t *vin = nullptr, *vout = P<uint32_t>(c->val);
-        for (uint32_t p = 0; p < passes; p++) {
-            const uint32_t shift = p * per;
-            if (p) {   // pass 0: counted by k_place and scanned on the auxiliary stream above
-                k_sort_hist<<<sgrid, PGM_BLOCK, 0, st>>>(kin, n_ev, shift, per, HIST(c), ntiles);
-                k_scan_hist<<<cdiv((uint64_t)(1u << per) * ntiles, LB_TILE), PGM_BLOCK, 0, st>>>(HIST(c), n_ev, 1u << per, ntiles,
-                                                                                               next_lb(c, cdiv((uint64_t)(1u << per) * ntiles, LB_TILE)));
-                c->launches += 2;
-            }
-            if (p + 1 < passes) {
-                SortPayload pl;
-                memset(&pl, 0, sizeof pl);
-                if (carry) {   // two passes: the rows travel with the keys, the index does not
-                    pl.s_in = P<uint32_t>(c->ev_start); pl.l_in = P<uint32_t>(c->ev_len); pl.r_in = P<uint32_t>(c->ev_read);
-                    pl.s_out = P<uint32_t>(c->p_start); pl.l_out = P<uint32_t>(c->p_len); pl.r_out = P<uint32_t>(c->p_read);
-                }
-                k_sort_scatter<<<sgrid, PGM_BLOCK, 0, st>>>(kin, vin, kout, carry ? nullptr : vout, n_ev, shift, per, HIST(c), ntiles, pl);
-                c->launches++;
-                // ping-pong: keys key<->key2, values val<->val2
-                uint32_t *t = kin; kin = kout; kout = t;
-                vin = vout; vout = (vout == P<uint32_t>(c->val)) ? P<uint32_t>(c->val2) : P<uint32_t>(c->val);
-            } else {
-                RankIO r;
-                r.n_events = n_ev; r.keys_in = kin; r.vals_in = carry ? nullptr : vin; r.hist_scanned = HIST(c);
-                r.p_start = carry ? P<uint32_t>(c->p_start) : nullptr; r.p_len = carry ? P<uint32_t>(c->p_len) : nullptr;
-                r.p_read = carry ? P<uint32_t>(c->p_read) : nullptr;
-                r.ntiles_cap = ntiles; r.shift = shift; r.bits = per;
-                r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
-                r.ev_start = P<uint32_t>(c->ev_start); r.ev_len = P<uint32_t>(c->ev_len); r.ev_read = P<uint32_t>(c->ev_read);
-                r.sel_start = P<uint32_t>(c->sel_start); r.sel_len = P<uint32_t>(c->sel_len); r.sel_read = P<uint32_t>(c->sel_read);
-                r.sel_src = P<unsigned long long>(c->sel_src); r.reads = c->db.reads; r.read_has_sel = HAS_SEL(c);
-                k_rank<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, RANK_SMEM, st>>>(r);
-                c->launches++;
-            }
+        uint8_t *has_sel = c->opts.scaling ? HAS_SEL(c) : nullptr;
+        if (!sp.hi_bits) {
+            RankIO r;
+            r.n_events = n_ev; r.src = ev_source(c); r.hist_scanned = HIST(c); r.ntiles_cap = ntiles; r.bits = sp.bits;
+            r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
+            r.sel = P<uint4>(c->sel); r.rec_src0 = P<unsigned long long>(c->rec_src0); r.read_has_sel = has_sel;
+            k_rank<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, (RANK_WARPS + 1) * (1u << sp.bits) * 4, st>>>(r);
+            c->launches++;
+        } else {
+            MsdScatterIO ms;
+            ms.n_events = n_ev; ms.src = ev_source(c); ms.hist_scanned = HIST(c); ms.ntiles_cap = ntiles;
+            ms.shift = sp.lo_bits; ms.bits = sp.hi_bits; ms.rows_out = P<uint4>(c->rows_a);
+            k_msd_scatter<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, (RANK_WARPS + 1) * (1u << sp.hi_bits) * 4, st>>>(ms);
+            MsdRankIO mr;
+            mr.n_events = n_ev; mr.rows_in = P<uint4>(c->rows_a); mr.hist_scanned = HIST(c); mr.ntiles_cap = ntiles;
+            mr.hi_bits = sp.hi_bits; mr.lo_bits = sp.lo_bits; mr.n_slots = NS;
+            mr.keep = P<uint32_t>(c->keep); mr.sel_base = P<uint32_t>(c->sel_base);
+            mr.sel = P<uint4>(c->sel); mr.rec_src0 = P<unsigned long long>(c->rec_src0); mr.read_has_sel = has_sel;
+            mr.ticket = MISC(c) + 4;
+            const uint32_t n_buckets = cdiv(NS, 1u << sp.lo_bits);
+            k_msd_rank<<<std::min<uint32_t>(n_buckets, (uint32_t)c->n_sm * 2), RANK_BLOCK, MSD_RANK_SMEM(sp.lo_bits), st>>>(mr);
+            c->launches += 2;
         }
         CU(c, cudaGetLastError());
     }
@@ -737,7 +739,7 @@ int pgm_emit(pgm_ctx *c) {
             CU(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
         }
         StageTimer t(c, PGM_STAGE_SCAN, ss);
-        k_scan_sel<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, ss>>>(P<uint32_t>(c->sel_len), P<unsigned long long>(c->sel_off),
+        k_scan_sel<<<cdiv((uint64_t)c->ev_cap + 1, LB_TILE), PGM_BLOCK, 0, ss>>>(P<uint4>(c->sel), P<unsigned long long>(c->sel_off),
                                                                                P<uint32_t>(c->sel_base) + NS, n_ev, SCALARS(c),
                                                                                next_lb(c, cdiv((uint64_t)c->ev_cap + 1, LB_TILE)));
         c->launches++;
@@ -761,7 +763,7 @@ int pgm_emit(pgm_ctx *c) {
         if (beside) CU(c, cudaStreamWaitEvent(st, c->ev_join, 0));
         StageTimer t(c, PGM_STAGE_GATHER);
         GatherIO g;
-        g.sel_src = P<unsigned long long>(c->sel_src); g.sel_len = P<uint32_t>(c->sel_len); g.sel_read = P<uint32_t>(c->sel_read);
+        g.sel = P<uint4>(c->sel);
         g.sel_off = P<uint64_t>(c->sel_off); g.n_sel = P<uint32_t>(c->sel_base) + NS; g.cal = P<ReadCal>(c->cal);
         g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
         if (!c->gather_ctas) {   // resident CTAs per SM of the instantiation in use (registers and shared memory decide)
@@ -815,7 +817,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     if (R) CU(c, cudaMemcpyAsync(c->h_rflags.p, c->rflags.p, R, cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     const Scalars s = *c->h_scalars;
-    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays");
+    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays (or ss records with a trim offset)");
     if (c->svb_used && *P<uint32_t>(c->h_svb_err))
         return fail(c, PGM_ERR_INPUT, "svb-zd stream of a record does not decode to its raw_len samples");
     if (s.n_pass > c->ev_cap || s.n_sel_samples > c->samples_cap)
@@ -828,6 +830,13 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     const bool as_text = c->opts.output != PGM_OUT_F64;
     const bool with_events = c->opts.output != PGM_OUT_TEXT_ONLY;   // per-event arrays travel to the host
     if (!as_text) RET(ensure_host(c, c->h_samples, nsamp * 8 + 8));
+    if (ne && (with_events || c->model_on)) {   // the rows as the three arrays of pgm_result
+        RET(ensure(c, c->sel_start, ne * 4)); RET(ensure(c, c->sel_len, ne * 4)); RET(ensure(c, c->sel_read, ne * 4));
+        k_unpack_sel<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(P<uint4>(c->sel), P<uint32_t>(c->sel_base) + NS, P<unsigned long long>(c->rec_src0),
+                                                       P<uint32_t>(c->sel_start), P<uint32_t>(c->sel_len), P<uint32_t>(c->sel_read));
+        c->launches++;
+        CU(c, cudaGetLastError());
+    }
     if (ne && with_events) {
         CU(c, cudaMemcpyAsync(c->h_ev_len.p, c->sel_len.p, ne * 4, cudaMemcpyDeviceToHost, st));
         CU(c, cudaMemcpyAsync(c->h_ev_read.p, c->sel_read.p, ne * 4, cudaMemcpyDeviceToHost, st));
@@ -896,7 +905,7 @@ int pgm_summary(pgm_ctx *c, pgm_result *out) {
     out->n_slots = c->opts.n_slots; out->n_reads = c->db.n_reads;
     out->n_events_examined = s.examined; out->n_events_pass = s.n_pass;
     out->n_sel_events = s.n_sel; out->n_sel_samples = s.n_sel_samples;
-    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays");
+    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays (or ss records with a trim offset)");
     return PGM_OK;
 }
 

@@ -9,9 +9,8 @@
 //   2. evaluate: the shared back end (pgm_eval_event) applies the reference's filters in the reference's
 //      order; passing events are counted per slot and written compactly, in position order, to a
 //      per-record temporary;
-//   3. place (k_scan_records, k_place): a scan over the per-record totals gives the record's offset
-//      in the batch-wide (record, position) order; the events are copied there and, on the way,
-//      counted into the first radix pass's tile histogram.
+//   3. k_scan_records: a scan over the per-record totals gives the record's offset in the batch-wide
+//      (record, position) order; the sort kernels (pgm_sort.cuh) read the rows from the temporaries in that order.
 #pragma once
 #include "pgm_device.cuh"
 #include "pgm_scan.cuh"
@@ -28,19 +27,18 @@ struct DecodeIO {
     uint32_t *n_pass;          // [R] passing events per record
     uint32_t *ev_base;         // [R+1] exclusive prefix of n_pass
     uint32_t ev_cap;           // capacity of the event arrays
-    uint32_t *key, *ev_start, *ev_len, *ev_read;  // [E] passing events, record-then-position order
     uint8_t *rflags;           // [R] PGM_RF_*
     unsigned long long *examined;
-    // scratch, indexed by the record's alignment offset (+ event / indel index)
-    uint32_t *sc_start, *sc_end;   // ss: event bounds, then (in place) start / length of the passing events
-    uint32_t *sc_key;              // slot of the passing events (temporary, compact per record)
-    uint8_t *sc_code;              // ss: 2-bit base code per event
-    int32_t *sc_indel;             // ss: indel positions
+    // per-record temporaries: record r's passing events, in position order, as rows {slot, start, len, r} at
+    // rows_tmp[(align_off >> tmp_shift) + j] (EvSource, pgm_sort.cuh)
+    uint4 *rows_tmp;
+    uint32_t tmp_shift;
+    // ss scratch, indexed by the record's alignment offset (+ event / indel index)
+    uint32_t *sc_start, *sc_end;   // event bounds
+    uint8_t *sc_code;              // 2-bit base code per event
+    int32_t *sc_indel;             // indel positions
     uint32_t *ticket;          // record hand-out
     const uint32_t *order;     // [R] ticket -> record, longest records first (k_read_prep)
-    // tile histogram of the first radix pass: hist[digit * ntiles_cap + tile]
-    uint32_t *hist;
-    uint32_t ntiles_cap, hist_mask;
 };
 
 // Reference gmove.cpp:641-662 (and 916-937, 1204-1225): duration filters, k-mer lookup, quota
@@ -97,126 +95,11 @@ __device__ __forceinline__ Lane16 load_lane16(const uint8_t *abase, uint32_t off
     return x;
 }
 
-// Copies the record's passing events from the per-record temporary to their place in the batch-wide
-// order and counts them into the first radix pass's tile histogram.
-__device__ __forceinline__ void place_events(const DecodeIO &io, uint32_t r, uint32_t base, uint32_t n_pass, const uint32_t *t_key,
-                                             const uint32_t *t_start, const uint32_t *t_len) {
-    const uint32_t lane = threadIdx.x & 31;
-    if (base >= io.ev_cap) return;
-    n_pass = min(n_pass, io.ev_cap - base);
-    // a warp makes ~10 trips of 32 events for a record: the loads of four trips are issued before the first store (the
-    // compiler may not move them across the stores itself: the arrays could alias)
-    for (uint32_t p0 = 0; p0 < n_pass; p0 += 128) {
-        uint32_t sl[4], st[4], ln[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const uint32_t p = p0 + 32 * u + lane;
-            sl[u] = st[u] = ln[u] = 0;
-            if (p < n_pass) { sl[u] = t_key[p]; st[u] = t_start[p]; ln[u] = t_len[p]; }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const uint32_t p = p0 + 32 * u + lane;
-            if (p < n_pass) {
-                const uint32_t P = base + p;
-                io.key[P] = sl[u]; io.ev_start[P] = st[u]; io.ev_len[P] = ln[u]; io.ev_read[P] = r;
-                atomicAdd(io.hist + (size_t)(sl[u] & io.hist_mask) * io.ntiles_cap + P / SORT_TILE, 1u);
-            }
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------
 // Move tables (TSV '0'/'1' bytes, or mv:B:c int8): reference gmove.cpp:620-690 and 1182-1252.
 // Event e (0-based over ALL set moves) lies between the e-th and (e+1)-th set move; it is examined
 // when e >= m and labelled with the k-mer at base s_off + (e - m). The run after the last set move
-// is never an event (the loop bound reads the terminator, gmove.cpp:632).
-// Returns the number of passing events (written to the per-record temporary); *exam += events examined.
-__device__ __forceinline__ uint32_t decode_moves_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd,
-                                                        uint32_t *exam, bool *bad) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint8_t *mv = b.align + rd.align_off;
-    const uint8_t *seq = b.bases + rd.seq_off;
-    const uint32_t M = rd.align_len;
-    const uint32_t one4 = (b.mode == PGM_MODE_MOVES_CHAR) ? 0x31313131u : 0x01010101u;
-    const uint64_t n_sig = (uint64_t)rd.raw_len - rd.trim;
-    const uint32_t head = (uint32_t)((uintptr_t)mv & 15);
-    const uint8_t *abase = mv - head;
-    const uint32_t span = head + M;
-    uint32_t *t_key = io.sc_key + rd.align_off, *t_start = io.sc_start + rd.align_off, *t_len = io.sc_end + rd.align_off;
-    uint32_t ones_carry = 0, pbase = 0, my_exam = 0;
-    int last_carry = -1;
-    for (uint32_t cb = 0; cb < span; cb += 512) {
-        const uint32_t off = cb + 16 * lane;
-        const Lane16 x = load_lane16(abase, off, span);
-        const int p0 = (int)off - (int)head;     // string position of the lane's byte 0
-        const uint32_t lo = (off < head) ? min(16u, head - off) : 0u;
-        const uint32_t hi = (off >= span) ? 0u : min(16u, span - off);
-        uint32_t bits = 0;                       // bit i <=> byte i of the lane is a set move
-#pragma unroll
-        for (int wi = 0; wi < 4; wi++) bits |= byte_nibble(byte_is_zero(x.w[wi] ^ one4)) << (4 * wi);
-        bits &= (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
-        const uint32_t cnt = __popc(bits);
-        const int lastpos = bits ? p0 + 31 - __clz(bits) : -1;
-        uint32_t tot_cnt;
-        int tot_last;
-        const uint32_t ex_cnt = ones_carry + warp_excl_scan_add(cnt, &tot_cnt);
-        const int ex_last = max(last_carry, warp_excl_scan_max(lastpos, &tot_last));
-        // the set move at position p with `rank` set moves before it closes event rank-1 (needs rank-1 >= m)
-        auto eval_at = [&](uint32_t rank, int prev, int p, uint32_t *slot, uint32_t *s2, uint32_t *len) {
-            const uint64_t ei = (uint64_t)rank - o.m - 1;
-            const uint64_t seqpos = (uint64_t)o.s_off + ei;
-            const uint32_t start = (uint32_t)((uint64_t)(uint32_t)prev * rd.stride);
-            const uint32_t end = (uint32_t)((uint64_t)(uint32_t)p * rd.stride);
-            bool id_ok = seqpos + o.k <= rd.seq_len;                                   // U4
-            uint32_t id = 0;
-            if (id_ok) {
-                for (uint32_t t = 0; t < o.k; t++) {
-                    const uint32_t c = pgm_base_code(__ldg(seq + seqpos + t), o.fourth, false);
-                    id_ok &= (c != 0xFF);
-                    id = (id << 2) | (c & 3);
-                }
-            }
-            return pgm_eval_event(o, io.consumed, start, end, id, id_ok, n_sig, slot, s2, len);
-        };
-        uint32_t okmask = 0;
-        {
-            uint32_t rank = ex_cnt, w = bits;
-            int prev = ex_last;
-            while (w) {
-                const int i = __ffs(w) - 1;
-                w &= w - 1;
-                if (rank > o.m) {
-                    uint32_t slot, s2, len;
-                    my_exam++;
-                    if (eval_at(rank, prev, p0 + i, &slot, &s2, &len)) {
-                        okmask |= 1u << i;
-                        atomicAdd(io.counts + slot, 1u);
-                    }
-                }
-                prev = p0 + i;
-                rank++;
-            }
-        }
-        uint32_t tot_pass;
-        uint32_t wr = pbase + warp_excl_scan_add(__popc(okmask), &tot_pass);
-        for (uint32_t w = okmask; w; w &= w - 1) {
-            const int i = __ffs(w) - 1;
-            const uint32_t below = bits & ((1u << i) - 1);
-            const int prev = below ? p0 + 31 - __clz(below) : ex_last;
-            uint32_t slot = 0, s2 = 0, len = 0;
-            eval_at(ex_cnt + __popc(below), prev, p0 + i, &slot, &s2, &len);
-            t_key[wr] = slot; t_start[wr] = s2; t_len[wr] = len;
-            wr++;
-        }
-        pbase += tot_pass;
-        ones_carry += tot_cnt;
-        last_carry = max(last_carry, tot_last);
-    }
-    *exam += my_exam;
-    *bad = ones_carry <= o.m;                                                          // U1
-    return pbase;
-}
+// is never an event (the loop bound reads the terminator, gmove.cpp:632). Decoder: k_decode_moves below.
 
 // ------------------------------------------------------------------------------------------------
 // ss:Z strings: reference gmove.cpp:831-955. Grammar (<uint>(','|'I'|'D'))*.
@@ -254,7 +137,7 @@ __device__ __forceinline__ bool ss_pick(const int32_t *pos, uint32_t n, int last
     return false;
 }
 
-__device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd,
+__device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const DevBatch &b, const DecodeIO &io, const pgm_read &rd, uint32_t r,
                                                      uint8_t *wsm, uint32_t *exam, bool *bad_out) {
     const uint32_t lane = threadIdx.x & 31;
     const uint8_t *ss = b.align + rd.align_off;
@@ -262,7 +145,8 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
     const uint32_t T = rd.align_len;
     const bool rna = (rd.flags & PGM_READ_RNA) != 0;
     const uint64_t n_sig = rd.raw_len;                  // the ss path never trims (gmove.cpp:750-753)
-    uint32_t *sc_start = io.sc_start + rd.align_off, *sc_end = io.sc_end + rd.align_off, *t_key = io.sc_key + rd.align_off;
+    uint32_t *sc_start = io.sc_start + rd.align_off, *sc_end = io.sc_end + rd.align_off;
+    uint4 *t_rows = io.rows_tmp + (rd.align_off >> io.tmp_shift);   // at most align_len / 2 events: every ',' token has a digit in front
     uint8_t *sc_code = io.sc_code + rd.align_off;
     int32_t *sc_indel = io.sc_indel + rd.align_off;
     const uint32_t head = (uint32_t)((uintptr_t)ss & 15);
@@ -423,10 +307,10 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
                 }
             }
             const uint32_t bm = __ballot_sync(0xffffffffu, ok);
-            if (ok) {   // positions <= i: behind every event still to be staged
+            if (ok) {
                 const uint32_t p = pbase + __popc(bm & ((1u << lane) - 1));
                 atomicAdd(io.counts + slot, 1u);
-                t_key[p] = slot; sc_start[p] = s2; sc_end[p] = len;
+                t_rows[p] = make_uint4(slot, s2, len, r);
             }
             pbase += __popc(bm);
         }
@@ -438,7 +322,7 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 
 // ------------------------------------------------------------------------------------------------
 // k_decode_moves: the move-table decoder (PGM_MODE_MOVES_CHAR / _I8), one CTA per record at a time.
-// Same semantics as decode_moves_record above (reference gmove.cpp:620-690, 1182-1252); the work is laid out
+// Reference gmove.cpp:620-690, 1182-1252; the work is laid out
 // for long records (C3: 8,700 moves, 4,200 events per record):
 //   * a step is DM_CHUNK move bytes, eight per thread (one aligned 8-byte load); a block scan numbers the set
 //     moves, a second one carries the position of the last set move in front of a thread's bytes;
@@ -486,7 +370,7 @@ __global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBa
         const uint32_t head = (uint32_t)((uintptr_t)mv & 7);
         const uint8_t *abase = mv - head;
         const uint32_t span = head + M;
-        uint32_t *t_key = io.sc_key + rd.align_off, *t_start = io.sc_start + rd.align_off, *t_len = io.sc_end + rd.align_off;
+        uint4 *t_rows = io.rows_tmp + (rd.align_off >> io.tmp_shift);
         uint32_t ones_carry = 0, pbase = 0;
         int last_carry = -1;
         for (uint32_t cb = 0; cb < span; cb += DM_CHUNK) {
@@ -591,7 +475,7 @@ __global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBa
             uint32_t wr = pbase + wbase_p + inc_p - np;
 #pragma unroll
             for (int i = 0; i < DM_PER; i++)
-                if ((okmask >> i) & 1u) { t_key[wr] = ev_slot[i]; t_start[wr] = ev_s2[i]; t_len[wr] = ev_len[i]; wr++; }
+                if ((okmask >> i) & 1u) t_rows[wr++] = make_uint4(ev_slot[i], ev_s2[i], ev_len[i], r);
             pbase += tot_p;
             ones_carry += tot_cnt;
             last_carry = max(last_carry, tot_last);
@@ -617,6 +501,7 @@ __global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBa
 #ifndef DEC_MIN_CTAS
 #define DEC_MIN_CTAS 4
 #endif
+// k_decode: the ss:Z decoder, one warp per record.
 __global__ void __launch_bounds__(PGM_BLOCK, DEC_MIN_CTAS) k_decode(DevOpts o, DevBatch b, DecodeIO gio) {
     __shared__ __align__(16) uint8_t sm_w[DEC_WARPS][DEC_WSM];   // per-warp staging (tokeniser, then evaluation tiles)
     // Small k-mer tables (k <= 5 at full range): the quota state every event looks up and the per-slot counts every passing
@@ -643,8 +528,7 @@ __global__ void __launch_bounds__(PGM_BLOCK, DEC_MIN_CTAS) k_decode(DevOpts o, D
         bool bad = false;
         if (io.rflags[r] == 0) {
             const pgm_read rd = b.reads[r];
-            if (b.mode == PGM_MODE_SS) n_pass = decode_ss_record(o, b, io, rd, sm_w[wid], &exam, &bad);
-            else n_pass = decode_moves_record(o, b, io, rd, &exam, &bad);
+            n_pass = decode_ss_record(o, b, io, rd, r, sm_w[wid], &exam, &bad);
             if (bad) {
                 n_pass = 0;
                 if (lane == 0) io.rflags[r] |= (PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED);
@@ -669,12 +553,3 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_scan_records(const uint32_t *n_pa
                       [&](uint32_t tot) { ev_base[R] = tot; });
 }
 
-// one warp per record: temporary -> batch-wide order (+ first-pass tile histogram)
-__global__ void __launch_bounds__(PGM_BLOCK) k_place(DevBatch b, DecodeIO io) {
-    const uint32_t r = blockIdx.x * DEC_WARPS + (threadIdx.x >> 5);
-    if (r >= b.n_reads) return;
-    const uint32_t base = io.ev_base[r], n_pass = io.ev_base[r + 1] - base;
-    if (!n_pass) return;
-    const uint64_t ao = b.reads[r].align_off;
-    place_events(io, r, base, n_pass, io.sc_key + ao, io.sc_start + ao, io.sc_end + ao);
-}

@@ -19,7 +19,8 @@ struct PrepOrder {
     uint32_t *order;       // [R] out
 };
 
-__global__ void __launch_bounds__(PGM_BLOCK) k_read_prep(DevOpts o, DevBatch b, ReadCal *cal, uint8_t *rflags, uint32_t *err_flag, PrepOrder po) {
+__global__ void __launch_bounds__(PGM_BLOCK) k_read_prep(DevOpts o, DevBatch b, ReadCal *cal, uint8_t *rflags, uint32_t *err_flag, PrepOrder po,
+                                                         unsigned long long *rec_src0) {
     const uint32_t r = blockIdx.x * PGM_BLOCK + threadIdx.x;
     if (r < b.n_reads) {
         const pgm_read rd = b.reads[r];
@@ -28,6 +29,11 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_read_prep(DevOpts o, DevBatch b, 
             atomicOr(err_flag, 1u);
             f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
         }
+        if (b.mode == PGM_MODE_SS && rd.trim != 0) {    // the ss path has no trim (gmove.cpp:750-753): a caller that sets one is mistaken
+            atomicOr(err_flag, 1u);
+            f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
+        }
+        rec_src0[r] = rd.raw_off + rd.trim;
         if (rd.flags & PGM_READ_SKIP) f |= PGM_RF_SKIPPED;
         const double scale = __ddiv_rn(rd.range, rd.digitisation);
         if (!isfinite(scale) || !isfinite(rd.offset)) f |= PGM_RF_BAD_CALIB | PGM_RF_SKIPPED;
@@ -149,11 +155,11 @@ struct BatchScalars {  // device -> host summary of one batch
     unsigned long long n_text;   // PGM_OUT_TEXT: characters of the dump text
 };
 
-__global__ void __launch_bounds__(PGM_BLOCK) k_scan_sel(const uint32_t *sel_len, unsigned long long *sel_off, const uint32_t *n_sel_ptr,
+__global__ void __launch_bounds__(PGM_BLOCK) k_scan_sel(const uint4 *sel, unsigned long long *sel_off, const uint32_t *n_sel_ptr,
                                                         const uint32_t *n_pass_ptr, BatchScalars *sc, LbBuf st) {
     const uint32_t n = *n_sel_ptr;
     lb_scan<unsigned long long>(
-        n, st, [&](uint64_t i) { return (unsigned long long)sel_len[i]; },
+        n, st, [&](uint64_t i) { return (unsigned long long)sel[i].z; },
         [&](uint64_t i, unsigned long long ex, unsigned long long) { sel_off[i] = ex; },
         [&](unsigned long long tot) {
             sel_off[n] = tot;

@@ -407,8 +407,7 @@ __global__ void __launch_bounds__(STATS_WARPS * 32) k_stats(DevOpts o, DevBatch 
 // one event's samples: raw -> pA (0.0 when out of range) -> (x - med) / mad (gmove.cpp:611-613).
 // Output offsets of consecutive events are consecutive, so the stores of a warp form one contiguous stream.
 struct GatherIO {
-    const unsigned long long *sel_src;      // [E_sel] index in raw[] of the event's first sample
-    const uint32_t *sel_len, *sel_read;     // [E_sel]
+    const uint4 *sel;                       // [E_sel] selected events {src lo, src hi, len, record}, grouped by slot; src = index in raw[] of the first sample
     const uint64_t *sel_off;                // [E_sel+1]
     const uint32_t *n_sel;
     const ReadCal *cal;
@@ -452,8 +451,9 @@ __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shf
 #define GATHER_UNROLL 3         // group iterations in flight per lane: the dependent shared-memory loads of one hide behind the other
 #endif
 #define GATHER_MAP 512
-#define GATHER_CH 6                         // 16-byte chunks staged per event: covers 41 samples at the worst alignment
-#define GATHER_EV_SAMPLES (GATHER_CH * 8)
+#define GATHER_CH 10                        // 16-byte chunks staged per event at most: covers 73 samples at the worst alignment
+#define GATHER_CAP_CH 160                   // chunks of staging per batch of 32 events, packed end to end (5 per event on average)
+#define GATHER_STAGE_SAMPLES (GATHER_CAP_CH * 8)
 constexpr int kGatherUnroll = GATHER_UNROLL;
 struct __align__(16) GatherEvP {   // 64 bytes, read with four 16-byte shared-memory loads
     double offset, scale;
@@ -463,10 +463,10 @@ struct __align__(16) GatherEvP {   // 64 bytes, read with four 16-byte shared-me
     uint32_t gstart;          // first group of the event (numbering inside the batch)
     uint32_t len;             // samples of the event
     uint32_t rel;             // output position of its first sample, relative to the batch's first
-    uint32_t packed;          // bits 0-10 index of sample 0 in the staged copy | 11-16 samples staged | 17 fast division | 18 odd start
+    uint32_t packed;          // bits 0-10 index of sample 0 in the staged copy | 11-18 samples staged | 19 fast division | 20 odd start
 };
 struct GatherStage {
-    int16_t raw[2][32 * GATHER_EV_SAMPLES];
+    int16_t raw[2][GATHER_STAGE_SAMPLES];
     GatherEvP ev[32];
     long long base[32];       // raw[] index of the event's first sample
     uint8_t map[GATHER_MAP];
@@ -495,38 +495,49 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
     if (q0 >= n) return;
     // level 1: the event's own row. level 2: its record's calibration and its raw samples (need level 1).
     // Both only ISSUE loads; nothing looks at a loaded value until a batch later.
-    uint32_t rd1, ln1, ok1;
-    uint64_t off1, src1;
+    uint4 row1 = make_uint4(0, 0, 0, 0);
+    uint32_t ok1 = 0;
+    uint64_t off1 = 0;
     auto level1 = [&](uint32_t base) {
         const uint32_t q = base + lane;
         ok1 = (q < n) ? 1u : 0u;
         const uint32_t qq = min(q, n - 1);
-        src1 = io.sel_src[qq]; rd1 = io.sel_read[qq]; ln1 = io.sel_len[qq]; off1 = io.sel_off[qq];
+        row1 = __ldg(io.sel + qq); off1 = io.sel_off[qq];
     };
     uint64_t off2, src2;
-    uint32_t ln2, nst2;      // nst2: samples of the event present in the staged copy
+    uint32_t ln2, nst2, sidx2;      // nst2: samples of the event present in the staged copy, sidx2: where its sample 0 is there
     int clo2, chi2;
     double offset2, scale2, med2 = 0.0, mad2 = 1.0;
+    const uint64_t raw_lim = b.n_raw & ~(uint64_t)7;      // whole 16-byte chunks of raw[] end here: nothing is fetched beyond
     auto level2 = [&](uint32_t buf) {
-        const uint32_t rd = ok1 ? rd1 : 0u;     // level 1 arrived an iteration ago
+        const uint32_t rd = ok1 ? row1.w : 0u;  // level 1 arrived an iteration ago
         const pgm_read *rp = b.reads + rd;
         const ReadCal *rc = io.cal + rd;
-        ln2 = ok1 ? ln1 : 0u;
-        off2 = off1; src2 = src1;
+        ln2 = ok1 ? row1.z : 0u;
+        off2 = off1;
+        src2 = ((uint64_t)row1.y << 32) | row1.x;
         if (off2 + ln2 > io.samples_cap) ln2 = 0;
         offset2 = rp->offset;
         clo2 = rc->clo; chi2 = rc->chi; scale2 = rc->scale;
         if (SCALING) { med2 = rc->med; mad2 = rc->mad; }
-        // raw samples: the 16-byte chunks that hold [src, src + ln), at most GATHER_CH of them
+        // raw samples: the 16-byte chunks that hold [src, src + ln), at most GATHER_CH of them, packed behind the chunks of
+        // the lanes in front (a warp scan places them); what does not fit the batch's staging area, or lies in the last
+        // partial chunk of raw[], is read from global memory by the walk
         const uint32_t mis = (uint32_t)(src2 & 7);                       // samples between the chunk boundary and src
         const uint64_t c0 = src2 - mis;
-        const uint32_t need = ln2 ? (mis + ln2 + 7) >> 3 : 0u;
-        const uint32_t dst = smem_u32(&S.raw[buf][lane * GATHER_EV_SAMPLES]);
+        uint32_t need = ln2 ? min((mis + ln2 + 7) >> 3, (uint32_t)GATHER_CH) : 0u;
+        if (c0 + 8ull * need > raw_lim) need = (raw_lim > c0) ? (uint32_t)((raw_lim - c0) >> 3) : 0u;
+        const uint32_t cinc = warp_incl_scan_add(need);
+        uint32_t cfirst = cinc - need;
+        if (cfirst >= (uint32_t)GATHER_CAP_CH) { cfirst = 0; need = 0; }
+        else if (cfirst + need > (uint32_t)GATHER_CAP_CH) need = GATHER_CAP_CH - cfirst;
+        const uint32_t dst = smem_u32(&S.raw[buf][cfirst * 8]);
 #pragma unroll
         for (int c = 0; c < GATHER_CH; c++)
             if ((uint32_t)c < need) cp_async16(dst + 16u * c, b.raw + c0 + 8u * c);
         cp_async_commit();
-        nst2 = ln2 ? min(ln2, (uint32_t)GATHER_EV_SAMPLES - mis) : 0u;
+        sidx2 = cfirst * 8 + mis;
+        nst2 = (need * 8 > mis) ? min(ln2, need * 8 - mis) : 0u;
     };
     level1(q0);
     level2(0);
@@ -551,7 +562,7 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
             ev.clo = clo2; ev.nbins = (chi2 >= clo2) ? (uint32_t)(chi2 - clo2 + 1) : 0u;
             ev.gstart = gstart; ev.len = ln; ev.rel = rel;
             const uint32_t fast = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
-            ev.packed = (lane * GATHER_EV_SAMPLES + (uint32_t)(src2 & 7)) | (nst2 << 11) | (fast << 17) | (par << 18);
+            ev.packed = sidx2 | (nst2 << 11) | (fast << 19) | (par << 20);
             S.ev[lane] = ev;
         }
         const bool all_staged = __all_sync(PGM_FULL, nst2 == ln);   // no event of the batch longer than its staged copy
@@ -581,11 +592,11 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
                     cv.offset = __hiloint2double((int)a0.y, (int)a0.x); cv.scale = __hiloint2double((int)a0.w, (int)a0.z);
                     cv.med = __hiloint2double((int)a1.y, (int)a1.x); cv.mad = __hiloint2double((int)a1.w, (int)a1.z);
                     cv.rcp = __hiloint2double((int)a2.y, (int)a2.x); cv.clo = (int)a2.z; cv.nbins = a2.w;
-                    cv.fast_div = ((a3.w >> 17) & 1u) != 0;
+                    cv.fast_div = ((a3.w >> 19) & 1u) != 0;
                     const uint32_t len = a3.y;
                     const int sidx = (int)(a3.w & 0x7ffu);
-                    const uint32_t nst = (a3.w >> 11) & 0x3fu;
-                    const int t0 = (int)(4u * (g - a3.x)) - (int)((a3.w >> 18) & 1u);   // event sample in the group's first slot
+                    const uint32_t nst = (a3.w >> 11) & 0xffu;
+                    const int t0 = (int)(4u * (g - a3.x)) - (int)((a3.w >> 20) & 1u);   // event sample in the group's first slot
                     double o4[4];
                     bool ok[4];
 #pragma unroll
