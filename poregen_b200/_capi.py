@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpgm_gmove.so")
+LIB_PATH = os.environ.get("PGM_LIB") or os.path.join(HERE, "libpgm_gmove.so")   # PGM_LIB: a kernel-variant build (profiles/micro)
 
 PGM_OK, PGM_ERR_ARG, PGM_ERR_CUDA, PGM_ERR_NOMEM, PGM_ERR_INPUT, PGM_ERR_STATE = range(6)
 PGM_MODE_MOVES_CHAR, PGM_MODE_SS, PGM_MODE_MOVES_I8 = 0, 1, 2

@@ -259,11 +259,11 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     if (bit_length(opts->n_slots - 1) > 2 * MSD_MAX_LO_BITS)
         return fail(nullptr, PGM_ERR_ARG, "n_slots %u needs more than two digits of %d bits", opts->n_slots, MSD_MAX_LO_BITS);
     if ((e = cudaFuncSetAttribute(k_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, RANK_SMEM)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_msd_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((RANK_WARPS + 1) * (1u << MSD_MAX_LO_BITS) * 4))) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_msd_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MSD_SCATTER_SMEM(MSD_MAX_LO_BITS))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_msd_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MSD_RANK_SMEM(MSD_MAX_LO_BITS))) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_stats, cudaFuncAttributeMaxDynamicSharedMemorySize, STATS_DYN_SMEM)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_gather<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_gather<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(GatherStage) * GATHER_WARPS))) != cudaSuccess)
+        (e = cudaFuncSetAttribute(k_gather<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GATHER_SMEM)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_gather<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GATHER_SMEM)) != cudaSuccess)
         return fail(nullptr, PGM_ERR_CUDA, "cudaFuncSetAttribute(k_stats / k_gather): %s", cudaGetErrorString(e));
 
     pgm_ctx *c = new pgm_ctx();
@@ -363,6 +363,7 @@ static SortPlan sort_plan(const pgm_ctx *c) {
 static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     if (b->mode > PGM_MODE_MOVES_I8) return fail(c, PGM_ERR_ARG, "unknown batch mode %u", b->mode);
     if (b->n_align >= (1ull << 32)) return fail(c, PGM_ERR_ARG, "n_align must be < 2^32 per batch");
+    if (b->n_raw >= (1ull << 40)) return fail(c, PGM_ERR_ARG, "n_raw must be < 2^40 per batch");
     if (b->n_reads && (!b->reads || (b->n_raw && !b->raw) || (b->n_align && !b->align) || (b->n_bases && !b->bases)))
         return fail(c, PGM_ERR_ARG, "null array in batch");
     const uint32_t R = b->n_reads;
@@ -393,7 +394,7 @@ static int prepare_batch(pgm_ctx *c, const pgm_batch *b) {
     const uint32_t ntiles = cdiv(cap ? cap : 1, SORT_TILE);
     c->sort_ntiles = ntiles;
     {   // per-batch zero region: scalars | misc words | look-back status words | read_has_sel[R]; then (not zeroed) the tile histogram
-        c->lb_words = (size_t)R / LB_TILE + c->opts.n_slots / LB_TILE + 2 * ((size_t)cap / LB_TILE) + 12 +
+        c->lb_words = (size_t)R / LB_TILE + c->opts.n_slots / LB_TILE + 2 * ((size_t)cap / LB_TILE) + 16 +
                       (((size_t)ntiles << sp.first_bits) / LB_TILE + 2);
         c->has_sel_off = (ZB_STATUS_OFF + c->lb_words * 8 + 255) & ~(size_t)255;
         c->hist_off = (c->has_sel_off + (size_t)R + 255) & ~(size_t)255;
@@ -554,6 +555,7 @@ int pgm_count(pgm_ctx *c) {
             io.ev_cap = c->ev_cap;
             io.rflags = P<uint8_t>(c->rflags);
             io.examined = &SCALARS(c)->examined;
+            io.err_flag = &SCALARS(c)->err_flag;
             io.rows_tmp = P<uint4>(c->rows_tmp); io.tmp_shift = c->tmp_shift;
             io.sc_start = P<uint32_t>(c->sc_start); io.sc_end = P<uint32_t>(c->sc_end);
             io.sc_code = P<uint8_t>(c->sc_code); io.sc_indel = P<int32_t>(c->sc_indel);
@@ -563,7 +565,7 @@ int pgm_count(pgm_ctx *c) {
                 const uint32_t want = cdiv(R, DEC_WARPS), full = (uint32_t)c->n_sm * (2048 / PGM_BLOCK);
                 k_decode<<<want < full ? want : full, PGM_BLOCK, 0, st>>>(d, c->db, io);
             } else {   // move tables: one CTA per record at a time
-                const uint32_t full = (uint32_t)c->n_sm * 3;
+                const uint32_t full = (uint32_t)c->n_sm * DM_MIN_CTAS;
                 k_decode_moves<<<R < full ? R : full, DM_THREADS, 0, st>>>(d, c->db, io);
             }
             c->launches++;
@@ -573,7 +575,7 @@ int pgm_count(pgm_ctx *c) {
             c->launches++;
             if (c->ev_cap) {   // tile histogram of the first digit, over the dense (record, position) order
                 const uint32_t grid = std::min<uint32_t>(c->sort_ntiles, (uint32_t)c->n_sm * 8);
-                k_tile_hist<<<grid, PGM_BLOCK, 0, st>>>(ev_source(c), P<uint32_t>(c->ev_base) + R, sp.first_shift, sp.first_bits, HIST(c), c->sort_ntiles);
+                k_tile_hist<<<grid, PGM_BLOCK, 0, st>>>(ev_source(c), P<uint32_t>(c->ev_base) + R, sp.first_shift, sp.first_bits, HIST(c));
                 c->launches++;
             }
         }
@@ -680,7 +682,7 @@ int pgm_emit(pgm_ctx *c) {
         CU(c, cudaEventRecord(c->ev_fork, st));
         CU(c, cudaStreamWaitEvent(c->aux, c->ev_fork, 0));
         StageTimer t(c, PGM_STAGE_SORT, c->aux);
-        k_scan_hist<<<cdiv((uint64_t)first_bins * c->sort_ntiles, LB_TILE), PGM_BLOCK, 0, c->aux>>>(HIST(c), n_ev, first_bins, c->sort_ntiles,
+        k_scan_hist<<<cdiv((uint64_t)first_bins * c->sort_ntiles, LB_TILE), PGM_BLOCK, 0, c->aux>>>(HIST(c), n_ev, first_bins,
                                                                                                next_lb(c, cdiv((uint64_t)first_bins * c->sort_ntiles, LB_TILE)));
         c->launches++;
         t.stop();
@@ -707,24 +709,24 @@ int pgm_emit(pgm_ctx *c) {
         uint8_t *has_sel = c->opts.scaling ? HAS_SEL(c) : nullptr;
         if (!sp.hi_bits) {
             RankIO r;
-            r.n_events = n_ev; r.src = ev_source(c); r.hist_scanned = HIST(c); r.ntiles_cap = ntiles; r.bits = sp.bits;
+            r.n_events = n_ev; r.src = ev_source(c); r.hist_scanned = HIST(c); r.bits = sp.bits;
             r.bucket_base = P<uint32_t>(c->bucket_base); r.keep = P<uint32_t>(c->keep); r.sel_base = P<uint32_t>(c->sel_base);
-            r.sel = P<uint4>(c->sel); r.rec_src0 = P<unsigned long long>(c->rec_src0); r.read_has_sel = has_sel;
+            r.sel = P<uint4>(c->sel); r.read_has_sel = has_sel;
             k_rank<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, (RANK_WARPS + 1) * (1u << sp.bits) * 4, st>>>(r);
             c->launches++;
         } else {
             MsdScatterIO ms;
-            ms.n_events = n_ev; ms.src = ev_source(c); ms.hist_scanned = HIST(c); ms.ntiles_cap = ntiles;
+            ms.n_events = n_ev; ms.src = ev_source(c); ms.hist_scanned = HIST(c);
             ms.shift = sp.lo_bits; ms.bits = sp.hi_bits; ms.rows_out = P<uint4>(c->rows_a);
-            k_msd_scatter<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, (RANK_WARPS + 1) * (1u << sp.hi_bits) * 4, st>>>(ms);
+            k_msd_scatter<<<std::min<uint32_t>(ntiles, (uint32_t)c->n_sm * 2), RANK_BLOCK, MSD_SCATTER_SMEM(sp.hi_bits), st>>>(ms);
             MsdRankIO mr;
-            mr.n_events = n_ev; mr.rows_in = P<uint4>(c->rows_a); mr.hist_scanned = HIST(c); mr.ntiles_cap = ntiles;
+            mr.n_events = n_ev; mr.rows_in = P<uint4>(c->rows_a); mr.hist_scanned = HIST(c);
             mr.hi_bits = sp.hi_bits; mr.lo_bits = sp.lo_bits; mr.n_slots = NS;
             mr.keep = P<uint32_t>(c->keep); mr.sel_base = P<uint32_t>(c->sel_base);
-            mr.sel = P<uint4>(c->sel); mr.rec_src0 = P<unsigned long long>(c->rec_src0); mr.read_has_sel = has_sel;
+            mr.sel = P<uint4>(c->sel); mr.read_has_sel = has_sel;
             mr.ticket = MISC(c) + 4;
             const uint32_t n_buckets = cdiv(NS, 1u << sp.lo_bits);
-            k_msd_rank<<<std::min<uint32_t>(n_buckets, (uint32_t)c->n_sm * 2), RANK_BLOCK, MSD_RANK_SMEM(sp.lo_bits), st>>>(mr);
+            k_msd_rank<<<std::min<uint32_t>(n_buckets, (uint32_t)c->n_sm * MSD_MIN_CTAS), MSD_BLOCK, MSD_RANK_SMEM(sp.lo_bits), st>>>(mr);
             c->launches += 2;
         }
         CU(c, cudaGetLastError());
@@ -768,14 +770,14 @@ int pgm_emit(pgm_ctx *c) {
         g.samples = P<double>(c->samples); g.samples_cap = c->samples_cap;
         if (!c->gather_ctas) {   // resident CTAs per SM of the instantiation in use (registers and shared memory decide)
             int nb = 0;
-            const size_t sm = sizeof(GatherStage) * GATHER_WARPS;
+            const size_t sm = GATHER_SMEM;
             if (c->opts.scaling) CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gather<true>, GATHER_WARPS * 32, sm));
             else CU(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_gather<false>, GATHER_WARPS * 32, sm));
             c->gather_ctas = nb > 0 ? (uint32_t)nb : 1u;
         }
         const uint32_t ggrid = (uint32_t)c->n_sm * c->gather_ctas;
-        if (c->opts.scaling) k_gather<true><<<ggrid, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
-        else k_gather<false><<<ggrid, GATHER_WARPS * 32, sizeof(GatherStage) * GATHER_WARPS, st>>>(d, c->db, g);
+        if (c->opts.scaling) k_gather<true><<<ggrid, GATHER_WARPS * 32, GATHER_SMEM, st>>>(d, c->db, g);
+        else k_gather<false><<<ggrid, GATHER_WARPS * 32, GATHER_SMEM, st>>>(d, c->db, g);
         c->launches++;
     }
     if (c->opts.output != PGM_OUT_F64) {
@@ -817,6 +819,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     if (R) CU(c, cudaMemcpyAsync(c->h_rflags.p, c->rflags.p, R, cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     const Scalars s = *c->h_scalars;
+    if (s.err_flag & 2u) return fail(c, PGM_ERR_INPUT, "an event is longer than %u samples (max_dur / --margin too large for the event rows)", EV_MAX_LEN);
     if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays (or ss records with a trim offset)");
     if (c->svb_used && *P<uint32_t>(c->h_svb_err))
         return fail(c, PGM_ERR_INPUT, "svb-zd stream of a record does not decode to its raw_len samples");

@@ -29,7 +29,8 @@ struct DecodeIO {
     uint32_t ev_cap;           // capacity of the event arrays
     uint8_t *rflags;           // [R] PGM_RF_*
     unsigned long long *examined;
-    // per-record temporaries: record r's passing events, in position order, as rows {slot, start, len, r} at
+    uint32_t *err_flag;        // bit 1: an event longer than EV_MAX_LEN samples (its row cannot hold it)
+    // per-record temporaries: record r's passing events, in position order, as rows (EvRow, pgm_sort.cuh) at
     // rows_tmp[(align_off >> tmp_shift) + j] (EvSource, pgm_sort.cuh)
     uint4 *rows_tmp;
     uint32_t tmp_shift;
@@ -310,7 +311,8 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
             if (ok) {
                 const uint32_t p = pbase + __popc(bm & ((1u << lane) - 1));
                 atomicAdd(io.counts + slot, 1u);
-                t_rows[p] = make_uint4(slot, s2, len, r);
+                if (len > EV_MAX_LEN) atomicOr(io.err_flag, 2u);
+                t_rows[p] = ev_row(slot, rd.raw_off + s2, len, r);            // the ss path never trims (gmove.cpp:750-753)
             }
             pbase += __popc(bm);
         }
@@ -322,24 +324,29 @@ __device__ __forceinline__ uint32_t decode_ss_record(const DevOpts &o, const Dev
 
 // ------------------------------------------------------------------------------------------------
 // k_decode_moves: the move-table decoder (PGM_MODE_MOVES_CHAR / _I8), one CTA per record at a time.
-// Reference gmove.cpp:620-690, 1182-1252; the work is laid out
-// for long records (C3: 8,700 moves, 4,200 events per record):
-//   * a step is DM_CHUNK move bytes, eight per thread (one aligned 8-byte load); a block scan numbers the set
-//     moves, a second one carries the position of the last set move in front of a thread's bytes;
-//   * the bases the step's events need are one contiguous window of the sequence: staged once as 2-bit codes in
-//     shared memory; a thread's events are consecutive, so its k-mer id ROLLS (one code per event);
-//   * every event is evaluated ONCE; the quota look-ups of a thread's (up to eight) events are issued together;
-//     passing events are kept in registers until a third block scan gives their place in the record's
-//     temporary (position order).
+// Reference gmove.cpp:620-690, 1182-1252; the work is laid out for long records (C3: 8,700 moves, 4,200 events each):
+//   * a step is DM_CHUNK move bytes, eight per thread (one aligned 8-byte load, the next step's already on its way);
+//     a block scan numbers the set moves and every thread drops the positions of its own into a shared list;
+//   * the events of the step are then dealt out EVENLY: thread t takes the c = ceil(n / 256) consecutive events from
+//     t * c on (a thread's own eight bytes hold anything from 0 to 8 set moves: walking those would run every warp
+//     for the worst lane - profiles/ncu_r02_c3block.md);
+//   * the bases the step's events need are one contiguous window of the sequence: fetched as 16-byte words at the
+//     top of the step, staged as 2-bit codes in shared memory; a thread's events are consecutive, so its k-mer id
+//     ROLLS (one code per event);
+//   * every event is evaluated ONCE; the quota look-ups of a thread's events are issued together; passing events stay
+//     in registers until a second block scan gives their place in the record's temporary (position order).
 #define DM_THREADS 256
 #define DM_WARPS (DM_THREADS / 32)
 #define DM_PER 8
 #define DM_CHUNK (DM_THREADS * DM_PER)
+#ifndef DM_MIN_CTAS
+#define DM_MIN_CTAS 4
+#endif
 
-__global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBatch b, DecodeIO gio) {
-    __shared__ uint8_t sm_codes[DM_CHUNK + 32];
+__global__ void __launch_bounds__(DM_THREADS, DM_MIN_CTAS) k_decode_moves(DevOpts o, DevBatch b, DecodeIO gio) {
+    __shared__ __align__(16) uint8_t sm_codes[DM_CHUNK + 64];
+    __shared__ uint16_t sm_pos[DM_CHUNK];            // step-relative byte index of every set move of the step
     __shared__ uint32_t sm_cnt_w[DM_WARPS], sm_pass_w[DM_WARPS];
-    __shared__ int sm_last_w[DM_WARPS];
     __shared__ uint32_t sm_rec;
     __shared__ uint32_t sm_cons[DEC_SLOT_SMEM], sm_cnt[DEC_SLOT_SMEM];
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -351,6 +358,7 @@ __global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBa
     }
     const uint32_t one8 = (b.mode == PGM_MODE_MOVES_CHAR) ? 0x31313131u : 0x01010101u;
     const uint32_t idmask = (o.k >= 16) ? 0xffffffffu : ((1u << (2 * o.k)) - 1u);
+    const uint8_t *bases_end = b.bases + b.n_bases;
     uint32_t my_exam = 0;
     for (;;) {
         __syncthreads();
@@ -371,100 +379,126 @@ __global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBa
         const uint8_t *abase = mv - head;
         const uint32_t span = head + M;
         uint4 *t_rows = io.rows_tmp + (rd.align_off >> io.tmp_shift);
+        const unsigned long long src0 = rd.raw_off + rd.trim;       // raw[] index of the record's sample 0
         uint32_t ones_carry = 0, pbase = 0;
         int last_carry = -1;
+        uint2 xn = make_uint2(0u, 0u);
+        if (DM_PER * tid < span) xn = __ldg(reinterpret_cast<const uint2 *>(abase + DM_PER * tid));   // a word with one valid byte lies inside the allocation
         for (uint32_t cb = 0; cb < span; cb += DM_CHUNK) {
             const uint32_t off = cb + DM_PER * tid;
-            uint2 x = make_uint2(0u, 0u);
-            if (off < span) x = __ldg(reinterpret_cast<const uint2 *>(abase + off));   // a word with one valid byte lies inside the allocation
+            const uint2 x = xn;
+            if (off + DM_CHUNK < span) xn = __ldg(reinterpret_cast<const uint2 *>(abase + off + DM_CHUNK));
+            // ---- the bases of the step's events. The set move with `rank` set moves of the record in front of it closes
+            // event rank-1, examined when rank > m, labelled with the k-mer at base s_off + rank - m - 1. The step's first set
+            // move has rank ones_carry: its window starts at base w0 and is at most DM_CHUNK + k - 1 bases long. Thread t
+            // fetches the aligned 16-byte word t of it now and turns it into codes while the set moves are being counted.
+            const int64_t w0 = (int64_t)o.s_off + (int64_t)ones_carry - (int64_t)o.m - 1;
+            const int64_t wlo = max(w0, (int64_t)0);
+            const uint8_t *wbase = seq + (wlo & ~(int64_t)15) - (((uintptr_t)seq) & 15);     // 16-byte aligned address at or below seq + wlo
+            const int shw = (int)(w0 - (int64_t)(wbase - seq));                              // codes index of window position 0 (may be negative: bases in front of the sequence)
+            if (16 * tid < DM_CHUNK + 48) {
+                const uint8_t *wword = wbase + 16 * tid;
+                const int64_t sp0 = (int64_t)(wword - seq);                                   // sequence position of the word's byte 0
+                const int lo_b = (int)min(max(wlo - sp0, (int64_t)0), (int64_t)16), hi_b = (int)min(max((int64_t)rd.seq_len - sp0, (int64_t)0), (int64_t)16);
+                uint32_t cw[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};     // 0xFF = no base here (U4: beyond the sequence = no match)
+                if (lo_b < hi_b) {
+                    uint32_t wv[4];
+                    if (wword >= b.bases && wword + 16 <= bases_end) {
+                        const uint4 bw = __ldg(reinterpret_cast<const uint4 *>(wword));
+                        wv[0] = bw.x; wv[1] = bw.y; wv[2] = bw.z; wv[3] = bw.w;
+                    } else {                                                               // the array's first / last partial word: byte by byte
+                        wv[0] = wv[1] = wv[2] = wv[3] = 0;
+                        for (int q = lo_b; q < hi_b; q++) wv[q >> 2] |= (uint32_t)__ldg(wword + q) << (8 * (q & 3));
+                    }
+                    const uint32_t m16 = ((1u << hi_b) - 1u) & ~((1u << lo_b) - 1u);
+                    const uint32_t f4 = o.fourth * 0x01010101u;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t w = wv[j];
+                        const uint32_t eC = byte_is_zero(w ^ 0x43434343u), eG = byte_is_zero(w ^ 0x47474747u), eF = byte_is_zero(w ^ f4);
+                        uint32_t valid = byte_is_zero(w ^ 0x41414141u) | eC | eG | eF;                     // 0x80 per byte that is A, C, G or the fourth letter
+                        valid &= ((((m16 >> (4 * j)) & 0xfu) * 0x00204081u) & 0x01010101u) << 7;              // and lies inside the sequence
+                        const uint32_t code = ((eC | eF) >> 7) | ((eG | eF) >> 6);
+                        cw[j] = (code & (valid >> 7) * 3u) | (((~valid & 0x80808080u) >> 7) * 0xffu);
+                    }
+                }
+                *reinterpret_cast<uint4 *>(sm_codes + 16 * tid) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+            }
             const int p0 = (int)off - (int)head;                                       // string position of the thread's byte 0
             const uint32_t lo = (off < head) ? min((uint32_t)DM_PER, head - off) : 0u;
             const uint32_t hi = (off >= span) ? 0u : min((uint32_t)DM_PER, span - off);
             uint32_t bits = byte_nibble(byte_is_zero(x.x ^ one8)) | (byte_nibble(byte_is_zero(x.y ^ one8)) << 4);
             bits &= (hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
             const uint32_t cnt = __popc(bits);
-            const int lastpos = bits ? p0 + 31 - __clz(bits) : -1;
-            // block scans: set moves in front of the thread (sum), last set position in front of it (max)
             const uint32_t inc_cnt = warp_incl_scan_add(cnt);
-            const int inc_last = warp_incl_scan_max(lastpos);
-            int ex_last_w = __shfl_up_sync(0xffffffffu, inc_last, 1);
-            if (lane == 0) ex_last_w = -1;
-            if (lane == 31) { sm_cnt_w[wid] = inc_cnt; sm_last_w[wid] = inc_last; }
-            __syncthreads();
+            if (lane == 31) sm_cnt_w[wid] = inc_cnt;
+            __syncthreads();                                                            // A
             uint32_t wbase_cnt = 0, tot_cnt = 0;
-            int wbase_last = -1, tot_last = -1;
 #pragma unroll
             for (int w = 0; w < DM_WARPS; w++) {
                 const uint32_t c = sm_cnt_w[w];
-                const int l = sm_last_w[w];
-                if ((uint32_t)w < wid) { wbase_cnt += c; wbase_last = max(wbase_last, l); }
-                tot_cnt += c; tot_last = max(tot_last, l);
+                if ((uint32_t)w < wid) wbase_cnt += c;
+                tot_cnt += c;
             }
-            const uint32_t li0 = wbase_cnt + inc_cnt - cnt;                           // set moves of the step in front of the thread
-            const int ex_last = max(last_carry, max(wbase_last, ex_last_w));
-            // ---- the bases of the step's events as codes. The set move with `rank` set moves of the record in front of it
-            // closes event rank-1, examined when rank > m, labelled with the k-mer at base s_off + rank - m - 1.
-            const int64_t w0 = (int64_t)o.s_off + (int64_t)ones_carry - (int64_t)o.m - 1;   // base of the step's first set move
-            const uint32_t nwin = tot_cnt ? tot_cnt + o.k - 1 : 0u;
-            for (uint32_t i = tid; i < nwin; i += DM_THREADS) {
-                const int64_t sp = w0 + i;
-                uint32_t c = 0xFF;
-                if (sp >= 0 && sp < (int64_t)rd.seq_len) c = pgm_base_code(__ldg(seq + sp), o.fourth, false);   // U4: beyond the sequence = no match
-                sm_codes[i] = (uint8_t)c;
+            {   // the positions of the thread's set moves, in order, into the step's list
+                uint32_t q = wbase_cnt + inc_cnt - cnt;
+                for (uint32_t m = bits; m; m &= m - 1) sm_pos[q++] = (uint16_t)(DM_PER * tid + __ffs(m) - 1);
             }
-            __syncthreads();
-            // ---- the thread's events (its own set bits: consecutive events, consecutive bases)
+            __syncthreads();                                                            // B
+            // ---- the thread's events: c consecutive ones from tid * c on
+            const uint32_t c_ev = (tot_cnt + DM_THREADS - 1) / DM_THREADS;
+            const uint32_t e0 = tid * c_ev;
+            const uint32_t c_mine = (e0 < tot_cnt) ? min(c_ev, tot_cnt - e0) : 0u;
             uint32_t ev_slot[DM_PER], ev_s2[DM_PER], ev_len[DM_PER];
-            uint32_t cand = 0;                       // bit i: byte i closes an event that passed everything but the quota
-            if (bits) {
+            uint32_t cand = 0;                       // bit j: the thread's j-th event passed everything but the quota
+            if (c_mine) {
                 uint32_t id = 0, run = 0;            // run = consecutive valid codes ending at the newest one (saturates at k)
                 for (uint32_t t = 0; t + 1 < o.k; t++) {
-                    const uint32_t c = sm_codes[li0 + t];
+                    const uint32_t c = sm_codes[max((int)(e0 + t) + shw, 0)];
                     id = ((id << 2) | (c & 3u)) & idmask;
                     run = (c == 0xFF) ? 0u : min(run + 1u, o.k);
                 }
-                uint32_t j = 0;
-                int prev = ex_last;
+                int prev = e0 ? (int)cb + (int)sm_pos[e0 - 1] - (int)head : last_carry;
 #pragma unroll
-                for (int i = 0; i < DM_PER; i++) {
-                    ev_slot[i] = 0; ev_s2[i] = 0; ev_len[i] = 0;
-                    if ((bits >> i) & 1u) {
-                        const uint32_t c = sm_codes[li0 + j + o.k - 1];
+                for (int j = 0; j < DM_PER; j++) {
+                    ev_slot[j] = 0; ev_s2[j] = 0; ev_len[j] = 0;
+                    if ((uint32_t)j < c_mine) {
+                        const uint32_t e = e0 + j;
+                        const uint32_t c = sm_codes[max((int)(e + o.k - 1) + shw, 0)];
                         id = ((id << 2) | (c & 3u)) & idmask;
                         run = (c == 0xFF) ? 0u : min(run + 1u, o.k);
-                        const uint32_t rank = ones_carry + li0 + j;
-                        const int p = p0 + i;
+                        const uint32_t rank = ones_carry + e;
+                        const int p = (int)cb + (int)sm_pos[e] - (int)head;
                         if (rank > o.m) {
                             my_exam++;
-                            const uint32_t start = (uint32_t)((uint64_t)(uint32_t)prev * rd.stride);
-                            const uint32_t end = (uint32_t)((uint64_t)(uint32_t)p * rd.stride);
+                            const uint32_t start = (uint32_t)prev * rd.stride, end = (uint32_t)p * rd.stride;   // modulo 2^32, like the reference's uint32_t
                             const uint32_t dur = end - start;
                             const uint32_t sl = (run >= o.k) ? pgm_slot_of(o, id) : PGM_INVALID;
                             const uint32_t a = (start < o.margin) ? 0u : start - o.margin;                 // U2
                             const uint32_t e1 = end + o.margin;
                             const uint32_t e2 = ((uint64_t)e1 > n_sig) ? (uint32_t)n_sig : e1;
                             if (!(dur > o.max_dur) && !(dur < o.min_dur) && sl != PGM_INVALID && a < e2) {   // gmove.cpp:641-662, U3
-                                cand |= 1u << i;
-                                ev_slot[i] = sl; ev_s2[i] = a; ev_len[i] = e2 - a;
+                                cand |= 1u << j;
+                                ev_slot[j] = sl; ev_s2[j] = a; ev_len[j] = e2 - a;
                             }
                         }
                         prev = p;
-                        j++;
                     }
                 }
             }
+            const int last_here = tot_cnt ? (int)cb + (int)sm_pos[tot_cnt - 1] - (int)head : -1;
             // quota look-ups of all candidates together (gmove.cpp:650-652), then the survivors
             uint32_t cons[DM_PER];
 #pragma unroll
-            for (int i = 0; i < DM_PER; i++) cons[i] = ((cand >> i) & 1u) ? io.consumed[ev_slot[i]] : 0xffffffffu;
+            for (int j = 0; j < DM_PER; j++) cons[j] = ((cand >> j) & 1u) ? io.consumed[ev_slot[j]] : 0xffffffffu;
             uint32_t okmask = 0;
 #pragma unroll
-            for (int i = 0; i < DM_PER; i++)
-                if (((cand >> i) & 1u) && cons[i] < o.limit) { okmask |= 1u << i; atomicAdd(io.counts + ev_slot[i], 1u); }
+            for (int j = 0; j < DM_PER; j++)
+                if (((cand >> j) & 1u) && cons[j] < o.limit) { okmask |= 1u << j; atomicAdd(io.counts + ev_slot[j], 1u); }
             const uint32_t np = __popc(okmask);
             const uint32_t inc_p = warp_incl_scan_add(np);
             if (lane == 31) sm_pass_w[wid] = inc_p;
-            __syncthreads();
+            __syncthreads();                                                            // C
             uint32_t wbase_p = 0, tot_p = 0;
 #pragma unroll
             for (int w = 0; w < DM_WARPS; w++) {
@@ -474,11 +508,14 @@ __global__ void __launch_bounds__(DM_THREADS, 3) k_decode_moves(DevOpts o, DevBa
             }
             uint32_t wr = pbase + wbase_p + inc_p - np;
 #pragma unroll
-            for (int i = 0; i < DM_PER; i++)
-                if ((okmask >> i) & 1u) t_rows[wr++] = make_uint4(ev_slot[i], ev_s2[i], ev_len[i], r);
+            for (int j = 0; j < DM_PER; j++)
+                if ((okmask >> j) & 1u) {
+                    if (ev_len[j] > EV_MAX_LEN) atomicOr(io.err_flag, 2u);
+                    t_rows[wr++] = ev_row(ev_slot[j], src0 + ev_s2[j], ev_len[j], r);
+                }
             pbase += tot_p;
             ones_carry += tot_cnt;
-            last_carry = max(last_carry, tot_last);
+            last_carry = max(last_carry, last_here);
         }
         if (tid == 0) {
             const bool bad = ones_carry <= o.m;                                        // U1

@@ -143,8 +143,6 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf st) {
         });
 }
 
-// k_scan_sel: sample offsets of the selected events (exclusive scan of their lengths, 64-bit) and the
-// batch summary, in one launch.
 struct BatchScalars {  // device -> host summary of one batch
     unsigned long long examined;
     unsigned long long n_sel_samples;
@@ -155,16 +153,57 @@ struct BatchScalars {  // device -> host summary of one batch
     unsigned long long n_text;   // PGM_OUT_TEXT: characters of the dump text
 };
 
+// k_scan_sel: sample offsets of the selected events (exclusive scan of their lengths, 64-bit, decoupled look-back over tiles
+// of LB_TILE events) and the batch summary, in one launch. The rows are read and the offsets written warp-contiguous
+// (a thread's sixteen consecutive events take the detour through shared memory): the kernel moves 16 bytes in and 8 bytes out
+// per event and nothing else.
+#define SCANSEL_PAD(j) ((j) + ((j) >> 4))      // one pad word per sixteen: the per-thread (stride 16) and the per-warp (stride 1) walks both stay conflict-free
 __global__ void __launch_bounds__(PGM_BLOCK) k_scan_sel(const uint4 *sel, unsigned long long *sel_off, const uint32_t *n_sel_ptr,
                                                         const uint32_t *n_pass_ptr, BatchScalars *sc, LbBuf st) {
+    __shared__ uint32_t sm_v[LB_TILE + LB_TILE / 16];
+    __shared__ unsigned long long sm_scan[PGM_WARPS + 1];
+    __shared__ unsigned long long sm_prefix;
+    __shared__ uint32_t sm_tile;
     const uint32_t n = *n_sel_ptr;
-    lb_scan<unsigned long long>(
-        n, st, [&](uint64_t i) { return (unsigned long long)sel[i].z; },
-        [&](uint64_t i, unsigned long long ex, unsigned long long) { sel_off[i] = ex; },
-        [&](unsigned long long tot) {
-            sel_off[n] = tot;
-            sc->n_sel_samples = tot;
-            sc->n_sel = n;
-            sc->n_pass = *n_pass_ptr;
-        });
+    if (threadIdx.x == 0) sm_tile = atomicAdd(st.ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = sm_tile;
+    const uint32_t ntiles = (n + LB_TILE - 1) / LB_TILE;
+    if (tile >= ntiles) {
+        if (n == 0 && tile == 0 && threadIdx.x == 0) { sel_off[0] = 0; sc->n_sel_samples = 0; sc->n_sel = 0; sc->n_pass = *n_pass_ptr; }
+        return;
+    }
+    const uint32_t base = tile * LB_TILE;
+#pragma unroll
+    for (int i = 0; i < LB_ITEMS; i++) {
+        const uint32_t j = threadIdx.x + PGM_BLOCK * i;
+        sm_v[SCANSEL_PAD(j)] = (base + j < n) ? (__ldg(sel + base + j).z & 0x00ffffffu) : 0u;
+    }
+    __syncthreads();
+    uint32_t v[LB_ITEMS];
+    unsigned long long s = 0;
+#pragma unroll
+    for (int i = 0; i < LB_ITEMS; i++) { v[i] = sm_v[SCANSEL_PAD(threadIdx.x * LB_ITEMS + i)]; s += v[i]; }
+    unsigned long long tot;
+    const unsigned long long ex = block_excl_scan_add_t<unsigned long long>(s, sm_scan, &tot);
+    if (threadIdx.x < 32) {
+        const unsigned long long excl = lb_lookback(st, tile, tot);
+        if (threadIdx.x == 0) sm_prefix = excl;
+    }
+    if (tot > 0xffffffffull && threadIdx.x == 0) atomicOr(&sc->err_flag, 4u);     // offsets inside a tile travel as 32 bits
+    uint32_t run = (uint32_t)ex;
+#pragma unroll
+    for (int i = 0; i < LB_ITEMS; i++) { sm_v[SCANSEL_PAD(threadIdx.x * LB_ITEMS + i)] = run; run += v[i]; }
+    __syncthreads();
+    const unsigned long long prefix = sm_prefix;
+#pragma unroll
+    for (int i = 0; i < LB_ITEMS; i++) {
+        const uint32_t j = threadIdx.x + PGM_BLOCK * i;
+        if (base + j < n) sel_off[base + j] = prefix + sm_v[SCANSEL_PAD(j)];
+    }
+    if (tile == ntiles - 1 && threadIdx.x == 0) {
+        sel_off[n] = prefix + tot;
+        sc->n_sel_samples = prefix + tot; sc->n_sel = n; sc->n_pass = *n_pass_ptr;
+    }
 }
+

@@ -59,6 +59,38 @@ __device__ __forceinline__ T warp_sum_t(T v) {
     return v;
 }
 
+// The look-back step on its own, for kernels that bring their own tile aggregate (k_gather): called by the 32 lanes of
+// ONE warp with uniform arguments. Publishes the aggregate of `tile`, sums the tiles in front of it (waiting for each
+// one's aggregate or inclusive prefix), publishes the inclusive prefix, returns the exclusive one in every lane.
+__device__ __forceinline__ unsigned long long lb_lookback(LbBuf st, uint32_t tile, unsigned long long tot) {
+    const uint32_t lane = threadIdx.x & 31;
+    unsigned long long excl = 0;
+    if (tile == 0) {
+        if (lane == 0) st_volatile_u64(st.status, (tot << 2) | 2ull);
+        return 0ull;
+    }
+    if (lane == 0) st_volatile_u64(st.status + tile, (tot << 2) | 1ull);
+    int64_t pos = (int64_t)tile - 1;
+    for (;;) {
+        const int64_t idx = pos - (int64_t)lane;
+        unsigned long long w = 2ull;   // before tile 0: prefix 0
+        if (idx >= 0) {
+            do { w = ld_volatile_u64(st.status + idx); } while ((w & 3ull) == 0);
+        }
+        const uint32_t m2 = __ballot_sync(0xffffffffu, (w & 3ull) == 2ull);
+        const unsigned long long val = w >> 2;
+        if (m2) {
+            const uint32_t L = __ffs(m2) - 1;
+            excl += warp_sum_t<unsigned long long>(lane <= L ? val : 0ull);
+            break;
+        }
+        excl += warp_sum_t<unsigned long long>(val);
+        pos -= 32;
+    }
+    if (lane == 0) st_volatile_u64(st.status + tile, ((excl + tot) << 2) | 2ull);
+    return excl;
+}
+
 // load(idx) -> T, store(idx, exclusive_prefix, own_value), fin(total) (one thread of the last tile).
 template <typename T, typename LoadF, typename StoreF, typename FinalF>
 __device__ __forceinline__ void lb_scan(uint64_t n, LbBuf st, LoadF load, StoreF store, FinalF fin) {
@@ -85,32 +117,8 @@ __device__ __forceinline__ void lb_scan(uint64_t n, LbBuf st, LoadF load, StoreF
     T tot;
     const T ex = block_excl_scan_add_t<T>(s, sm_scan, &tot);
     if (threadIdx.x < 32) {
-        const uint32_t lane = threadIdx.x;
-        unsigned long long excl = 0;
-        if (tile == 0) {
-            if (lane == 0) st_volatile_u64(st.status, ((unsigned long long)tot << 2) | 2ull);
-        } else {
-            if (lane == 0) st_volatile_u64(st.status + tile, ((unsigned long long)tot << 2) | 1ull);
-            int64_t pos = (int64_t)tile - 1;
-            for (;;) {
-                const int64_t idx = pos - (int64_t)lane;
-                unsigned long long w = 2ull;   // before tile 0: prefix 0
-                if (idx >= 0) {
-                    do { w = ld_volatile_u64(st.status + idx); } while ((w & 3ull) == 0);
-                }
-                const uint32_t m2 = __ballot_sync(0xffffffffu, (w & 3ull) == 2ull);
-                const unsigned long long val = w >> 2;
-                if (m2) {
-                    const uint32_t L = __ffs(m2) - 1;
-                    excl += warp_sum_t<unsigned long long>(lane <= L ? val : 0ull);
-                    break;
-                }
-                excl += warp_sum_t<unsigned long long>(val);
-                pos -= 32;
-            }
-            if (lane == 0) st_volatile_u64(st.status + tile, ((excl + (unsigned long long)tot) << 2) | 2ull);
-        }
-        if (lane == 0) sm_prefix = (T)excl;
+        const unsigned long long excl = lb_lookback(st, tile, (unsigned long long)tot);
+        if (threadIdx.x == 0) sm_prefix = (T)excl;
     }
     __syncthreads();
     T run = sm_prefix + ex;

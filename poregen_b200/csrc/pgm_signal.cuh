@@ -8,6 +8,7 @@
 // values, each evaluated with the reference's own double expression, so ties and rounding agree.
 #pragma once
 #include "pgm_device.cuh"
+#include "pgm_sort.cuh"
 
 #define SIG_SMEM_BINS 2048      // in-range code span k_stats handles (per-warp shared-memory histogram)
 #define STATS_SMEM_BINS 8192    // k_stats_wide: shared memory up to here, then global scratch
@@ -407,8 +408,8 @@ __global__ void __launch_bounds__(STATS_WARPS * 32) k_stats(DevOpts o, DevBatch 
 // one event's samples: raw -> pA (0.0 when out of range) -> (x - med) / mad (gmove.cpp:611-613).
 // Output offsets of consecutive events are consecutive, so the stores of a warp form one contiguous stream.
 struct GatherIO {
-    const uint4 *sel;                       // [E_sel] selected events {src lo, src hi, len, record}, grouped by slot; src = index in raw[] of the first sample
-    const uint64_t *sel_off;                // [E_sel+1]
+    const uint4 *sel;                       // [E_sel] selected events (EvRow, pgm_sort.cuh), grouped by slot
+    const uint64_t *sel_off;                // [E_sel+1] sample offset of every selected event (k_scan_sel)
     const uint32_t *n_sel;
     const ReadCal *cal;
     double *samples;
@@ -450,6 +451,10 @@ __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shf
 #ifndef GATHER_UNROLL
 #define GATHER_UNROLL 3         // group iterations in flight per lane: the dependent shared-memory loads of one hide behind the other
 #endif
+#ifndef GATHER_G
+#define GATHER_G 4              // output positions per group (one lane, one step): 4 or 8 (8 measured slower on C3: 666 vs 637 us per block)
+#endif
+#define GATHER_G_SHIFT (GATHER_G == 8 ? 3 : 2)
 #define GATHER_MAP 512
 #define GATHER_CH 10                        // 16-byte chunks staged per event at most: covers 73 samples at the worst alignment
 #define GATHER_CAP_CH 160                   // chunks of staging per batch of 32 events, packed end to end (5 per event on average)
@@ -471,6 +476,8 @@ struct GatherStage {
     long long base[32];       // raw[] index of the event's first sample
     uint8_t map[GATHER_MAP];
 };
+
+#define GATHER_SMEM (sizeof(GatherStage) * GATHER_WARPS)
 
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
@@ -513,9 +520,9 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
         const uint32_t rd = ok1 ? row1.w : 0u;  // level 1 arrived an iteration ago
         const pgm_read *rp = b.reads + rd;
         const ReadCal *rc = io.cal + rd;
-        ln2 = ok1 ? row1.z : 0u;
+        ln2 = ok1 ? ev_row_len(row1) : 0u;
         off2 = off1;
-        src2 = ((uint64_t)row1.y << 32) | row1.x;
+        src2 = ev_row_src(row1);
         if (off2 + ln2 > io.samples_cap) ln2 = 0;
         offset2 = rp->offset;
         clo2 = rc->clo; chi2 = rc->chi; scale2 = rc->scale;
@@ -543,14 +550,14 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
     level2(0);
     if (q0 + stride < n) level1(q0 + stride);
     for (uint32_t buf = 0;; buf ^= 1) {
-        // ---- publish the batch. The unit of the walk is a GROUP: four consecutive output positions of ONE event that
-        // start on an even index of samples[] (so a group is two 16-byte stores); an event that starts on an odd index
+        // ---- publish the batch. The unit of the walk is a GROUP: GATHER_G consecutive output positions of ONE event that
+        // start on an even index of samples[] (so a group is GATHER_G / 2 16-byte stores); an event that starts on an odd index
         // has an empty first slot. Lane j owns event j: it counts the event's groups, a warp scan numbers them.
         const uint32_t ln = ln2;
         const uint64_t out0 = __shfl_sync(PGM_FULL, (unsigned long long)off2, 0);        // first output position of the batch
         const uint32_t rel = (uint32_t)(off2 - out0);
         const uint32_t par = (uint32_t)(off2 & 1);
-        const uint32_t ng = ln ? (ln + par + 3) >> 2 : 0u;
+        const uint32_t ng = ln ? (ln + par + (GATHER_G - 1)) >> GATHER_G_SHIFT : 0u;
         const uint32_t ginc = warp_incl_scan_add(ng);
         const uint32_t gstart = ginc - ng;
         const uint32_t total = __shfl_sync(PGM_FULL, ginc, 31);      // groups in the batch
@@ -586,35 +593,39 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
                 for (uint32_t g = w0 + lane; g < wend; g += 32) {
                     const uint32_t e = S.map[g - w0];
                     const uint4 *ep = reinterpret_cast<const uint4 *>(&S.ev[e]);
-                    const uint4 a0 = ep[0], a1 = ep[1], a2 = ep[2], a3 = ep[3];
+                    // the event's parameter record: 64 bytes, of which a pass without Med-MAD needs 48 (three 16-byte loads)
+                    const uint4 a0 = ep[0], a2 = ep[2], a3 = ep[3];
                     SigConv cv;
                     cv.scaling = SCALING;
                     cv.offset = __hiloint2double((int)a0.y, (int)a0.x); cv.scale = __hiloint2double((int)a0.w, (int)a0.z);
-                    cv.med = __hiloint2double((int)a1.y, (int)a1.x); cv.mad = __hiloint2double((int)a1.w, (int)a1.z);
-                    cv.rcp = __hiloint2double((int)a2.y, (int)a2.x); cv.clo = (int)a2.z; cv.nbins = a2.w;
-                    cv.fast_div = ((a3.w >> 19) & 1u) != 0;
+                    cv.clo = (int)a2.z; cv.nbins = a2.w;
+                    cv.med = 0.0; cv.mad = 1.0; cv.rcp = 1.0; cv.fast_div = true;
+                    if (SCALING) {
+                        const uint4 a1 = ep[1];
+                        cv.med = __hiloint2double((int)a1.y, (int)a1.x); cv.mad = __hiloint2double((int)a1.w, (int)a1.z);
+                        cv.rcp = __hiloint2double((int)a2.y, (int)a2.x);
+                        cv.fast_div = ((a3.w >> 19) & 1u) != 0;
+                    }
                     const uint32_t len = a3.y;
                     const int sidx = (int)(a3.w & 0x7ffu);
                     const uint32_t nst = (a3.w >> 11) & 0xffu;
-                    const int t0 = (int)(4u * (g - a3.x)) - (int)((a3.w >> 20) & 1u);   // event sample in the group's first slot
-                    double o4[4];
-                    bool ok[4];
+                    const int t0 = (int)((uint32_t)GATHER_G * (g - a3.x)) - (int)((a3.w >> 20) & 1u);   // event sample in the group's first slot
+                    double o4[GATHER_G];
+                    bool ok[GATHER_G];
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
+                    for (int i = 0; i < GATHER_G; i++) {
                         ok[i] = (uint32_t)(t0 + i) < len;
                         const uint32_t t = ok[i] ? (uint32_t)(t0 + i) : 0u;
                         o4[i] = cv(fetch(e, sidx, nst, t));
                     }
                     double *dst = io.samples + out0 + a3.z + (long long)t0;
-                    if (ok[0] && ok[1]) *reinterpret_cast<double2 *>(dst) = make_double2(o4[0], o4[1]);
-                    else {
-                        if (ok[0]) dst[0] = o4[0];
-                        if (ok[1]) dst[1] = o4[1];
-                    }
-                    if (ok[2] && ok[3]) *reinterpret_cast<double2 *>(dst + 2) = make_double2(o4[2], o4[3]);
-                    else {
-                        if (ok[2]) dst[2] = o4[2];
-                        if (ok[3]) dst[3] = o4[3];
+#pragma unroll
+                    for (int i = 0; i < GATHER_G; i += 2) {
+                        if (ok[i] && ok[i + 1]) *reinterpret_cast<double2 *>(dst + i) = make_double2(o4[i], o4[i + 1]);
+                        else {
+                            if (ok[i]) dst[i] = o4[i];
+                            if (ok[i + 1]) dst[i + 1] = o4[i + 1];
+                        }
                     }
                 }
             };

@@ -5,14 +5,15 @@
 // order the reference would have appended to dump/<kmer> (reference gmove.cpp:650-652, 680-685), and
 // rank-in-bucket < remaining quota == "emitted".
 //
-// An event travels as ONE 16-byte row {slot, start, len, record}: a scatter is one 16-byte store per event, and two
-// events of a bucket complete a 32-byte sector (the 4-byte structure-of-arrays stores of round 1 left partial sectors
-// that DRAM had to read back: profiles/ncu_r01_count_sort.md).
+// An event travels as ONE 16-byte row (EvRow below): a scatter is one 16-byte store per event, and two events of a
+// bucket complete a 32-byte sector (the 4-byte structure-of-arrays stores of round 1 left partial sectors that DRAM had
+// to read back: profiles/ncu_r01_count_sort.md). The row already holds what the gather needs (the event's first sample
+// as an index into raw[], its length, its record), so the selected rows ARE the selection: nothing is looked up again.
 //
 // The decoders leave every record's passing events in a per-record temporary (they cannot know the record's place in
 // the batch before every earlier record is done). Nothing copies them into a dense array: the kernels here walk the
 // dense (record, position) order in tiles of SORT_TILE events and fetch the rows of a tile straight from the
-// temporaries (EvSource: dense index -> record by a search in ev_base[], restricted to the few records of the tile).
+// temporaries (EvSource: dense index -> record; the handful of records a tile touches sit in shared memory).
 //
 //   tables up to 2^SORT_MAX_BITS slots (k <= 5):   k_tile_hist -> k_scan_hist -> k_rank                (one digit)
 //   larger tables (k = 9: 262,144 slots):          k_tile_hist -> k_scan_hist -> k_msd_scatter -> k_msd_rank
@@ -33,6 +34,16 @@
 #define MSD_MAX_LO_BITS 11      // k_msd_rank: slots per high-digit bucket (shared-memory counters)
 
 // ------------------------------------------------------------------------------------------------
+// EvRow, the 16 bytes of an event:  x = slot,  y = src bits 0-31,  z = src bits 32-39 << 24 | len,  w = record.
+// src = index in raw[] of the event's first sample (after --margin), len = its samples (< 2^24: longer events make the
+// decoders flag the batch), record = index of its alignment record in the batch.
+#define EV_MAX_LEN 0x00ffffffu
+__device__ __forceinline__ uint4 ev_row(uint32_t slot, unsigned long long src, uint32_t len, uint32_t rec) {
+    return make_uint4(slot, (uint32_t)src, ((uint32_t)(src >> 32) << 24) | len, rec);
+}
+__device__ __forceinline__ unsigned long long ev_row_src(const uint4 &r) { return ((unsigned long long)(r.z >> 24) << 32) | r.y; }
+__device__ __forceinline__ uint32_t ev_row_len(const uint4 &r) { return r.z & EV_MAX_LEN; }
+
 // Where the passing events are: record r's events, in position order, at rows_tmp[tmp_base(r) + j], j < n_pass[r];
 // dense index of the first one = ev_base[r] (exclusive scan of n_pass, k_scan_records).
 struct EvSource {
@@ -71,36 +82,60 @@ __device__ __forceinline__ uint32_t ev_find_rec_warp(const uint32_t *ev_base, ui
     return lo + __ffs(m) - 1;
 }
 
-// Records of the tile [t0, t1) (t0 < t1 <= n_ev) -> sm_rec[0] = first, sm_rec[1] = last. Called by all threads; contains a barrier.
-__device__ __forceinline__ void ev_tile_records(const EvSource &s, uint32_t t0, uint32_t t1, uint32_t *sm_rec) {
+// The records of one tile, in shared memory: a tile of long records touches one or two of them, so dense index ->
+// temporary address is a compare against EV_SEGS cached boundaries; tiles that touch more records (short records, or
+// batches where the quota leaves a few events per record) search ev_base[] between the tile's first and last record.
+#define EV_SEGS 4
+struct EvTile {
+    uint32_t r_lo, r_hi;
+    uint32_t seg_start[EV_SEGS];             // dense index of the first event of record r_lo + k (0xffffffff: not cached)
+    long long seg_delta[EV_SEGS];            // temporary address - dense index, for record r_lo + k
+};
+
+// Fills *t for the tile [t0, t1) (t0 < t1 <= n_ev). Called by all threads of the CTA; contains a barrier.
+__device__ __forceinline__ void ev_tile_setup(const EvSource &s, uint32_t t0, uint32_t t1, EvTile *t) {
     if (threadIdx.x < 32) {
         const uint32_t r_lo = ev_find_rec_warp(s.ev_base, 0u, s.n_reads - 1, t0);
         const uint32_t r_hi = ev_find_rec_warp(s.ev_base, r_lo, s.n_reads - 1, t1 - 1);
-        if (threadIdx.x == 0) { sm_rec[0] = r_lo; sm_rec[1] = r_hi; }
+        if (threadIdx.x == 0) { t->r_lo = r_lo; t->r_hi = r_hi; }
+        if (threadIdx.x < EV_SEGS) {
+            const uint32_t r = r_lo + threadIdx.x;
+            uint32_t st = 0xffffffffu;
+            long long dl = 0;
+            if (r <= r_hi) {
+                const uint32_t eb = s.ev_base[r];
+                st = threadIdx.x ? eb : 0u;          // everything below the second record's start belongs to the first
+                dl = (long long)(s.reads[r].align_off >> s.shift) - (long long)eb;
+            }
+            t->seg_start[threadIdx.x] = st; t->seg_delta[threadIdx.x] = dl;
+        }
     }
     __syncthreads();
 }
 
-__device__ __forceinline__ uint4 ev_fetch(const EvSource &s, uint32_t i, uint32_t r_lo, uint32_t r_hi) {
-    const uint32_t r = (r_lo == r_hi) ? r_lo : ev_find_rec(s.ev_base, r_lo, r_hi, i);
-    const size_t t = (size_t)(s.reads[r].align_off >> s.shift) + (i - s.ev_base[r]);
-    return __ldg(s.rows_tmp + t);
+// temporary address of dense event i of the tile
+__device__ __forceinline__ size_t ev_addr(const EvSource &s, const EvTile &t, uint32_t i) {
+    if (t.r_hi - t.r_lo < EV_SEGS) {
+        uint32_t k = 0;
+#pragma unroll
+        for (int q = 1; q < EV_SEGS; q++) k += (i >= t.seg_start[q]) ? 1u : 0u;     // a record without events shares its successor's start: the successor wins
+        return (size_t)((long long)i + t.seg_delta[k]);
+    }
+    const uint32_t r = ev_find_rec(s.ev_base, t.r_lo, t.r_hi, i);
+    return (size_t)(s.reads[r].align_off >> s.shift) + (i - s.ev_base[r]);
 }
-
+__device__ __forceinline__ uint4 ev_fetch(const EvSource &s, const EvTile &t, uint32_t i) { return __ldg(s.rows_tmp + ev_addr(s, t, i)); }
 // slot of dense event i only (the histogram pass needs nothing else)
-__device__ __forceinline__ uint32_t ev_fetch_slot(const EvSource &s, uint32_t i, uint32_t r_lo, uint32_t r_hi) {
-    const uint32_t r = (r_lo == r_hi) ? r_lo : ev_find_rec(s.ev_base, r_lo, r_hi, i);
-    const size_t t = (size_t)(s.reads[r].align_off >> s.shift) + (i - s.ev_base[r]);
-    return __ldg(reinterpret_cast<const uint32_t *>(s.rows_tmp + t));
+__device__ __forceinline__ uint32_t ev_fetch_slot(const EvSource &s, const EvTile &t, uint32_t i) {
+    return __ldg(reinterpret_cast<const uint32_t *>(s.rows_tmp + ev_addr(s, t, i)));
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_tile_hist: per-tile histogram of one digit of the slot, hist[digit * ntiles_cap + tile]. Every used tile writes
-// all its bins (nothing is zeroed beforehand, nothing is atomic in global memory).
-__global__ void __launch_bounds__(PGM_BLOCK) k_tile_hist(EvSource src, const uint32_t *n_ptr, uint32_t shift, uint32_t bits, uint32_t *hist,
-                                                         uint32_t ntiles_cap) {
+// k_tile_hist: per-tile histogram of one digit of the slot, tile-major: hist[tile * bins + digit]. Every used tile
+// writes all its bins (nothing is zeroed beforehand, nothing is atomic in global memory).
+__global__ void __launch_bounds__(PGM_BLOCK) k_tile_hist(EvSource src, const uint32_t *n_ptr, uint32_t shift, uint32_t bits, uint32_t *hist) {
     __shared__ uint32_t sm[1 << MSD_MAX_LO_BITS];
-    __shared__ uint32_t sm_rec[2];
+    __shared__ EvTile sm_tile;
     const uint32_t n = *n_ptr;
     const uint32_t bins = 1u << bits, mask = bins - 1;
     const uint32_t used = (n + SORT_TILE - 1) / SORT_TILE;
@@ -108,13 +143,12 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_tile_hist(EvSource src, const uin
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) sm[i] = 0;
         const uint32_t base = tile * SORT_TILE, end = min(n, base + SORT_TILE);
-        ev_tile_records(src, base, end, sm_rec);
-        const uint32_t r_lo = sm_rec[0], r_hi = sm_rec[1];
+        ev_tile_setup(src, base, end, &sm_tile);
         uint32_t slot[SORT_ITEMS];
 #pragma unroll
         for (int i = 0; i < SORT_ITEMS; i++) {
             const uint32_t idx = base + i * PGM_BLOCK + threadIdx.x;
-            slot[i] = (idx < end) ? ev_fetch_slot(src, idx, r_lo, r_hi) : 0u;
+            slot[i] = (idx < end) ? ev_fetch_slot(src, sm_tile, idx) : 0u;
         }
 #pragma unroll
         for (int i = 0; i < SORT_ITEMS; i++) {
@@ -122,52 +156,47 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_tile_hist(EvSource src, const uin
             if (idx < end) atomicAdd(&sm[(slot[i] >> shift) & mask], 1u);
         }
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) hist[(size_t)i * ntiles_cap + tile] = sm[i];
+        for (uint32_t i = threadIdx.x; i < bins; i += PGM_BLOCK) hist[(size_t)tile * bins + i] = sm[i];
     }
 }
 
 // ------------------------------------------------------------------------------------------------
-// One-launch scan of the digit-major tile histogram hist[bin * ntiles_cap + tile] over the tiles in
-// use (n_events known on the device only), in place.
-__global__ void __launch_bounds__(PGM_BLOCK) k_scan_hist(uint32_t *hist, const uint32_t *n_ptr, uint32_t bins, uint32_t ntiles_cap,
-                                                         LbBuf st) {
+// One-launch scan of the tile histogram in digit-major ORDER (all tiles of digit 0, then digit 1, ...) over the tiles in
+// use (n_events known on the device only), in place. The storage is tile-major (hist[tile * bins + digit]): the tile
+// kernels read and write their bins coalesced; this kernel moves 4 bytes per 32-byte sector, on a table of a few megabytes.
+__global__ void __launch_bounds__(PGM_BLOCK) k_scan_hist(uint32_t *hist, const uint32_t *n_ptr, uint32_t bins, LbBuf st) {
     const uint32_t n_ev = *n_ptr;
     const uint32_t ntu = (n_ev + SORT_TILE - 1) / SORT_TILE;
     const uint64_t n = (uint64_t)bins * ntu;
-    auto addr = [&](uint64_t e) { return (size_t)(e / ntu) * ntiles_cap + (size_t)(e % ntu); };
+    auto addr = [&](uint64_t e) { return (size_t)(e % ntu) * bins + (size_t)(e / ntu); };
     lb_scan<uint32_t>(n, st, [&](uint64_t e) { return hist[addr(e)]; },
                       [&](uint64_t e, uint32_t ex, uint32_t) { hist[addr(e)] = ex; }, [](uint32_t) {});
 }
 
 // ------------------------------------------------------------------------------------------------
-// Stable rank of every item of a tile inside its digit: the tile's items are taken in (warp, round, lane) order,
-// 512-thread CTAs (a tile's 4096 events are 8 rounds per warp; the rounds of a warp are serial: every one reads the
-// counters the previous one wrote). On return wcount[w][d] holds the items of digit d in warps < w (exclusive
-// over warps) and lrank[rd] the item's rank among the items of its digit in its own warp.
-#define RANK_BLOCK 512
-#define RANK_WARPS (RANK_BLOCK / 32)
-#define RANK_ITEMS (SORT_TILE / RANK_BLOCK)
-
-template <typename Counter>
-__device__ __forceinline__ void tile_rank(const uint32_t (&dig)[RANK_ITEMS], uint32_t nvalid_warp, uint32_t bins, Counter *wcount /* [RANK_WARPS][bins] */,
-                                          uint32_t (&lrank)[RANK_ITEMS]) {
+// Stable rank of every item of a tile inside its digit: the tile's items are taken in (warp, round, lane) order: warp w
+// owns the 32 * ITEMS consecutive items from w * 32 * ITEMS on, ITEMS rounds of 32 (the rounds of a warp are serial: every
+// one reads the counters the previous one wrote). On return wcount[w][d] holds the warp's items of digit d and lrank[rd]
+// the item's rank among the items of its digit in its own warp.
+template <int ITEMS>
+__device__ __forceinline__ void tile_rank(const uint32_t (&dig)[ITEMS], uint32_t nvalid_warp, uint32_t bins, uint32_t *wcount, uint32_t (&lrank)[ITEMS]) {
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    Counter *mine = wcount + (size_t)w * bins;
-    uint32_t peers[RANK_ITEMS];
+    uint32_t *mine = wcount + (size_t)w * bins;
+    uint32_t peers[ITEMS];
     // the matches of all rounds first (they depend on nothing but the digits), then the serial counter updates
 #pragma unroll
-    for (int rd = 0; rd < RANK_ITEMS; rd++) {
+    for (int rd = 0; rd < ITEMS; rd++) {
         const bool valid = (uint32_t)(rd * 32) + lane < nvalid_warp;
         peers[rd] = __match_any_sync(0xffffffffu, valid ? dig[rd] : 0xffffffffu);   // invalid lanes form their own group
     }
 #pragma unroll
-    for (int rd = 0; rd < RANK_ITEMS; rd++) {
+    for (int rd = 0; rd < ITEMS; rd++) {
         const bool valid = (uint32_t)(rd * 32) + lane < nvalid_warp;
         const uint32_t leader = __ffs(peers[rd]) - 1;
         uint32_t old = 0;
         if (valid && lane == leader) {
             old = mine[dig[rd]];
-            mine[dig[rd]] = (Counter)(old + __popc(peers[rd]));
+            mine[dig[rd]] = old + __popc(peers[rd]);
         }
         old = __shfl_sync(0xffffffffu, old, leader);
         lrank[rd] = old + __popc(peers[rd] & ((1u << lane) - 1));
@@ -180,27 +209,25 @@ __device__ __forceinline__ void tile_rank(const uint32_t (&dig)[RANK_ITEMS], uin
 // the position the stable sort would give it (so its rank inside its slot), decides "emitted" =
 // rank < keep[slot] (reference gmove.cpp:650-652, 680-685) and writes the event's row straight to its
 // place in the slot-grouped output; no sorted intermediate is materialised.
+// 512-thread CTAs: a tile's 4096 events are 8 rounds per warp instead of 16, and the 830 tiles of C2 make 2.8 waves of
+// half-length tiles instead of 1.4 of full ones.
+#define RANK_BLOCK 512
+#define RANK_WARPS (RANK_BLOCK / 32)
+#define RANK_ITEMS (SORT_TILE / RANK_BLOCK)
 struct RankIO {
     const uint32_t *n_events;
     EvSource src;
     const uint32_t *hist_scanned;           // scanned tile histogram of the digit
-    uint32_t ntiles_cap, bits;
+    uint32_t bits;
     const uint32_t *bucket_base, *keep, *sel_base;
-    uint4 *sel;                             // [E_sel] selected events grouped by slot, as SelRow
-    const unsigned long long *rec_src0;     // [R] index in raw[] of the record's sample 0 (k_read_prep)
+    uint4 *sel;                             // [E_sel] selected events (EvRow) grouped by slot
     uint8_t *read_has_sel;                  // [R] or null (only the Med-MAD pass needs it)
 };
-
-// A selected event as the gather wants it: {src lo, src hi, len, record}, src = index in raw[] of its first sample.
-__device__ __forceinline__ uint4 sel_row(const uint4 &row, const unsigned long long *rec_src0) {
-    const unsigned long long src = rec_src0[row.w] + row.y;
-    return make_uint4((uint32_t)src, (uint32_t)(src >> 32), row.z, row.w);
-}
 
 #define RANK_SMEM ((RANK_WARPS + 1) * SORT_MAX_BINS * 4)
 __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
     extern __shared__ __align__(16) uint32_t sm_rank[];
-    __shared__ uint32_t sm_rec[2];
+    __shared__ EvTile sm_tile;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.bits, mask = bins - 1;
     uint32_t *wcount = sm_rank;                         // [RANK_WARPS][bins]
@@ -210,10 +237,9 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
     for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < RANK_WARPS * bins; i += RANK_BLOCK) wcount[i] = 0;
-        for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)i * io.ntiles_cap + tile];
+        for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)tile * bins + i];
         const uint32_t base = tile * SORT_TILE, end = min(n, base + SORT_TILE);
-        ev_tile_records(io.src, base, end, sm_rec);
-        const uint32_t r_lo = sm_rec[0], r_hi = sm_rec[1];
+        ev_tile_setup(io.src, base, end, &sm_tile);
         const uint32_t wbase = base + w * (32 * RANK_ITEMS);
         const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * RANK_ITEMS)) : 0u;
         uint4 row[RANK_ITEMS];
@@ -221,10 +247,10 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
 #pragma unroll
         for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
-            row[rd] = (idx < end) ? ev_fetch(io.src, idx, r_lo, r_hi) : make_uint4(0, 0, 0, 0);
+            row[rd] = (idx < end) ? ev_fetch(io.src, sm_tile, idx) : make_uint4(0, 0, 0, 0);
             dig[rd] = row[rd].x & mask;
         }
-        tile_rank<uint32_t>(dig, nvw, bins, wcount, lrank);
+        tile_rank<RANK_ITEMS>(dig, nvw, bins, wcount, lrank);
         __syncthreads();
         for (uint32_t b = threadIdx.x; b < bins; b += RANK_BLOCK) {   // exclusive scan over warps, per digit
             uint32_t run = 0;
@@ -244,7 +270,7 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
                 const uint32_t pos = goff[dig[rd]] + wcount[w * bins + dig[rd]] + lrank[rd];
                 const uint32_t rank = pos - io.bucket_base[slot];
                 if (rank < io.keep[slot]) {
-                    io.sel[io.sel_base[slot] + rank] = sel_row(row[rd], io.rec_src0);
+                    io.sel[io.sel_base[slot] + rank] = row[rd];
                     if (io.read_has_sel) io.read_has_sel[row[rd].w] = 1;
                 }
             }
@@ -253,32 +279,44 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_msd_scatter (tables of two digits, first pass): stable split of the batch by the HIGH digit of the slot.
+// The two-digit kernels. k_msd_scatter works on the histogram's tiles (SORT_TILE events, 512 threads x 8 rounds like
+// k_rank). k_msd_rank is free to pick its own tile (MSD_BLOCK threads x 8 rounds); measured on a C3 block (13 M events,
+// whole sort stage): 512 threads 515 us, 128 threads 528 us, 256 threads 573 us.
+#ifndef MSD_BLOCK
+#define MSD_BLOCK 512
+#endif
+#ifndef MSD_MIN_CTAS
+#define MSD_MIN_CTAS 2
+#endif
+#define MSD_WARPS (MSD_BLOCK / 32)
+#define MSD_ITEMS 8
+#define MSD_TILE (MSD_BLOCK * MSD_ITEMS)
+
+// k_msd_scatter (first pass): stable split of the batch by the HIGH digit of the slot.
 // rows_out[pos], pos = (events of lower high digits) + (events of the same high digit in earlier tiles) + rank in tile.
 struct MsdScatterIO {
     const uint32_t *n_events;
     EvSource src;
     const uint32_t *hist_scanned;
-    uint32_t ntiles_cap, shift, bits;
+    uint32_t shift, bits;
     uint4 *rows_out;
 };
 
 __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) {
     extern __shared__ __align__(16) uint32_t sm_rank[];
-    __shared__ uint32_t sm_rec[2];
+    __shared__ EvTile sm_tile;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.bits;
-    uint32_t *wcount = sm_rank;
-    uint32_t *goff = sm_rank + RANK_WARPS * bins;
+    uint32_t *wcount = sm_rank;                          // [RANK_WARPS][bins]
+    uint32_t *goff = sm_rank + RANK_WARPS * bins;         // [bins]
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t used_tiles = (n + SORT_TILE - 1) / SORT_TILE;
     for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < RANK_WARPS * bins; i += RANK_BLOCK) wcount[i] = 0;
-        for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)i * io.ntiles_cap + tile];
+        for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)tile * bins + i];
         const uint32_t base = tile * SORT_TILE, end = min(n, base + SORT_TILE);
-        ev_tile_records(io.src, base, end, sm_rec);
-        const uint32_t r_lo = sm_rec[0], r_hi = sm_rec[1];
+        ev_tile_setup(io.src, base, end, &sm_tile);
         const uint32_t wbase = base + w * (32 * RANK_ITEMS);
         const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * RANK_ITEMS)) : 0u;
         uint4 row[RANK_ITEMS];
@@ -286,10 +324,10 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
 #pragma unroll
         for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
-            row[rd] = (idx < end) ? ev_fetch(io.src, idx, r_lo, r_hi) : make_uint4(0, 0, 0, 0);
+            row[rd] = (idx < end) ? ev_fetch(io.src, sm_tile, idx) : make_uint4(0, 0, 0, 0);
             dig[rd] = (row[rd].x >> io.shift) & (bins - 1);
         }
-        tile_rank<uint32_t>(dig, nvw, bins, wcount, lrank);
+        tile_rank<RANK_ITEMS>(dig, nvw, bins, wcount, lrank);
         __syncthreads();
         for (uint32_t b = threadIdx.x; b < bins; b += RANK_BLOCK) {
             uint32_t run = goff[b];
@@ -308,6 +346,7 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
         }
     }
 }
+#define MSD_SCATTER_SMEM(bits) ((size_t)(RANK_WARPS + 1) * (1u << (bits)) * 4)
 
 // ------------------------------------------------------------------------------------------------
 // k_msd_rank (second pass): one CTA per high-digit bucket at a time. The bucket is the contiguous range
@@ -317,22 +356,21 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
 struct MsdRankIO {
     const uint32_t *n_events;
     const uint4 *rows_in;
-    const uint32_t *hist_scanned;           // first pass's scanned histogram: [hi_bins][ntiles_cap]
-    uint32_t ntiles_cap, hi_bits, lo_bits, n_slots;
+    const uint32_t *hist_scanned;           // first pass's scanned histogram (tile-major: tile 0's row holds the bucket starts)
+    uint32_t hi_bits, lo_bits, n_slots;
     const uint32_t *keep, *sel_base;
     uint4 *sel;
-    const unsigned long long *rec_src0;
     uint8_t *read_has_sel;                  // or null
     uint32_t *ticket;                       // bucket hand-out (zeroed per batch)
 };
 
-__global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_rank(MsdRankIO io) {
+__global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO io) {
     extern __shared__ __align__(16) uint32_t sm_rank[];
     __shared__ uint32_t sm_bucket;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.lo_bits, mask = bins - 1;
-    uint32_t *wcount = sm_rank;                          // [RANK_WARPS][bins]
-    uint32_t *cnt = sm_rank + RANK_WARPS * bins;         // [bins] events of the slot so far
+    uint32_t *wcount = sm_rank;                          // [MSD_WARPS][bins]
+    uint32_t *cnt = sm_rank + MSD_WARPS * bins;          // [bins] events of the slot so far
     uint32_t *keep_s = cnt + bins, *selb_s = keep_s + bins;
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t n_buckets = (io.n_slots + bins - 1) >> io.lo_bits;
@@ -343,37 +381,38 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_rank(MsdRankIO io) {
         __syncthreads();
         const uint32_t h = sm_bucket;
         if (h >= n_buckets) break;
-        const uint32_t start = io.hist_scanned[(size_t)h * io.ntiles_cap];
-        const uint32_t stop = (h + 1 < (1u << io.hi_bits)) ? io.hist_scanned[(size_t)(h + 1) * io.ntiles_cap] : n;
+        const uint32_t start = io.hist_scanned[h];
+        const uint32_t stop = (h + 1 < (1u << io.hi_bits)) ? io.hist_scanned[h + 1] : n;
         if (start >= stop) continue;
         const uint32_t slot0 = h << io.lo_bits;
-        for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) {
+        for (uint32_t i = threadIdx.x; i < bins; i += MSD_BLOCK) {
             const uint32_t s = slot0 + i;
             cnt[i] = 0;
             keep_s[i] = (s < io.n_slots) ? io.keep[s] : 0u;
             selb_s[i] = (s < io.n_slots) ? io.sel_base[s] : 0u;
         }
-        for (uint32_t base = start; base < stop; base += SORT_TILE) {
+        for (uint32_t base = start; base < stop; base += MSD_TILE) {
             __syncthreads();
-            for (uint32_t i = threadIdx.x; i < RANK_WARPS * bins; i += RANK_BLOCK) wcount[i] = 0;
-            __syncthreads();
-            const uint32_t end = min(stop, base + SORT_TILE);
-            const uint32_t wbase = base + w * (32 * RANK_ITEMS);
-            const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * RANK_ITEMS)) : 0u;
-            uint4 row[RANK_ITEMS];
-            uint32_t dig[RANK_ITEMS], lrank[RANK_ITEMS];
+            for (uint32_t i = threadIdx.x; i < MSD_WARPS * bins; i += MSD_BLOCK) wcount[i] = 0;
+            const uint32_t end = min(stop, base + MSD_TILE);
+            const uint32_t wbase = base + w * (32 * MSD_ITEMS);
+            const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * MSD_ITEMS)) : 0u;
+            uint4 row[MSD_ITEMS];
+            uint32_t dig[MSD_ITEMS], lrank[MSD_ITEMS];
 #pragma unroll
-            for (int rd = 0; rd < RANK_ITEMS; rd++) {
+            for (int rd = 0; rd < MSD_ITEMS; rd++) {   // the loads are on their way while the counters are cleared
                 const uint32_t idx = wbase + rd * 32 + lane;
                 row[rd] = (idx < end) ? __ldg(io.rows_in + idx) : make_uint4(0, 0, 0, 0);
-                dig[rd] = row[rd].x & mask;
             }
-            tile_rank<uint32_t>(dig, nvw, bins, wcount, lrank);
             __syncthreads();
-            for (uint32_t b = threadIdx.x; b < bins; b += RANK_BLOCK) {   // running count of the slot, then exclusive over warps
+#pragma unroll
+            for (int rd = 0; rd < MSD_ITEMS; rd++) dig[rd] = row[rd].x & mask;
+            tile_rank<MSD_ITEMS>(dig, nvw, bins, wcount, lrank);
+            __syncthreads();
+            for (uint32_t b = threadIdx.x; b < bins; b += MSD_BLOCK) {   // running count of the slot, then exclusive over warps
                 uint32_t run = cnt[b];
 #pragma unroll
-                for (int ww = 0; ww < RANK_WARPS; ww++) {
+                for (int ww = 0; ww < MSD_WARPS; ww++) {
                     const uint32_t t = wcount[ww * bins + b];
                     wcount[ww * bins + b] = run;
                     run += t;
@@ -382,13 +421,13 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_rank(MsdRankIO io) {
             }
             __syncthreads();
 #pragma unroll
-            for (int rd = 0; rd < RANK_ITEMS; rd++) {
+            for (int rd = 0; rd < MSD_ITEMS; rd++) {
                 const uint32_t idx = wbase + rd * 32 + lane;
                 if (idx < end) {
                     const uint32_t d = dig[rd];
                     const uint32_t rank = wcount[w * bins + d] + lrank[rd];
                     if (rank < keep_s[d]) {
-                        io.sel[selb_s[d] + rank] = sel_row(row[rd], io.rec_src0);
+                        io.sel[selb_s[d] + rank] = row[rd];
                         if (io.read_has_sel) io.read_has_sel[row[rd].w] = 1;
                     }
                 }
@@ -396,15 +435,15 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_rank(MsdRankIO io) {
         }
     }
 }
-#define MSD_RANK_SMEM(lo_bits) ((size_t)(RANK_WARPS + 3) * (1u << (lo_bits)) * 4)
+#define MSD_RANK_SMEM(lo_bits) ((size_t)(MSD_WARPS + 3) * (1u << (lo_bits)) * 4)
 
 // Selected rows -> the structure-of-arrays form of pgm_result (ev_start / ev_len / ev_read), for callers that download them.
+// ev_start is relative to the record's first sample after trim (rec_src0, k_read_prep).
 __global__ void __launch_bounds__(PGM_BLOCK) k_unpack_sel(const uint4 *sel, const uint32_t *n_sel_ptr, const unsigned long long *rec_src0, uint32_t *ev_start,
                                                           uint32_t *ev_len, uint32_t *ev_read) {
     const uint32_t n = *n_sel_ptr;
     for (uint32_t i = blockIdx.x * PGM_BLOCK + threadIdx.x; i < n; i += gridDim.x * PGM_BLOCK) {
         const uint4 r = sel[i];
-        const unsigned long long src = ((unsigned long long)r.y << 32) | r.x;
-        ev_start[i] = (uint32_t)(src - rec_src0[r.w]); ev_len[i] = r.z; ev_read[i] = r.w;
+        ev_start[i] = (uint32_t)(ev_row_src(r) - rec_src0[r.w]); ev_len[i] = ev_row_len(r); ev_read[i] = r.w;
     }
 }

@@ -178,7 +178,7 @@ __device__ __forceinline__ void fmt8_write(const Fmt8 &f, double x, char term, c
 // Kernels. One warp per selected event (grid-stride), lanes over its samples.
 struct TextIO {
     const double *samples;
-    const uint4 *sel;            // selected events; .z = samples of the event
+    const uint4 *sel;            // selected events (EvRow): .z & 0xffffff = samples of the event
     const unsigned long long *sel_off;
     const uint32_t *n_sel;
     uint32_t *ev_tlen;                // [E_sel] characters of the event
@@ -198,7 +198,7 @@ __device__ __forceinline__ TextAhead text_row(const TextIO &io, uint32_t q, uint
     TextAhead r;
     r.q = q; r.ln = 0; r.off = 0; r.toff = 0;
     if (q < n) {
-        r.ln = io.sel[q].z; r.off = io.sel_off[q];
+        r.ln = io.sel[q].z & 0x00ffffffu; r.off = io.sel_off[q];
         if (WITH_TOFF) r.toff = io.ev_toff[q];
     }
     return r;

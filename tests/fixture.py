@@ -80,3 +80,39 @@ def FIXTURE_CASES():
                     o.resolve_range()
                     out.append((f"{form}_{lname.split('.')[0]}_pm{margin}_sc{sc}", form, o, lname))
     return out
+
+
+def write_fixture_files(d: str) -> dict:
+    """The reference fixture test/data/raw/gmove/single_read re-created from the committed arrays (same content for
+    gmove, not the same bytes): reads.slow5, guppy_move (TSV), guppy_move.paf, guppy_move.sam, guppy_move.bam,
+    read_0.fastq(+.fai), kmer_file.txt, single_kmer_file.txt. Returns {name: path}."""
+    from poregen_b200 import synth
+    os.makedirs(d, exist_ok=True)
+    fx = np.load(os.path.join(HERE, "golden", "single_read.npz"))
+    rid = str(fx["read_id"])
+    p = {n: os.path.join(d, n) for n in ("reads.slow5", "guppy_move", "guppy_move.paf", "guppy_move.sam", "guppy_move.bam",
+                                          "read_0.fastq", "kmer_file.txt", "single_kmer_file.txt")}
+    tsv = fixture_batch("tsv", 6)
+    synth.write_slow5(tsv, p["reads.slow5"])
+    with open(p["guppy_move"], "w") as f:
+        f.write(f"{rid}\t{int(fx['tsv_fastq_len'])}\t{str(fx['tsv_seq'])}\t{int(fx['tsv_stride'])}\t{str(fx['tsv_moves'])}\t"
+                f"{int(fx['tsv_signal_len'])}\t{int(fx['tsv_trim'])}\n")
+    seq = str(fx["fastq_seq"])
+    n = int(fx["raw"].size)
+    with open(p["guppy_move.paf"], "w") as f:
+        ts, te = int(fx["paf_tstart"]), int(fx["paf_tend"])
+        f.write(f"{rid}\t{n}\t{int(fx['paf_qstart'])}\t{n}\t+\t{rid}\t{len(seq)}\t{ts}\t{te}\t{abs(te - ts)}\t{abs(te - ts)}\t0\t"
+                f"sc:f:1.000000\tsh:f:0.000000\tss:Z:{str(fx['paf_ss'])}\n")
+    hdr = f"@{rid}\n"
+    with open(p["read_0.fastq"], "w") as f:
+        f.write(hdr + seq + "\n+\n" + "I" * len(seq) + "\n")
+    with open(p["read_0.fastq"] + ".fai", "w") as f:
+        f.write(f"{rid}\t{len(seq)}\t{len(hdr)}\t{len(seq)}\t{len(seq) + 1}\t{len(hdr) + len(seq) + 3}\n")
+    sam = fixture_batch("sam", 6)
+    fl = synth.write_alignment(sam, os.path.join(d, "_sam"))
+    os.replace(fl["align"], p["guppy_move.sam"])
+    synth.write_bam(sam, p["guppy_move.bam"])
+    for name, lst in _kmer_lists().items():
+        with open(os.path.join(d, name), "w") as f:
+            f.write("".join(k + "\n" for k in lst))
+    return p
