@@ -176,6 +176,23 @@ int pgm_sync(pgm_ctx *ctx);
  * emitted, so pgm_download can still follow. For callers that keep the result in HBM (benchmarks, K7). */
 int pgm_summary(pgm_ctx *ctx, pgm_result *out);
 
+/* Batches in flight (pgm_submit / pgm_wait). The reference's loop handles one record after the other; a host that
+ * streams a file wants batch j+1 on its way to the device, and its kernels running, while batch j's dump text travels back.
+ * pgm_submit queues one whole pass (upload or svb upload when `svb` is not NULL, count, emit) of the NEXT batch in alignment-
+ * file order and returns at once; at most two batches are in flight. pgm_wait(batch_id) blocks until that batch is done and
+ * hands out its result like pgm_download; batches are waited for in submission order. The per-k-mer totals are carried from
+ * batch to batch on the device (batch j+1's decoder waits for batch j's quota kernel, nothing else is serialised), so the
+ * output is the reference's single loop. The caller's (pinned) input buffers must stay untouched until pgm_wait returns for
+ * that batch; a result stays valid until the second pgm_submit after it. Not combinable with pgm_model_begin or the
+ * multi-GPU exchange (use the split-phase calls on sibling contexts for those). */
+int pgm_submit(pgm_ctx *ctx, const pgm_batch *host_batch, const struct pgm_svb *svb, uint64_t *batch_id);
+int pgm_wait(pgm_ctx *ctx, uint64_t batch_id, pgm_result *out);
+/* A sibling of `parent`: same options and device, its own stream (NULL: a private one), batch buffers and results, and the
+ * SAME per-k-mer totals. Split-phase calls on siblings may be interleaved freely as long as the batches are counted in
+ * alignment-file order: a sibling's pgm_count waits (on the device) for the quota kernel of the family's previous pgm_emit.
+ * Destroy siblings before the parent. */
+int pgm_create_sibling(pgm_ctx *parent, void *stream, pgm_ctx **out);
+
 /* Compressed signal. Replaces the host-side signal decompression slow5lib runs inside
  * slow5_get / slow5_rec_parse (slow5lib/src/slow5.c:2876-2905 -> slow5_press.c:1085-1130 ptr_depress_svb_zd ->
  * thirdparty/streamvbyte/src/streamvbyte_decode.c:57-104 and streamvbyte_zigzag.c:34-40): record i's stream
@@ -275,6 +292,20 @@ typedef struct pgm_model_row {
 #define PGM_MODEL_CLAMPED 8u    /* stddev was above stddev_limit                                     */
 int pgm_model_begin(pgm_ctx *ctx);
 int pgm_model_finalize(pgm_ctx *ctx, double stddev_limit, const pgm_model_row **rows_out);
+/* Logs the batch pgm_emit just finished without downloading anything (pgm_download logs it too, once). Synchronises. */
+int pgm_model_log(pgm_ctx *ctx);
+/* K7 across GPUs (SURVEY.md 8e "Output merge"; BASELINE.json configs[4]). A rank's log holds one entry per logged batch: the
+ * batch's values (int64 N of the "%.8f" text, device memory) grouped by k-mer in file order, and the table
+ * slot_off[n_slots+1] (host memory) of where each k-mer's values start. The owner of a k-mer range collects, round by
+ * round and rank by rank (= file order), every rank's values of that range - the transport is the caller's (NCCL
+ * all-to-all in poregen_b200.gmove.model_exchange, device-to-device copies in the one-GPU tests) - appends them to a
+ * context of its own with pgm_model_log_append (slot_off_host: full table, zero-length outside the owned range; vals_dev:
+ * the values behind slot_off_host[0] ... slot_off_host[n_slots]) and calls pgm_model_finalize there: the rows of its range
+ * are then what one context that saw every batch would have produced. Event lengths are not exchanged (pgm_model_dwell stays
+ * a one-context call). Pointers handed out stay valid until the next call that logs or clears. */
+int pgm_model_log_size(pgm_ctx *ctx, uint32_t *n_batches);
+int pgm_model_log_entry(pgm_ctx *ctx, uint32_t i, const int64_t **vals_dev, const uint64_t **slot_off_host);
+int pgm_model_log_append(pgm_ctx *ctx, const int64_t *vals_dev, uint64_t n_vals, const uint64_t *slot_off_host);
 
 /* Dwell medians (reference scripts/poregen.sh:33-52, calculate_dwell_times_medians): per dump file, `datamash
  * median` over the comma counts of its ';'-separated fields = (event length - 1) of every event, plus one 0 for the empty field

@@ -301,6 +301,10 @@ done:
     free(seq); free(ev_start); free(ev_end); free(refined); free(indel);
 }
 
+/* Full-size checks compare the doubles, not the text: formatting 6e8 samples with snprintf would take minutes. */
+static int g_want_text = 1;
+void oracle_set_text(int on) { g_want_text = on; }
+
 int oracle_gmove_batch(const pgm_opts *opts, const pgm_batch *batch, uint32_t *totals, oracle_result *out) {
     memset(out, 0, sizeof(*out));
     if (!opts || !batch || !totals || opts->kmer_size < 1 || opts->kmer_size > 15) return PGM_ERR_ARG;
@@ -327,7 +331,7 @@ int oracle_gmove_batch(const pgm_opts *opts, const pgm_batch *batch, uint32_t *t
     out->samples = (double *)malloc((ns ? ns : 1) * sizeof(double));
     out->slot_text_off = (uint64_t *)calloc((size_t)opts->n_slots + 1, sizeof(uint64_t));
     /* text: "%.8f," ... "%.8f;" per event (674-678) */
-    size_t tcap = (size_t)ns * 14 + 16, tl = 0;
+    size_t tcap = g_want_text ? (size_t)ns * 14 + 16 : 16, tl = 0;
     out->text = (char *)malloc(tcap);
     uint64_t pe = 0, ps = 0;
     for (uint32_t s = 0; s < opts->n_slots; s++) {
@@ -337,7 +341,7 @@ int oracle_gmove_batch(const pgm_opts *opts, const pgm_batch *batch, uint32_t *t
         size_t q = 0;
         for (size_t e = 0; e < sb->n; e++) {
             out->ev_len[pe] = sb->len[e]; out->ev_read[pe] = sb->read[e]; out->ev_start[pe] = sb->start[e]; pe++;
-            for (uint32_t t = 0; t < sb->len[e]; t++, q++) {
+            for (uint32_t t = 0; g_want_text && t < sb->len[e]; t++, q++) {
                 if (tl + 400 > tcap) { tcap = tcap * 2 + 1024; out->text = (char *)realloc(out->text, tcap); }
                 tl += (size_t)snprintf(out->text + tl, 390, (t + 1 == sb->len[e]) ? "%.8f;" : "%.8f,", sb->s[q]);
             }

@@ -33,6 +33,7 @@ typedef struct oracle_result {
  * Returns PGM_OK or PGM_ERR_*. */
 int oracle_gmove_batch(const pgm_opts *opts, const pgm_batch *batch, uint32_t *totals, oracle_result *out);
 void oracle_free_result(oracle_result *r);
+void oracle_set_text(int on);   /* 0: leave text empty (slot_text_off all zero) - for full-size comparisons of the doubles */
 
 /* Single pieces, exposed for unit tests. */
 double oracle_median(const double *x, size_t n);              /* gmove.cpp:142-150 */

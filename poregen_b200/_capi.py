@@ -118,7 +118,8 @@ SYMBOLS = [
     "pgm_totals_device", "pgm_set_prior", "pgm_reset", "pgm_stream", "pgm_launch_count",
     "pgm_profile_enable", "pgm_profile_read", "pgm_stage_name", "pgm_debug_format",
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
-    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw", "pgm_model_dwell", "pgm_summary",
+    "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw", "pgm_model_dwell", "pgm_summary", "pgm_submit", "pgm_wait", "pgm_create_sibling",
+    "pgm_model_log", "pgm_model_log_size", "pgm_model_log_entry", "pgm_model_log_append",
 ]
 PGM_N_STAGES = 11
 # pgm_model_row (include/pgm_gmove.h)
@@ -160,6 +161,20 @@ def load() -> C.CDLL:
         getattr(lib, name).restype = C.c_int
     lib.pgm_download.argtypes = [C.c_void_p, P(PgmResult)]
     lib.pgm_download.restype = C.c_int
+    lib.pgm_submit.argtypes = [C.c_void_p, P(PgmBatch), C.c_void_p, P(C.c_uint64)]
+    lib.pgm_submit.restype = C.c_int
+    lib.pgm_wait.argtypes = [C.c_void_p, C.c_uint64, P(PgmResult)]
+    lib.pgm_wait.restype = C.c_int
+    lib.pgm_create_sibling.argtypes = [C.c_void_p, C.c_void_p, P(C.c_void_p)]
+    lib.pgm_create_sibling.restype = C.c_int
+    lib.pgm_model_log.argtypes = [C.c_void_p]
+    lib.pgm_model_log.restype = C.c_int
+    lib.pgm_model_log_size.argtypes = [C.c_void_p, P(C.c_uint32)]
+    lib.pgm_model_log_size.restype = C.c_int
+    lib.pgm_model_log_entry.argtypes = [C.c_void_p, C.c_uint32, P(C.c_void_p), P(C.c_void_p)]
+    lib.pgm_model_log_entry.restype = C.c_int
+    lib.pgm_model_log_append.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.pgm_model_log_append.restype = C.c_int
     lib.pgm_summary.argtypes = [C.c_void_p, P(PgmResult)]
     lib.pgm_summary.restype = C.c_int
     lib.pgm_counts_device.argtypes = [C.c_void_p, P(C.c_void_p)]

@@ -59,14 +59,18 @@ struct pgm_ctx {
 
     // per-context persistent device state
     DBuf lut, consumed, counts, keep, bucket_base, sel_base, gscratch;
+    DBuf totals_snap;                 // kmer_frequency_map right after this context's newest batch (consumed is shared by siblings)
     uint32_t lb_ticket = 0;          // look-back scans launched since the last zeroing (each gets its own ticket + status words)
     size_t lb_used = 0, lb_words = 0;   // status words handed out / available in zbatch
     const uint32_t *user_prior = nullptr, *user_consumed = nullptr;
     const uint32_t *gathered = nullptr;       // pgm_set_gathered
-    // model aggregation log (pgm_model_begin / pgm_model_finalize): one entry per batch
-    struct ModelBatch { long long *vals; unsigned long long *slot_off; std::vector<unsigned long long> h_slot_off;
-                        uint32_t *lens = nullptr, *ev_off = nullptr; std::vector<uint32_t> h_ev_off; };   // event lengths / slot ranges (dwell medians)
-    bool model_on = false;
+    // model aggregation log (pgm_model_begin / pgm_model_finalize): one entry per batch, the values in two growing arenas
+    // (nothing is allocated per batch once the arenas have their size)
+    struct ModelBatch { size_t vals_off, n_vals, lens_off, n_ev; std::vector<unsigned long long> h_slot_off; std::vector<uint32_t> h_ev_off; };
+    DBuf model_vals, model_lens;              // int64 values (N of "%.8f") / uint32 event lengths of every logged batch, back to back
+    size_t model_vals_used = 0, model_lens_used = 0;
+    DBuf model_tab;                           // device copy of one batch's slot table while it is grouped
+    bool model_on = false, model_logged = false;   // model_logged: the emitted batch is in the log already
     std::vector<ModelBatch> model_log;
     DBuf model_bad, model_grouped, model_off, model_dst, model_rows;
     std::vector<pgm_model_row> h_model_rows;
@@ -75,6 +79,13 @@ struct pgm_ctx {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     size_t text_written_cap = 0;              // capacity of `text` when pgm_emit formatted into it (0: it did not)
     uint32_t n_ranks = 1, rank = 0;
+
+    // context family: siblings share the per-k-mer totals (`consumed` of the root) and take turns in record order
+    pgm_ctx *root = nullptr;                  // null: this context is the root of its family
+    cudaEvent_t ev_quota = nullptr;           // root: recorded after the newest k_quota / reset of the family
+    bool quota_recorded = false;
+    std::vector<pgm_ctx *> pipe;              // pgm_submit / pgm_wait: the internal siblings, one per batch in flight
+    uint64_t submitted = 0, waited = 0;
 
     // batch (device view) + owned copies
     DevBatch db{};
@@ -156,6 +167,25 @@ int ensure_host(pgm_ctx *c, DBuf &b, size_t bytes) {
     return PGM_OK;
 }
 
+// Room for `more` elements of `elem` bytes behind the `used` ones of a growing device array: the contents move to a buffer
+// of at least twice the size when it is full (amortised: a long run settles on its final size after a few batches).
+int arena_reserve(pgm_ctx *c, DBuf &b, size_t used, size_t more, size_t elem) {
+    const size_t need = (used + more) * elem;
+    if (need <= b.cap && b.p) return PGM_OK;
+    size_t want = std::max(need + need / 2, (size_t)1 << 20);
+    void *np = nullptr;
+    cudaError_t e = cudaMalloc(&np, want);
+    if (e != cudaSuccess) return fail(c, PGM_ERR_NOMEM, "cudaMalloc(%zu) for the model log failed: %s", want, cudaGetErrorString(e));
+    if (b.p && used) {
+        e = cudaMemcpyAsync(np, b.p, used * elem, cudaMemcpyDeviceToDevice, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) { cudaFree(np); return fail(c, PGM_ERR_CUDA, "moving the model log failed: %s", cudaGetErrorString(e)); }
+    }
+    if (b.p) cudaFree(b.p);
+    b.p = np; b.cap = want;
+    return PGM_OK;
+}
+
 void release(DBuf &b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
 void release_host(DBuf &b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
 
@@ -214,14 +244,17 @@ const char *pgm_last_error(const pgm_ctx *ctx) { return ctx ? ctx->err.c_str() :
 void pgm_destroy(pgm_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    for (pgm_ctx *k : c->pipe) pgm_destroy(k);
+    c->pipe.clear();
+    if (c->root) { c->consumed.p = nullptr; c->consumed.cap = 0; }   // the totals belong to the root
+    if (c->ev_quota) cudaEventDestroy(c->ev_quota);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->aux) { cudaStreamSynchronize(c->aux); cudaStreamDestroy(c->aux); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
-    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); cudaFree(mb.lens); cudaFree(mb.ev_off); }
     c->model_log.clear();
-    for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
-    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->bucket_base, &c->sel_base,
+    for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows, &c->model_vals, &c->model_lens, &c->model_tab}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
+    DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->bucket_base, &c->sel_base, &c->totals_snap,
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->rows_tmp, &c->rows_a, &c->sel, &c->rec_src0, &c->sc_start, &c->sc_end, &c->sc_code,
                    &c->sc_indel, &c->zbatch, &c->sel_start, &c->sel_len, &c->sel_read, &c->sel_off, &c->samples, &c->rec_packed, &c->rec_order, &c->ev_tlen, &c->ev_toff, &c->text, &c->slot_toff, &c->hp_prior, &c->hp_consumed, &c->svb_blob, &c->svb_off, &c->svb_words};
@@ -278,7 +311,8 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         }
         c->own_stream = true;
     }
-    if ((e = cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking)) != cudaSuccess ||
+    if ((e = cudaEventCreateWithFlags(&c->ev_quota, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&c->aux, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming)) != cudaSuccess) {
         delete c;
@@ -320,7 +354,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
         d.use_lut = 1; d.lut = P<uint32_t>(c->lut);
     }
     const size_t sb = (size_t)opts->n_slots * 4;
-    DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep};
+    DBuf *slotbufs[] = {&c->consumed, &c->counts, &c->keep, &c->totals_snap};
     for (DBuf *b : slotbufs) if ((rc = ensure(c, *b, sb)) != PGM_OK) return bail(rc);
     if ((rc = ensure(c, c->bucket_base, sb + 4)) != PGM_OK || (rc = ensure(c, c->sel_base, sb + 4)) != PGM_OK) return bail(rc);
     if (cudaMemset(c->consumed.p, 0, sb) != cudaSuccess) { c->err = "memset failed"; return bail(PGM_ERR_CUDA); }
@@ -333,6 +367,10 @@ int pgm_reset(pgm_ctx *c) {
     if (!c) return PGM_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaMemsetAsync(c->consumed.p, 0, (size_t)c->opts.n_slots * 4, c->stream));
+    {
+        pgm_ctx *root = c->root ? c->root : c;
+        if (root->ev_quota) { CU(c, cudaEventRecord(root->ev_quota, c->stream)); root->quota_recorded = true; }
+    }
     c->user_prior = c->user_consumed = nullptr; c->gathered = nullptr;
     if (c->state != ST_IDLE) c->state = ST_LOADED;  // the loaded batch stays usable: count/emit can be re-run
     return PGM_OK;
@@ -522,6 +560,10 @@ int pgm_count(pgm_ctx *c) {
     const uint32_t R = c->db.n_reads;
     cudaStream_t st = c->stream;
     const SortPlan sp = sort_plan(c);
+    {   // the decoder reads the totals the newest k_quota of the family wrote (a sibling's batch in front of this one)
+        pgm_ctx *root = c->root ? c->root : c;
+        if (root->quota_recorded) CU(c, cudaStreamWaitEvent(st, root->ev_quota, 0));
+    }
     {
         StageTimer t(c, PGM_STAGE_MISC);
         CU(c, cudaMemsetAsync(c->counts.p, 0, (size_t)c->opts.n_slots * 4, st));
@@ -697,9 +739,11 @@ int pgm_emit(pgm_ctx *c) {
         q.user_consumed = c->user_consumed;
         q.gathered = c->gathered; q.n_ranks = c->n_ranks; q.rank = c->rank;
         q.counts = P<uint32_t>(c->counts); q.keep = P<uint32_t>(c->keep); q.consumed = P<uint32_t>(c->consumed);
-        q.bucket_base = P<uint32_t>(c->bucket_base); q.sel_base = P<uint32_t>(c->sel_base);
+        q.bucket_base = P<uint32_t>(c->bucket_base); q.sel_base = P<uint32_t>(c->sel_base); q.snapshot = P<uint32_t>(c->totals_snap);
         k_quota<<<cdiv(NS, LB_TILE), PGM_BLOCK, 0, st>>>(q, next_lb(c, cdiv(NS, LB_TILE)));
         c->launches++;
+        pgm_ctx *root = c->root ? c->root : c;
+        if (root->ev_quota) { CU(c, cudaEventRecord(root->ev_quota, st)); root->quota_recorded = true; }
     }
     if (sorting) {
         // stable bucketing by slot fused with the selection (pgm_sort.cuh)
@@ -799,7 +843,39 @@ int pgm_emit(pgm_ctx *c) {
         }
     }
     CU(c, cudaGetLastError());
+    c->model_logged = false;
     c->state = ST_EMITTED;
+    return PGM_OK;
+}
+
+// K7: appends the emitted batch's selected samples (as the integers their "%.8f" text spells) and event lengths to the
+// model log. Everything is enqueued on the context's stream; the host tables are valid after the next synchronisation.
+static int model_log_batch(pgm_ctx *c, size_t ne, size_t nsamp) {
+    cudaStream_t st = c->stream;
+    const uint32_t NS = c->opts.n_slots;
+    if (ne) {   // the rows as arrays (the dwell log wants the lengths)
+        RET(ensure(c, c->sel_start, ne * 4)); RET(ensure(c, c->sel_len, ne * 4)); RET(ensure(c, c->sel_read, ne * 4));
+        k_unpack_sel<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(P<uint4>(c->sel), P<uint32_t>(c->sel_base) + NS, P<unsigned long long>(c->rec_src0),
+                                                       P<uint32_t>(c->sel_start), P<uint32_t>(c->sel_len), P<uint32_t>(c->sel_read));
+        c->launches++;
+    }
+    pgm_ctx::ModelBatch mb;
+    RET(arena_reserve(c, c->model_vals, c->model_vals_used, nsamp ? nsamp : 1, 8));
+    RET(arena_reserve(c, c->model_lens, c->model_lens_used, ne ? ne : 1, 4));
+    RET(ensure(c, c->model_tab, (size_t)(NS + 1) * 8));
+    mb.vals_off = c->model_vals_used; mb.n_vals = nsamp; mb.lens_off = c->model_lens_used; mb.n_ev = ne;
+    mb.h_slot_off.resize(NS + 1);
+    mb.h_ev_off.resize(NS + 1);
+    k_model_scale<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(P<double>(c->samples), &SCALARS(c)->n_sel_samples, P<long long>(c->model_vals) + mb.vals_off, P<uint32_t>(c->model_bad));
+    k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), P<unsigned long long>(c->sel_off), NS, P<unsigned long long>(c->model_tab));
+    c->launches += 2;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(mb.h_slot_off.data(), c->model_tab.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (ne) CU(c, cudaMemcpyAsync(P<uint32_t>(c->model_lens) + mb.lens_off, c->sel_len.p, ne * 4, cudaMemcpyDeviceToDevice, st));
+    CU(c, cudaMemcpyAsync(mb.h_ev_off.data(), c->sel_base.p, (size_t)(NS + 1) * 4, cudaMemcpyDeviceToHost, st));
+    c->model_vals_used += nsamp; c->model_lens_used += ne;
+    c->model_log.push_back(std::move(mb));
+    c->model_logged = true;
     return PGM_OK;
 }
 
@@ -815,7 +891,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     RET(ensure_host(c, c->h_slot_total, (size_t)NS * 4));
     RET(ensure_host(c, c->h_rflags, R ? R : 1));
     CU(c, cudaMemcpyAsync(c->h_slot_sel.p, c->keep.p, (size_t)NS * 4, cudaMemcpyDeviceToHost, st));
-    CU(c, cudaMemcpyAsync(c->h_slot_total.p, c->consumed.p, (size_t)NS * 4, cudaMemcpyDeviceToHost, st));
+    CU(c, cudaMemcpyAsync(c->h_slot_total.p, c->totals_snap.p, (size_t)NS * 4, cudaMemcpyDeviceToHost, st));
     if (R) CU(c, cudaMemcpyAsync(c->h_rflags.p, c->rflags.p, R, cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     const Scalars s = *c->h_scalars;
@@ -833,7 +909,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     const bool as_text = c->opts.output != PGM_OUT_F64;
     const bool with_events = c->opts.output != PGM_OUT_TEXT_ONLY;   // per-event arrays travel to the host
     if (!as_text) RET(ensure_host(c, c->h_samples, nsamp * 8 + 8));
-    if (ne && (with_events || c->model_on)) {   // the rows as the three arrays of pgm_result
+    if (ne && with_events) {   // the rows as the three arrays of pgm_result
         RET(ensure(c, c->sel_start, ne * 4)); RET(ensure(c, c->sel_len, ne * 4)); RET(ensure(c, c->sel_read, ne * 4));
         k_unpack_sel<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(P<uint4>(c->sel), P<uint32_t>(c->sel_base) + NS, P<unsigned long long>(c->rec_src0),
                                                        P<uint32_t>(c->sel_start), P<uint32_t>(c->sel_len), P<uint32_t>(c->sel_read));
@@ -863,26 +939,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
         CU(c, cudaMemcpyAsync(c->h_slot_toff.p, c->slot_toff.p, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
         if (with_events) CU(c, cudaMemcpyAsync(c->h_ev_toff.p, c->ev_toff.p, (ne + 1) * 8, cudaMemcpyDeviceToHost, st));
     }
-    if (c->model_on && nsamp) {   // K7: this batch's selected samples, as the integers their "%.8f" text spells
-        pgm_ctx::ModelBatch mb;
-        mb.vals = nullptr; mb.slot_off = nullptr;
-        CU(c, cudaMalloc(&mb.vals, nsamp * 8));
-        CU(c, cudaMalloc(&mb.slot_off, (size_t)(NS + 1) * 8));
-        mb.h_slot_off.resize(NS + 1);
-        k_model_scale<<<c->n_sm * 8, PGM_BLOCK, 0, st>>>(P<double>(c->samples), &SCALARS(c)->n_sel_samples, mb.vals, P<uint32_t>(c->model_bad));
-        k_slot_text_off<<<cdiv((uint64_t)NS + 1, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<uint32_t>(c->sel_base), P<unsigned long long>(c->sel_off), NS, mb.slot_off);
-        c->launches += 2;
-        CU(c, cudaGetLastError());
-        CU(c, cudaMemcpyAsync(mb.h_slot_off.data(), mb.slot_off, (size_t)(NS + 1) * 8, cudaMemcpyDeviceToHost, st));
-        // the events' lengths and slot ranges, for the dwell medians
-        CU(c, cudaMalloc(&mb.lens, (ne ? ne : 1) * 4));
-        CU(c, cudaMalloc(&mb.ev_off, (size_t)(NS + 1) * 4));
-        mb.h_ev_off.resize(NS + 1);
-        if (ne) CU(c, cudaMemcpyAsync(mb.lens, c->sel_len.p, ne * 4, cudaMemcpyDeviceToDevice, st));
-        CU(c, cudaMemcpyAsync(mb.ev_off, c->sel_base.p, (size_t)(NS + 1) * 4, cudaMemcpyDeviceToDevice, st));
-        CU(c, cudaMemcpyAsync(mb.h_ev_off.data(), c->sel_base.p, (size_t)(NS + 1) * 4, cudaMemcpyDeviceToHost, st));
-        c->model_log.push_back(std::move(mb));
-    }
+    if (c->model_on && !c->model_logged) RET(model_log_batch(c, ne, nsamp));
     CU(c, cudaStreamSynchronize(st));
     memset(out, 0, sizeof *out);
     out->n_slots = NS; out->n_reads = R;
@@ -939,8 +996,8 @@ int pgm_profile_read(pgm_ctx *c, float *ms, uint32_t *launches) {
 }
 
 static void model_clear(pgm_ctx *c) {
-    for (auto &mb : c->model_log) { cudaFree(mb.vals); cudaFree(mb.slot_off); cudaFree(mb.lens); cudaFree(mb.ev_off); }
     c->model_log.clear();
+    c->model_vals_used = c->model_lens_used = 0;
 }
 
 int pgm_model_begin(pgm_ctx *c) {
@@ -972,21 +1029,25 @@ int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **ro
     CU(c, cudaMemcpyAsync(c->model_off.p, off.data(), (size_t)(NS + 1) * 8, cudaMemcpyHostToDevice, st));
     const long long *grouped = nullptr;
     std::vector<unsigned long long> dst;   // must outlive the copies below
-    if (c->model_log.size() == 1) grouped = c->model_log[0].vals;   // one batch: its order is the grouped order
+    if (c->model_log.size() == 1) grouped = P<long long>(c->model_vals) + c->model_log[0].vals_off;   // one batch: its order is the grouped order
     else if (total) {
         RET(ensure(c, c->model_grouped, (size_t)total * 8));
-        RET(ensure(c, c->model_dst, (size_t)NS * 8 * c->model_log.size()));
-        dst.assign((size_t)NS * c->model_log.size(), 0);
+        RET(ensure(c, c->model_dst, (size_t)(NS + 1) * 8 * 2 * c->model_log.size()));
+        // per batch: [its slot table | where each of its slots goes]
+        dst.assign((size_t)(2 * NS + 2) * c->model_log.size(), 0);
         std::vector<unsigned long long> cur(off.begin(), off.end() - 1);
-        for (size_t bi = 0; bi < c->model_log.size(); bi++)
+        for (size_t bi = 0; bi < c->model_log.size(); bi++) {
+            unsigned long long *tab = dst.data() + bi * (2 * NS + 2), *to = tab + NS + 1;
+            memcpy(tab, c->model_log[bi].h_slot_off.data(), (size_t)(NS + 1) * 8);
             for (uint32_t s = 0; s < NS; s++) {
-                dst[bi * NS + s] = cur[s];
-                cur[s] += c->model_log[bi].h_slot_off[s + 1] - c->model_log[bi].h_slot_off[s];
+                to[s] = cur[s];
+                cur[s] += tab[s + 1] - tab[s];
             }
+        }
         CU(c, cudaMemcpyAsync(c->model_dst.p, dst.data(), dst.size() * 8, cudaMemcpyHostToDevice, st));
         for (size_t bi = 0; bi < c->model_log.size(); bi++) {
-            k_model_group<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(c->model_log[bi].vals, c->model_log[bi].slot_off,
-                                                             P<unsigned long long>(c->model_dst) + bi * NS, NS, P<long long>(c->model_grouped));
+            const unsigned long long *tab = P<unsigned long long>(c->model_dst) + bi * (2 * NS + 2);
+            k_model_group<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(P<long long>(c->model_vals) + c->model_log[bi].vals_off, tab, tab + NS + 1, NS, P<long long>(c->model_grouped));
             c->launches++;
         }
         grouped = P<long long>(c->model_grouped);
@@ -999,6 +1060,56 @@ int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **ro
     CU(c, cudaMemcpyAsync(c->h_model_rows.data(), c->model_rows.p, (size_t)NS * sizeof(pgm_model_row), cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     *rows_out = c->h_model_rows.data();
+    return PGM_OK;
+}
+
+int pgm_model_log(pgm_ctx *c) {
+    if (!c) return PGM_ERR_ARG;
+    if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_log needs pgm_model_begin first");
+    if (c->state != ST_EMITTED) return fail(c, PGM_ERR_STATE, "pgm_model_log needs pgm_emit first");
+    if (c->model_logged) return PGM_OK;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaMemcpyAsync(c->h_scalars, SCALARS(c), sizeof(Scalars), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    const Scalars s = *c->h_scalars;
+    if (s.err_flag) return fail(c, PGM_ERR_INPUT, "the batch is flawed (err_flag %u): see pgm_download", s.err_flag);
+    RET(model_log_batch(c, s.n_sel, (size_t)s.n_sel_samples));
+    CU(c, cudaStreamSynchronize(c->stream));
+    return PGM_OK;
+}
+
+int pgm_model_log_size(pgm_ctx *c, uint32_t *n_batches) {
+    if (!c || !n_batches) return PGM_ERR_ARG;
+    *n_batches = (uint32_t)c->model_log.size();
+    return PGM_OK;
+}
+
+int pgm_model_log_entry(pgm_ctx *c, uint32_t i, const int64_t **vals_dev, const uint64_t **slot_off_host) {
+    if (!c || !vals_dev || !slot_off_host || i >= c->model_log.size()) return PGM_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    static_assert(sizeof(unsigned long long) == sizeof(uint64_t) && sizeof(long long) == sizeof(int64_t), "64-bit types");
+    *vals_dev = reinterpret_cast<const int64_t *>(P<long long>(c->model_vals) + c->model_log[i].vals_off);
+    *slot_off_host = reinterpret_cast<const uint64_t *>(c->model_log[i].h_slot_off.data());
+    return PGM_OK;
+}
+
+int pgm_model_log_append(pgm_ctx *c, const int64_t *vals_dev, uint64_t n_vals, const uint64_t *slot_off_host) {
+    if (!c || !slot_off_host || (n_vals && !vals_dev)) return PGM_ERR_ARG;
+    if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_log_append needs pgm_model_begin first");
+    const uint32_t NS = c->opts.n_slots;
+    if (slot_off_host[NS] - slot_off_host[0] != n_vals) return fail(c, PGM_ERR_ARG, "pgm_model_log_append: the slot table does not add up to n_vals");
+    CU(c, cudaSetDevice(c->device));
+    RET(arena_reserve(c, c->model_vals, c->model_vals_used, n_vals ? n_vals : 1, 8));
+    pgm_ctx::ModelBatch mb;
+    mb.vals_off = c->model_vals_used; mb.n_vals = n_vals; mb.lens_off = c->model_lens_used; mb.n_ev = 0;
+    mb.h_slot_off.resize(NS + 1);
+    for (uint32_t s = 0; s <= NS; s++) mb.h_slot_off[s] = slot_off_host[s] - slot_off_host[0];
+    mb.h_ev_off.assign(NS + 1, 0);
+    if (n_vals) CU(c, cudaMemcpyAsync(P<long long>(c->model_vals) + mb.vals_off, vals_dev, n_vals * 8, cudaMemcpyDeviceToDevice, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+    c->model_vals_used += n_vals;
+    c->model_log.push_back(std::move(mb));
     return PGM_OK;
 }
 
@@ -1019,20 +1130,30 @@ int pgm_model_dwell(pgm_ctx *c, const int64_t **twice_median_out) {
     RET(ensure(c, c->model_off, (size_t)(NS + 1) * 8));
     RET(ensure(c, c->model_rows, (size_t)NS * sizeof(ModelRowDev)));
     RET(ensure(c, c->model_grouped, (size_t)total * 8));
-    RET(ensure(c, c->model_dst, (size_t)NS * 8 * (c->model_log.size() + 1)));
+    const size_t nb = c->model_log.size();
+    RET(ensure(c, c->model_dst, ((size_t)NS * 8 + (size_t)(NS + 1) * 4) * (nb + 1) + 64));
     CU(c, cudaMemcpyAsync(c->model_off.p, off.data(), (size_t)(NS + 1) * 8, cudaMemcpyHostToDevice, st));
-    std::vector<unsigned long long> dst((size_t)NS * c->model_log.size(), 0), cur(NS);
+    // device layout: nb destination tables (u64[NS]) followed by nb event tables (u32[NS+1])
+    std::vector<unsigned long long> dst((size_t)NS * nb, 0), cur(NS);
+    std::vector<uint32_t> evt((size_t)(NS + 1) * nb, 0);
     for (uint32_t s = 0; s < NS; s++) cur[s] = off[s] + 2;
-    for (size_t bi = 0; bi < c->model_log.size(); bi++)
+    for (size_t bi = 0; bi < nb; bi++) {
+        memcpy(evt.data() + bi * (NS + 1), c->model_log[bi].h_ev_off.data(), (size_t)(NS + 1) * 4);
         for (uint32_t s = 0; s < NS; s++) {
             dst[bi * NS + s] = cur[s];
             cur[s] += c->model_log[bi].h_ev_off[s + 1] - c->model_log[bi].h_ev_off[s];
         }
-    if (!dst.empty()) CU(c, cudaMemcpyAsync(c->model_dst.p, dst.data(), dst.size() * 8, cudaMemcpyHostToDevice, st));
+    }
+    unsigned long long *d_dst = P<unsigned long long>(c->model_dst);
+    uint32_t *d_evt = reinterpret_cast<uint32_t *>(d_dst + (size_t)NS * nb);
+    if (nb) {
+        CU(c, cudaMemcpyAsync(d_dst, dst.data(), dst.size() * 8, cudaMemcpyHostToDevice, st));
+        CU(c, cudaMemcpyAsync(d_evt, evt.data(), evt.size() * 4, cudaMemcpyHostToDevice, st));
+    }
     k_dwell_heads<<<cdiv(NS, PGM_BLOCK), PGM_BLOCK, 0, st>>>(P<unsigned long long>(c->model_off), NS, P<long long>(c->model_grouped));
     c->launches++;
-    for (size_t bi = 0; bi < c->model_log.size(); bi++) {
-        k_dwell_group<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(c->model_log[bi].lens, c->model_log[bi].ev_off, P<unsigned long long>(c->model_dst) + bi * NS, NS,
+    for (size_t bi = 0; bi < nb; bi++) {
+        k_dwell_group<<<c->n_sm * 4, PGM_BLOCK, 0, st>>>(P<uint32_t>(c->model_lens) + c->model_log[bi].lens_off, d_evt + bi * (NS + 1), d_dst + bi * NS, NS,
                                                          P<long long>(c->model_grouped));
         c->launches++;
     }
@@ -1082,6 +1203,54 @@ int pgm_debug_format(pgm_ctx *c, const double *vals, uint32_t n, char *text_out,
         cudaFree(dt);
     }
     cudaFree(dx); cudaFree(dl);
+    return PGM_OK;
+}
+
+int pgm_create_sibling(pgm_ctx *parent, void *stream, pgm_ctx **out) {
+    if (!parent || !out) return PGM_ERR_ARG;
+    *out = nullptr;
+    pgm_ctx *root = parent->root ? parent->root : parent;
+    pgm_ctx *k = nullptr;
+    const int rc = pgm_create(&root->opts, root->device, stream, &k);
+    if (rc != PGM_OK) return fail(parent, rc, "pgm_create_sibling: %s", g_create_error.c_str());
+    release(k->consumed);
+    k->consumed = root->consumed;            // one kmer_frequency_map for the family
+    k->root = root;
+    *out = k;
+    return PGM_OK;
+}
+
+#define PGM_PIPE_DEPTH 2
+int pgm_submit(pgm_ctx *c, const pgm_batch *host_batch, const pgm_svb *svb, uint64_t *batch_id) {
+    if (!c || !host_batch) return PGM_ERR_ARG;
+    if (c->root) return fail(c, PGM_ERR_STATE, "pgm_submit works on the root context of a family");
+    if (c->model_on) return fail(c, PGM_ERR_STATE, "pgm_submit does not feed the model log: use the split-phase calls after pgm_model_begin");
+    if (c->submitted - c->waited >= PGM_PIPE_DEPTH) return fail(c, PGM_ERR_STATE, "%d batches in flight: pgm_wait for batch %llu first", PGM_PIPE_DEPTH, (unsigned long long)c->waited);
+    CU(c, cudaSetDevice(c->device));
+    while (c->pipe.size() < PGM_PIPE_DEPTH) {
+        pgm_ctx *k = nullptr;
+        RET(pgm_create_sibling(c, nullptr, &k));
+        c->pipe.push_back(k);
+    }
+    pgm_ctx *k = c->pipe[c->submitted % PGM_PIPE_DEPTH];
+    int rc = svb ? pgm_upload_svb(k, host_batch, svb) : pgm_upload(k, host_batch);
+    if (rc == PGM_OK) rc = pgm_count(k);
+    if (rc == PGM_OK) rc = pgm_emit(k);
+    if (rc != PGM_OK) return fail(c, rc, "%s", k->err.c_str());
+    c->launches = 0;
+    for (pgm_ctx *q : c->pipe) c->launches += q->launches;
+    if (batch_id) *batch_id = c->submitted;
+    c->submitted++;
+    return PGM_OK;
+}
+
+int pgm_wait(pgm_ctx *c, uint64_t batch_id, pgm_result *out) {
+    if (!c || !out) return PGM_ERR_ARG;
+    if (batch_id != c->waited || c->waited >= c->submitted) return fail(c, PGM_ERR_STATE, "pgm_wait takes the batches in the order they were submitted (next: %llu)", (unsigned long long)c->waited);
+    pgm_ctx *k = c->pipe[batch_id % PGM_PIPE_DEPTH];
+    const int rc = pgm_download(k, out);
+    c->waited++;
+    if (rc != PGM_OK) return fail(c, rc, "%s", k->err.c_str());
     return PGM_OK;
 }
 

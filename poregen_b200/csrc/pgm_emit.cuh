@@ -108,6 +108,7 @@ struct QuotaIO {
     const uint32_t *gathered;       // multi-GPU, fused form: counts of every rank [n_ranks][n_slots] (or nullptr)
     uint32_t n_ranks, rank;
     uint32_t *keep, *consumed, *bucket_base, *sel_base;   // consumed may alias prior
+    uint32_t *snapshot;             // this batch's copy of the totals after it (siblings share `consumed` and move on)
 };
 
 __global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf st) {
@@ -131,6 +132,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_quota(QuotaIO io, LbBuf st) {
             io.keep[s] = k;
             if (!io.gathered) after = io.user_consumed ? io.user_consumed[s] : p + k;
             io.consumed[s] = after;
+            io.snapshot[s] = after;
             return (unsigned long long)c | ((unsigned long long)k << 31);   // two 31-bit sums in one 62-bit scan value
         },
         [&](uint64_t s, unsigned long long ex, unsigned long long) {

@@ -56,6 +56,39 @@ class GmoveEngine:
         if rc != capi.PGM_OK:
             raise PgmError(rc, self.lib.pgm_last_error(self._ctx).decode())
 
+    # -- batches in flight ---------------------------------------------------------------------
+    def submit(self, batch: ReadBatch, svb=None) -> int:
+        """pgm_submit: queue one whole pass of the next batch; returns its id. `svb` = (stream bytes, stream offsets)."""
+        cb = batch.to_c()
+        sv = None
+        if svb is not None:
+            cb.raw = None
+            sv = capi.PgmSvb()
+            sv.n_bytes, sv.bytes, sv.off = int(svb[0].size), svb[0].ctypes.data, svb[1].ctypes.data
+        bid = C.c_uint64(0)
+        self._inflight = getattr(self, "_inflight", {})
+        self._chk(self.lib.pgm_submit(self._ctx, C.byref(cb), C.byref(sv) if sv is not None else None, C.byref(bid)))
+        self._inflight[int(bid.value)] = (batch, svb)        # keeps the host buffers alive until the batch was waited for
+        return int(bid.value)
+
+    def wait_raw(self, batch_id: int) -> capi.PgmResult:
+        """pgm_wait: the C result structure (pointers into the context's pinned buffers)."""
+        r = capi.PgmResult()
+        self._chk(self.lib.pgm_wait(self._ctx, batch_id, C.byref(r)))
+        self._inflight.pop(batch_id, None)
+        return r
+
+    def wait(self, batch_id: int) -> GmoveResult:
+        return GmoveResult.from_c(self.wait_raw(batch_id), want_text=self.opts.output != capi.PGM_OUT_F64)
+
+    def sibling(self, stream: Optional[int] = None) -> "GmoveEngine":
+        """pgm_create_sibling: another context of the same family (shared per-k-mer totals)."""
+        k = GmoveEngine.__new__(GmoveEngine)
+        k.lib, k.opts, k._copts, k._keep, k.n_slots, k._batch_keep = self.lib, self.opts, self._copts, self._keep, self.n_slots, None
+        k._ctx = C.c_void_p()
+        self._chk(self.lib.pgm_create_sibling(self._ctx, C.c_void_p(stream or 0), C.byref(k._ctx)))
+        return k
+
     # -- one-call form (host buffers in, host result out) -------------------------------------
     def process(self, batch: ReadBatch) -> GmoveResult:
         cb = batch.to_c()
@@ -152,6 +185,27 @@ class GmoveEngine:
         buf = (C.c_char * (n * 40)).from_address(p.value)
         return np.frombuffer(buf, dtype=np.dtype(capi.MODEL_ROW_DTYPE), count=n).copy()
 
+    def model_log(self):
+        """pgm_model_log: put the emitted batch into the model log without downloading it."""
+        self._chk(self.lib.pgm_model_log(self._ctx))
+
+    def model_log_size(self) -> int:
+        n = C.c_uint32(0)
+        self._chk(self.lib.pgm_model_log_size(self._ctx, C.byref(n)))
+        return int(n.value)
+
+    def model_log_entry(self, i: int):
+        """(device pointer to the batch's int64 values, slot_off uint64[n_slots+1] copy) of log entry i."""
+        v, t = C.c_void_p(), C.c_void_p()
+        self._chk(self.lib.pgm_model_log_entry(self._ctx, i, C.byref(v), C.byref(t)))
+        buf = (C.c_char * ((self.n_slots + 1) * 8)).from_address(t.value)
+        return int(v.value or 0), np.frombuffer(buf, dtype=np.uint64, count=self.n_slots + 1).copy()
+
+    def model_log_append(self, vals_ptr: int, slot_off: np.ndarray):
+        so = np.ascontiguousarray(slot_off, dtype=np.uint64)
+        assert so.size == self.n_slots + 1
+        self._chk(self.lib.pgm_model_log_append(self._ctx, C.c_void_p(vals_ptr), int(so[-1] - so[0]), so.ctypes.data))
+
     def model_dwell(self) -> np.ndarray:
         """Twice the per-k-mer dwell median over everything logged since model_begin (scripts/poregen.sh:33-52); -1: no event."""
         p = C.c_void_p()
@@ -196,3 +250,96 @@ def quota_exchange(counts_all: np.ndarray, before: np.ndarray, limit: int):
     prior = np.minimum(before.astype(np.uint64)[None, :] + excl, limit).astype(np.uint32)
     consumed = np.minimum(before.astype(np.uint64) + c.sum(axis=0), limit).astype(np.uint32)
     return prior, consumed
+
+
+# ---------------------------------------------------------------------------------------------
+# K7 across GPUs (SURVEY.md 8e "Output merge"; BASELINE.json configs[4]): every rank logged the values of its own
+# batches; the k-mers are dealt to the ranks in contiguous ranges and the owner of a range collects, round by round and
+# rank by rank (= the order the values stand in the reference's dump file), what every rank logged for it.
+# ---------------------------------------------------------------------------------------------
+def model_owner_ranges(n_slots: int, world: int):
+    return [(n_slots * g // world, n_slots * (g + 1) // world) for g in range(world)]
+
+
+def _piece_table(counts: np.ndarray, lo: int, hi: int, n_slots: int) -> np.ndarray:
+    """slot_off[n_slots+1] of a piece that only holds the k-mers [lo, hi) (counts = values per k-mer of the range)."""
+    t = np.zeros(n_slots + 1, np.uint64)
+    t[lo + 1:hi + 1] = np.cumsum(counts.astype(np.uint64))
+    t[hi + 1:] = t[hi]
+    return t
+
+
+def model_merge_local(engines, opts: GmoveOptions, stddev_limit: float) -> np.ndarray:
+    """The exchange with every rank's context on ONE device (tests): engines[g] holds rank g's log; device-to-device
+    copies stand in for the all-to-all. Returns the assembled rows of all k-mers."""
+    world, NS = len(engines), engines[0].n_slots
+    n_rounds = engines[0].model_log_size()
+    assert all(e.model_log_size() == n_rounds for e in engines)
+    entries = [[e.model_log_entry(r) for e in engines] for r in range(n_rounds)]
+    rows = np.zeros(NS, np.dtype(capi.MODEL_ROW_DTYPE))
+    for o, (lo, hi) in enumerate(model_owner_ranges(NS, world)):
+        with GmoveEngine(opts) as agg:
+            agg.model_begin()
+            for r in range(n_rounds):
+                for g in range(world):
+                    ptr, so = entries[r][g]
+                    agg.model_log_append(ptr + 8 * int(so[lo]), _piece_table(np.diff(so[lo:hi + 1]), lo, hi, NS))
+            rows[lo:hi] = agg.model_finalize(stddev_limit)[lo:hi]
+    return rows
+
+
+def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, stddev_limit: float, device) -> np.ndarray:
+    """One process per GPU: NCCL all-to-all of the logged values by k-mer range (torch.distributed on the log's device
+    memory), pgm_model_finalize on the owner, all-gather of the rows. Every rank returns all rows. Collective."""
+    import torch
+    import torch.distributed as dist
+
+    class _Dev:
+        def __init__(self, ptr, n):
+            self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (ptr, False), "version": 3}
+
+    NS = eng.n_slots
+    ranges = model_owner_ranges(NS, world)
+    lo, hi = ranges[rank]
+    n_rounds = eng.model_log_size()
+    nr = torch.tensor([n_rounds], device=device)
+    dist.all_reduce(nr, op=dist.ReduceOp.MAX)
+    assert int(nr.item()) == n_rounds, "every rank logs one entry per round (empty batches included)"
+    agg = GmoveEngine(opts, device=device.index)
+    try:
+        agg.model_begin()
+        for r in range(n_rounds):
+            ptr, so = eng.model_log_entry(r)
+            # per-k-mer counts of every owner's range travel first (NS int64 in, my range from every rank out)
+            cnt = torch.from_numpy(np.diff(so).astype(np.int64)).to(device)
+            in_split = [b - a for a, b in ranges]
+            got_cnt = torch.empty(world * (hi - lo), dtype=torch.int64, device=device)
+            dist.all_to_all_single(got_cnt, cnt, output_split_sizes=[hi - lo] * world, input_split_sizes=in_split)
+            got_cnt = got_cnt.view(world, hi - lo)
+            recv_n = got_cnt.sum(dim=1).cpu().tolist()
+            send_n = [int(so[b] - so[a]) for a, b in ranges]
+            n_mine = int(so[-1])
+            vals = torch.as_tensor(_Dev(ptr, n_mine), device=device) if n_mine else torch.empty(0, dtype=torch.int64, device=device)
+            recv = torch.empty(int(sum(recv_n)), dtype=torch.int64, device=device)
+            dist.all_to_all_single(recv, vals, output_split_sizes=[int(x) for x in recv_n], input_split_sizes=send_n)
+            torch.cuda.synchronize(device)
+            cnt_host = got_cnt.cpu().numpy()
+            at = 0
+            for g in range(world):
+                agg.model_log_append(recv.data_ptr() + 8 * at, _piece_table(cnt_host[g], lo, hi, NS))
+                at += int(recv_n[g])
+        mine = agg.model_finalize(stddev_limit)[lo:hi]
+    finally:
+        agg.close()
+    # rows of every range to every rank (byte view: 40 bytes per row)
+    width = max(b - a for a, b in ranges)
+    buf = np.zeros(width, np.dtype(capi.MODEL_ROW_DTYPE))
+    buf[:hi - lo] = mine
+    t = torch.from_numpy(buf.view(np.uint8).copy()).to(device)
+    allt = torch.empty(world * t.numel(), dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allt, t)
+    allr = allt.cpu().numpy().view(np.dtype(capi.MODEL_ROW_DTYPE)).reshape(world, width)
+    rows = np.zeros(NS, np.dtype(capi.MODEL_ROW_DTYPE))
+    for g, (a, b) in enumerate(ranges):
+        rows[a:b] = allr[g, :b - a]
+    return rows

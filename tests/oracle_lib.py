@@ -125,8 +125,10 @@ def model_row_text(text: bytes, limit: float):
     return int(n), med.value, sd.value, ms.value.decode(), ss.value.decode()
 
 
-def oracle_run(opts: GmoveOptions, batch: ReadBatch, totals: np.ndarray | None = None) -> GmoveResult:
-    """One pass of the CPU restatement over `batch`; `totals` (uint32[n_slots]) is updated in place."""
+def oracle_run(opts: GmoveOptions, batch: ReadBatch, totals: np.ndarray | None = None, want_text: bool = True) -> GmoveResult:
+    """One pass of the CPU restatement over `batch`; `totals` (uint32[n_slots]) is updated in place.
+    want_text=False skips the "%.8f" formatting (full-size comparisons look at the doubles)."""
+    lib().oracle_set_text(1 if want_text else 0)
     co, keep = opts.to_c()
     cb = batch.to_c()
     if totals is None:
@@ -136,8 +138,9 @@ def oracle_run(opts: GmoveOptions, batch: ReadBatch, totals: np.ndarray | None =
     rc = lib().oracle_gmove_batch(C.byref(co), C.byref(cb), totals.ctypes.data, C.byref(r))
     if rc != 0:
         raise RuntimeError(f"oracle failed rc={rc}")
-    res = GmoveResult.from_c(r, want_text=True)
+    res = GmoveResult.from_c(r, want_text=want_text)
     lib().oracle_free_result(C.byref(r))
+    lib().oracle_set_text(1)
     del keep
     return res
 

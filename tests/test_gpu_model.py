@@ -12,6 +12,7 @@ import pytest
 import oracle_lib as ol
 from cases import _o
 from poregen_b200 import _capi as capi, synth
+from poregen_b200.batch import GmoveOptions
 from poregen_b200.gmove import GmoveEngine
 from poregen_b200.synth import SynthConfig
 
@@ -128,3 +129,55 @@ def test_dwell_medians_sparse(built):
         tm = eng.model_dwell()
     _check_dwell(tm, _slot_texts(ref))
     assert (tm == -1).any()          # k-mers without events: the file is empty, datamash prints nothing
+
+
+@pytest.mark.parametrize("n_ranks", [2, 3, 8])
+def test_model_rows_across_ranks_equal_one_context(built, n_ranks):
+    """K7 across GPUs (BASELINE.json configs[4]), the ranks' contexts on one device: every round the records are dealt to the
+    ranks in contiguous ranges with the quota exchange of a multi-GPU job, every rank logs its own values, the owners of the
+    k-mer ranges collect them round by round and rank by rank. The rows must be the ones a single context that saw every
+    record in file order produces - including which value is the file's first (the one `tail -n +2` drops)."""
+    import torch
+    from poregen_b200.gmove import model_merge_local, quota_exchange
+    cfg = synth.SynthConfig(n_reads=96, median_samples=5000, seed=77)
+    opts = GmoveOptions(kmer_size=5, sample_limit=40, file_limit=1024, index_end=1024).resolve_range()
+    batch = synth.make_batch(cfg)
+    n_rounds = 3
+    rcut = [batch.n_reads * i // n_rounds for i in range(n_rounds + 1)]
+    # one context over the whole file, streamed in the same rounds
+    with GmoveEngine(opts) as one:
+        one.model_begin()
+        for r in range(n_rounds):
+            one.process(batch.slice(rcut[r], rcut[r + 1]))
+        want = one.model_finalize(3.1)
+    engines = [GmoveEngine(opts) for _ in range(n_ranks)]
+    try:
+        for e in engines:
+            e.model_begin()
+        totals = np.zeros(engines[0].n_slots, np.uint32)
+        for r in range(n_rounds):
+            n = rcut[r + 1] - rcut[r]
+            cuts = [rcut[r] + n * g // n_ranks for g in range(n_ranks + 1)]
+            counts = []
+            for g, e in enumerate(engines):
+                e.upload(batch.slice(cuts[g], cuts[g + 1])); e.count(); e.sync()
+                t = torch.as_tensor(type("A", (), {"__cuda_array_interface__": {"shape": (e.n_slots,), "typestr": "<u4", "data": (e.counts_ptr(), False), "version": 3}})(), device="cuda:0")
+                counts.append(t.cpu().numpy().astype(np.uint32))
+            prior, consumed = quota_exchange(np.stack(counts), totals, opts.sample_limit)
+            keep = []
+            for g, e in enumerate(engines):
+                p = torch.from_numpy(prior[g].astype(np.int32)).cuda(); cns = torch.from_numpy(consumed.astype(np.int32)).cuda()
+                keep += [p, cns]
+                e.set_prior(p.data_ptr(), cns.data_ptr())
+                e.emit()
+                e.model_log()
+            torch.cuda.synchronize()
+            totals = consumed
+        got = model_merge_local(engines, opts, 3.1)
+    finally:
+        for e in engines:
+            e.close()
+    for f in ("n", "flags", "median_num"):
+        np.testing.assert_array_equal(got[f], want[f], err_msg=f)
+    assert np.array_equal(got["median"].view(np.uint64), want["median"].view(np.uint64))
+    assert np.array_equal(got["stddev"].view(np.uint64), want["stddev"].view(np.uint64))
