@@ -501,6 +501,37 @@ def run_own_arm(args):
     if world > 1:
         dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
     ms_step = float(t_res.item()) / args.steps
+
+    # ---- K7 (BASELINE.json configs[4]: per-k-mer median / stddev of everything the job dumped; scripts/poregen.sh:54-85):
+    # one more pass of the job with the model log on (every block's selected values stay in HBM as the integers their
+    # "%.8f" text spells), then the aggregation itself is timed: one GPU: pgm_model_finalize; several: all-to-all of the
+    # logged values by k-mer range over NVLink (NCCL), pgm_model_finalize on the owners, all-gather of the rows.
+    model_info = None
+    if not args.no_model:
+        from poregen_b200.gmove import model_exchange
+        eng.model_begin()
+        eng.reset()
+        for j in range(rounds):
+            blk = dev_blocks[j]
+            eng.attach_device(blk[0] if blk else empty_batch)
+            eng.count()
+            if world > 1:
+                dist.all_gather_into_tensor(all_counts.view(-1), counts_t)
+                eng.set_gathered(all_counts.data_ptr(), world, rank)
+            eng.emit()
+            eng.model_log()
+        barrier()
+        tm0 = time.perf_counter()
+        rows = eng.model_finalize(3.1) if world == 1 else model_exchange(eng, opts, world, rank, 3.1, dev)
+        barrier()
+        model_s = time.perf_counter() - tm0
+        tmx = torch.tensor([model_s], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tmx, op=dist.ReduceOp.MAX)
+        model_info = {"ms": float(tmx.item()) * 1e3, "values": int(rows["n"].sum()), "rows": int(rows.size),
+                      "rows_with_stddev": int(np.isfinite(rows["stddev"]).sum()),
+                      "how": "pgm_model_finalize (median by int64 radix selection + exact 128-bit variance per k-mer)" if world == 1 else
+                             "NCCL all-to-all of the logged values by k-mer range, pgm_model_finalize on the owners, all-gather of the rows"}
     eng.close()
 
     # ---- end to end: every block from pinned host memory in, its dump TEXT out to host memory. Two blocks are in flight:
@@ -626,6 +657,7 @@ def run_own_arm(args):
                 "roofline_step": {"algorithmic_bytes": alg_step, "gbs": alg_step / (ms_step * 1e-3) / 1e9,
                                   "frac": alg_step / (ms_step * 1e-3) / 1e9 / peak, "note": "rank 0's share / step time"},
                 "stages": stage_rows, "stages_note": "per-stage times from an untimed pass of the same steps with all stage timers on; the timed region brackets only the roofline kernel",
+                "model_aggregation": model_info,
                 "setup": {"generate_and_upload_s": gen_s}, "clocks": clocks}
         if world == 1 and not args.no_c2:
             line["c2"] = c2_leg(args, local, stream)
@@ -717,6 +749,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3, help="steps of the end-to-end leg (each moves ~55 GB over PCIe)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-c2", action="store_true", help="skip the C2 comparison leg")
+    ap.add_argument("--no-model", action="store_true", help="skip the K7 model aggregation leg")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "own":
         args.warmup = 3
