@@ -176,6 +176,8 @@ int pgm_sync(pgm_ctx *ctx);
  * emitted, so pgm_download can still follow. For callers that keep the result in HBM (benchmarks, K7). */
 int pgm_summary(pgm_ctx *ctx, pgm_result *out);
 
+struct pgm_svb; /* defined below (pgm_upload_svb) */
+
 /* Batches in flight (pgm_submit / pgm_wait). The reference's loop handles one record after the other; a host that
  * streams a file wants batch j+1 on its way to the device, and its kernels running, while batch j's dump text travels back.
  * pgm_submit queues one whole pass (upload or svb upload when `svb` is not NULL, count, emit) of the NEXT batch in alignment-

@@ -17,6 +17,10 @@ extern "C" {
 #endif
 int pgm_gmove_main(int argc, char **argv);   /* = gmove(argc, argv) */
 int pgm_reform_main(int argc, char **argv);  /* = reform(argc, argv) */
+/* apply_transformation <input_file> <output_file> <A> <B> <C> <D> of the workflow script (reference
+ * scripts/poregen.sh:87-129): argv[0] is ignored, argv[1..6] are the six arguments as TEXT (bc's result scales depend on
+ * the digits written). Host text work, no GPU. */
+int pgm_transform_main(int argc, char **argv);
 const char *pgm_cli_build_info(void);        /* sha256 of the command line's sources at build time */
 #ifdef __cplusplus
 }

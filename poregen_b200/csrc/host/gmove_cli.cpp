@@ -79,6 +79,8 @@ struct Opt {
     const char *dwell_out = nullptr;   // --dwell FILE: kmer<TAB>median dwell (scripts/poregen.sh:33-52)
     const char *model_out = nullptr;   // --model FILE: kmer<TAB>median<TAB>stddev (scripts/poregen.sh:54-85)
     double stddev_limit = 1e300;
+    const char *ont_model_out = nullptr;   // --ont_model FILE: the --model rows through apply_transformation (scripts/poregen.sh:87-129)
+    const char *transform = "17.569300789355,84.112089074928,2.5,4";   // A,B,C,D of the workflow (scripts/poregen.sh:175)
     int host_signal = 0;          // --host-signal-decode: let slow5lib decompress the signal (default: svb-zd streams go to the GPU)
 };
 
@@ -111,6 +113,8 @@ void print_help(FILE *fp, const Opt &o) {
     fprintf(fp, "   --threads INT              host threads decoding SLOW5 records [all cores]\n");
     fprintf(fp, "   --batch-samples INT        raw samples per device batch [%" PRIu64 "]\n", o.batch_samples);
     fprintf(fp, "   --model FILE               also write kmer<TAB>median<TAB>stddev per dumped k-mer (calculate_mean_stddev_all of scripts/poregen.sh)\n");
+    fprintf(fp, "   --ont_model FILE           with --model: also write the ONT .model file (apply_transformation of scripts/poregen.sh)\n");
+    fprintf(fp, "   --transform A,B,C,D        level_mean*A+B, stddev rescaled to [C,D] [17.569300789355,84.112089074928,2.5,4]\n");
     fprintf(fp, "   --stddev_limit FLOAT       upper clamp of the stddev column [none]\n");
     fprintf(fp, "   --dwell FILE               per-k-mer median of (event length - 1), as calculate_dwell_times_medians prints it\n");
     fprintf(fp, "   --host-signal-decode       decompress svb-zd signals with slow5lib on the host instead of on the GPU\n");
@@ -343,6 +347,7 @@ void bam_to_rec(const BamRecord &b, Rec &r) {
 }
 
 #include "reform.inc"
+#include "transform.inc"
 
 // ---------------------------------------------------------------------------------------------------
 // Pinned, growable array for batch data.
@@ -710,7 +715,7 @@ void process_batch(Run &R, Batch &b) {
 
 enum { LO_SCALING = 3, LO_MARGIN, LO_SAMPLE_LIMIT, LO_FILE_LIMIT, LO_KMER_FILE, LO_INDEX_START, LO_INDEX_END, LO_FASTQ, LO_D,
        LO_MAX_DUR, LO_MIN_DUR, LO_PA_MIN, LO_PA_MAX, LO_PICK_MARGIN, LO_RNA, LO_VERBOSE, LO_HELP, LO_VERSION, LO_DEBUG_BREAK,
-       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT, LO_HOSTSIG, LO_DWELL };
+       LO_GPUS, LO_THREADS, LO_BATCH, LO_MODEL, LO_SDLIMIT, LO_HOSTSIG, LO_DWELL, LO_ONT_MODEL, LO_TRANSFORM };
 
 const struct option long_options[] = {
     {"kmer_size", required_argument, 0, 'k'},          // 0
@@ -742,6 +747,8 @@ const struct option long_options[] = {
     {"stddev_limit", required_argument, 0, 0},         // 26
     {"host-signal-decode", no_argument, 0, 0},         // 27
     {"dwell", required_argument, 0, 0},                // 28
+    {"ont_model", required_argument, 0, 0},            // 29
+    {"transform", required_argument, 0, 0},            // 30
     {0, 0, 0, 0}};
 
 }  // namespace
@@ -822,6 +829,8 @@ int gmove(int argc, char *argv[]) {
                 case LO_SDLIMIT: opt.stddev_limit = atof(optarg); break;
                 case LO_HOSTSIG: opt.host_signal = 1; break;
                 case LO_DWELL: opt.dwell_out = optarg; break;
+                case LO_ONT_MODEL: opt.ont_model_out = optarg; break;
+                case LO_TRANSFORM: opt.transform = optarg; break;
                 default: break;
             }
         }
@@ -957,6 +966,7 @@ int gmove(int argc, char *argv[]) {
     R.t_start = t_c0 - t_gmove0;
     for (int g = 0; g < opt.gpus; g++)
         if (pgm_create(&po, g % ndev, nullptr, &R.gpus[g].ctx) != PGM_OK) DIE("%s", pgm_last_error(nullptr));
+    if (opt.ont_model_out && !opt.model_out) DIE("%s", "--ont_model needs --model (it transforms that file)");
     if (opt.model_out || opt.dwell_out) {
         // a k-mer's values would be spread over the devices: the segmented median needs them in one place
         if (opt.gpus != 1) DIE("%s", "--model / --dwell need --gpus 1");
@@ -1028,6 +1038,17 @@ int gmove(int argc, char *argv[]) {
             else fprintf(fm, "%s\t%.14g\t%.14g\n", name, (double)rows[s].median_num / 2e8, rows[s].stddev);
         }
         fclose(fm);
+        if (opt.ont_model_out) {
+            std::vector<std::string> abcd;
+            for (const char *p = opt.transform;; ) {
+                const char *c = strchr(p, ',');
+                abcd.push_back(c ? std::string(p, c) : std::string(p));
+                if (!c) break;
+                p = c + 1;
+            }
+            if (abcd.size() != 4) DIE("%s", "--transform wants A,B,C,D");
+            if (apply_transformation(opt.model_out, opt.ont_model_out, abcd[0].c_str(), abcd[1].c_str(), abcd[2].c_str(), abcd[3].c_str())) exit(EXIT_FAILURE);
+        }
     }
     if (opt.dwell_out) {
         const int64_t *tm = nullptr;
@@ -1054,15 +1075,23 @@ int gmove(int argc, char *argv[]) {
 extern "C" int pgm_gmove_main(int argc, char **argv) { return gmove(argc, argv); }
 extern "C" int pgm_reform_main(int argc, char **argv) { return reform(argc, argv); }
 
+// poregen transform <input_file> <output_file> <A> <B> <C> <D>: apply_transformation with the script's argument order
+extern "C" int pgm_transform_main(int argc, char **argv) {
+    if (argc != 7) { fprintf(stderr, "Usage: apply_transformation <input_file> <output_file> <A> <B> <C> <D>\n"); return 1; }
+    return apply_transformation(argv[1], argv[2], argv[3], argv[4], argv[5], argv[6]);
+}
+
 #ifndef PGM_NO_MAIN
 // poregen's dispatcher (reference src/main.c:64-103), gmove only.
 int main(int argc, char *argv[]) {
     const double t0 = realtime();
     const bool is_gmove = argc >= 2 && strcmp(argv[1], "gmove") == 0, is_reform = argc >= 2 && strcmp(argv[1], "reform") == 0;
     if (argc >= 2 && strcmp(argv[1], "--build-info") == 0) { printf("%s\n", pgm_cli_build_info()); return 0; }
+    if (argc >= 2 && strcmp(argv[1], "transform") == 0) return pgm_transform_main(argc - 1, argv + 1);
     if (!is_gmove && !is_reform) {
         fprintf(stderr, "Usage: poregen <command> [options]\n\ncommand:\n         gmove     B200 build of `poregen gmove`\n"
-                        "         reform    move table (SAM/BAM) -> per-k-mer TSV or PAF with ss:Z\n");
+                        "         reform    move table (SAM/BAM) -> per-k-mer TSV or PAF with ss:Z\n"
+                        "         transform raw model -> ONT .model (apply_transformation of scripts/poregen.sh)\n");
         return (argc >= 2 && (strcmp(argv[1], "--help") == 0 || strcmp(argv[1], "-h") == 0)) ? 0 : 1;
     }
     if (is_reform) {
