@@ -326,6 +326,24 @@ int pgm_debug_format(pgm_ctx *ctx, const double *vals, uint32_t n, char *text_ou
  * decoded), and the decoder's verdict (PGM_ERR_INPUT for a malformed stream). Synchronises. */
 int pgm_debug_raw(pgm_ctx *ctx, int16_t *out, uint64_t n);
 
+/* The dump text ("%.8f," ... "%.8f;": one event of n values, as pgm_debug_format writes it) of n doubles that are
+ * already in device memory, for callers that cannot allocate. This entry point has NO counterpart in the reference:
+ * it was added for code under CUDA graph capture, tight serving loops and
+ * harnesses that forbid cudaMalloc. It calls no cudaMalloc / cudaFree / allocating routine and takes no context:
+ * its scan scratch is a static __device__ array of NOALLOC_SCRATCH_BYTES (33,024 bytes) that every GPU loading the
+ * library holds until exit, which bounds n at PGM_NOALLOC_MAX_VALUES; a larger n is rejected with PGM_ERR_ARG and a
+ * message in pgm_last_error(NULL).
+ *   vals_dev[n]   device doubles;  text_dev[cap] device characters (NULL: lengths only);  *len_dev (device, 8 bytes)
+ *   = the length of the whole text, always. A value whose characters do not all fit below cap is not written.
+ * One memset node + one kernel on `stream` (NULL = the legacy default stream); returns without synchronising.
+ * Makes `device` current. The first call on a device looks the array's address up (cudaGetSymbolAddress) and may load
+ * the module: make it outside stream capture (n = 0 will do).
+ * All calls on a device share the one scratch array, and each call clears what it uses: two calls whose work overlaps
+ * on the GPU (different streams without an ordering between them) RACE. Keep calls on one stream or order them. */
+#define PGM_NOALLOC_MAX_VALUES (1u << 24)
+int pgm_format_noalloc(int device, void *stream, const double *vals_dev, uint32_t n, char *text_dev, uint64_t cap,
+                       unsigned long long *len_dev);
+
 #ifdef __cplusplus
 }
 #endif

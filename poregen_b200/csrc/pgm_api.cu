@@ -14,6 +14,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -1263,3 +1264,58 @@ int pgm_process(pgm_ctx *c, const pgm_batch *host_batch, pgm_result *out) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// pgm_format_noalloc: the dump text of n doubles without any allocation (include/pgm_gmove.h). No counterpart in the
+// reference; added for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops). A variant of k_scan_text (pgm_text.cuh): the same single-pass look-back scan, with the length
+// of a value computed in the scan's load step and its characters written in the store step, and with the scan's
+// scratch (one ticket + one status word per tile of LB_TILE values) in a file-scope __device__ array instead of the
+// context's per-batch zero region. Every GPU that loads this library holds the array until the process exits.
+#define NOALLOC_TILES ((PGM_NOALLOC_MAX_VALUES + LB_TILE - 1) / LB_TILE)
+#define NOALLOC_STATUS_OFF 256                                     // bytes: the ticket has a 256-byte line of its own
+#define NOALLOC_SCRATCH_BYTES (NOALLOC_STATUS_OFF + NOALLOC_TILES * 8)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+__global__ void __launch_bounds__(PGM_BLOCK) k_format_noalloc(const double *x, uint32_t n, char *text, unsigned long long cap, unsigned long long *len_out, LbBuf st) {
+    lb_scan<unsigned long long>(
+        n, st, [&](uint64_t i) { return (unsigned long long)fmt8_len(x[i]); },
+        [&](uint64_t i, unsigned long long at, unsigned long long len) {
+            if (text && at + len <= cap) {
+                const double v = x[i];
+                fmt8_write(fmt8_prepare(v), v, (i + 1 == n) ? ';' : ',', text + at);      // gmove.cpp:674-678
+            }
+        },
+        [&](unsigned long long tot) { *len_out = tot; });
+}
+
+namespace {
+#define NOALLOC_MAX_DEVICES 64
+// In host code g_noalloc_scratch is a host-side stand-in, not a device address: the address a kernel can use comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+std::atomic<void *> g_noalloc_addr[NOALLOC_MAX_DEVICES];
+}  // namespace
+
+extern "C" int pgm_format_noalloc(int device, void *stream, const double *vals_dev, uint32_t n, char *text_dev, uint64_t cap, unsigned long long *len_dev) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(nullptr, PGM_ERR_ARG, "pgm_format_noalloc: device %d outside [0, %d)", device, NOALLOC_MAX_DEVICES);
+    if (!len_dev || (n && !vals_dev)) return fail(nullptr, PGM_ERR_ARG, "pgm_format_noalloc: vals_dev / len_dev is NULL");
+    if (n > PGM_NOALLOC_MAX_VALUES)
+        return fail(nullptr, PGM_ERR_ARG, "pgm_format_noalloc: n = %u exceeds PGM_NOALLOC_MAX_VALUES = %u (the static scratch holds one status word per %u values)",
+                    n, (unsigned)PGM_NOALLOC_MAX_VALUES, (unsigned)LB_TILE);
+    CU(nullptr, cudaSetDevice(device));
+    void *base = g_noalloc_addr[device].load(std::memory_order_acquire);
+    if (!base) {                                                     // set-up, once per device (a second thread asking at the same time gets the same answer)
+        CU(nullptr, cudaGetSymbolAddress(&base, g_noalloc_scratch));
+        g_noalloc_addr[device].store(base, std::memory_order_release);
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t tiles = (n + LB_TILE - 1) / LB_TILE;
+    // the array keeps the last call's contents: the ticket and the status words this call will use start at zero
+    CU(nullptr, cudaMemsetAsync(base, 0, NOALLOC_STATUS_OFF + (size_t)(tiles ? tiles : 1) * 8, s));
+    LbBuf st;
+    st.ticket = (uint32_t *)base;
+    st.status = (unsigned long long *)((unsigned char *)base + NOALLOC_STATUS_OFF);
+    k_format_noalloc<<<tiles ? tiles : 1, PGM_BLOCK, 0, s>>>(vals_dev, n, text_dev, (unsigned long long)cap, len_dev, st);
+    CU(nullptr, cudaGetLastError());
+    return PGM_OK;
+}
