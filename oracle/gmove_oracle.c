@@ -408,10 +408,11 @@ size_t oracle_model_row_text(const char *text, size_t len, double limit, double 
     if (n < 2) { free(v); return 0; }
     size_t m = n - 1;
     long double *c = v + 1;                                   /* tail -n +2 */
-    qsort(c, m, sizeof(long double), ld_cmp);
-    long double med = (m & 1) ? c[m / 2] : (c[m / 2 - 1] + c[m / 2]) / 2.0L;
+    /* sstdev is a datamash run of its own (poregen.sh:74): its sums go over the values in FILE order */
     long double mean = 0; for (size_t k = 0; k < m; k++) mean += c[k]; mean /= (long double)m;
     long double ss = 0; for (size_t k = 0; k < m; k++) ss += (c[k] - mean) * (c[k] - mean);
+    qsort(c, m, sizeof(long double), ld_cmp);
+    long double med = (m & 1) ? c[m / 2] : (c[m / 2 - 1] + c[m / 2]) / 2.0L;
     long double sd = (m > 1) ? sqrtl(ss / (long double)(m - 1)) : (long double)NAN;
     *median = (double)med;
     if (median_str) sprintf(median_str, "%.14Lg", med);

@@ -8,12 +8,14 @@
 // Element counts that only the device knows (passing / selected events) stay on the device: grids
 // are sized by capacities derived from the batch and the kernels read the counts themselves.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>   // header-only: resolves to no-ops unless a tool (nsys, ncu --nvtx) injects itself
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
 #include <string>
 #include <vector>
@@ -35,7 +37,10 @@ thread_local std::string g_create_error;
 struct DBuf {
     void *p = nullptr;
     size_t cap = 0;
+    bool guarded = false;        // PGM_GUARD=1: PGM_GUARD_BYTES of 0xA5 in front of p and behind p + cap (cap = the bytes asked for)
+    const char *name = nullptr;
 };
+#define PGM_GUARD_BYTES 4096
 
 
 typedef BatchScalars Scalars;  // device -> host summary of one batch (pgm_emit.cuh)
@@ -83,6 +88,9 @@ struct pgm_ctx {
 
     // context family: siblings share the per-k-mer totals (`consumed` of the root) and take turns in record order
     pgm_ctx *root = nullptr;                  // null: this context is the root of its family
+    bool guard = false;                       // PGM_GUARD=1 at pgm_create: every device buffer exact-sized between guard zones, checked by pgm_download
+    std::vector<DBuf *> guard_list;
+    bool guard_selftest = false;              // PGM_GUARD=2: guard_check first writes one byte behind `cal`, to show that the check sees it
     cudaEvent_t ev_quota = nullptr;           // root: recorded after the newest k_quota / reset of the family
     bool quota_recorded = false;
     std::vector<pgm_ctx *> pipe;              // pgm_submit / pgm_wait: the internal siblings, one per batch in flight
@@ -142,19 +150,75 @@ int fail(pgm_ctx *c, int code, const char *fmt, ...) {
     return code;
 }
 
+// NVTX range around a C-ABI phase (the reference has no tracing; an nsys timeline of the e2e leg shows
+// upload / count / emit / download of two batches overlapping). Domain "pgm_gmove".
+struct PhaseRange {
+    static nvtxDomainHandle_t domain() { static nvtxDomainHandle_t d = nvtxDomainCreateA("pgm_gmove"); return d; }
+    explicit PhaseRange(const char *name) {
+        nvtxEventAttributes_t a = {};
+        a.version = NVTX_VERSION; a.size = NVTX_EVENT_ATTRIB_STRUCT_SIZE;
+        a.messageType = NVTX_MESSAGE_TYPE_ASCII; a.message.ascii = name;
+        nvtxDomainRangePushEx(domain(), &a);
+    }
+    ~PhaseRange() { nvtxDomainRangePop(domain()); }
+};
+#define PHASE(name) PhaseRange phase_range_(name)
+
 #define CU(c, call)                                                                                        \
     do {                                                                                                   \
         cudaError_t e_ = (call);                                                                           \
         if (e_ != cudaSuccess) return fail((c), PGM_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
     } while (0)
 
-int ensure(pgm_ctx *c, DBuf &b, size_t bytes) {
+void free_dev(DBuf &b) {
+    if (b.p) cudaFree(b.guarded ? (void *)((char *)b.p - PGM_GUARD_BYTES) : b.p);
+    b.p = nullptr; b.cap = 0; b.guarded = false;
+}
+
+// Guard mode (environment PGM_GUARD=1, read by pgm_create; a debugging aid where compute-sanitizer is not available):
+// a buffer is exactly the bytes asked for, filled with 0xA5 (so stale or never-written data is not zero), with
+// PGM_GUARD_BYTES of 0xA5 on both sides; guard_check() after every pgm_download / pgm_summary / pgm_model_finalize
+// fails the call when a kernel wrote into a guard zone. Slow (reallocates whenever a size changes): tests only.
+int ensure_(pgm_ctx *c, DBuf &b, size_t bytes, const char *name) {
+    if (c->guard) {
+        if (b.p && b.guarded && b.cap == bytes) return PGM_OK;
+        free_dev(b);
+        char *raw = nullptr;
+        cudaError_t e = cudaMalloc(&raw, bytes + 2 * PGM_GUARD_BYTES);
+        if (e == cudaSuccess) e = cudaMemset(raw, 0xA5, bytes + 2 * PGM_GUARD_BYTES);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();      // the fill runs on the legacy stream: the context's non-blocking streams do not wait for it
+        if (e != cudaSuccess) return fail(c, PGM_ERR_NOMEM, "guarded cudaMalloc(%zu) for %s failed: %s", bytes, name, cudaGetErrorString(e));
+        b.p = raw + PGM_GUARD_BYTES; b.cap = bytes; b.guarded = true; b.name = name;
+        if (std::find(c->guard_list.begin(), c->guard_list.end(), &b) == c->guard_list.end()) c->guard_list.push_back(&b);
+        return PGM_OK;
+    }
     if (bytes <= b.cap && b.p) return PGM_OK;
-    if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+    free_dev(b);
     size_t want = bytes + bytes / 8 + 256;
     cudaError_t e = cudaMalloc(&b.p, want);
     if (e != cudaSuccess) { b.p = nullptr; return fail(c, PGM_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); }
     b.cap = want;
+    return PGM_OK;
+}
+#define ensure(c, b, bytes) ensure_((c), (b), (bytes), #b)
+
+// All guard zones of the context's buffers still hold 0xA5? (synchronises; guard mode only)
+int guard_check(pgm_ctx *c, const char *where) {
+    if (!c->guard) return PGM_OK;
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess) return PGM_OK;      // the caller reports CUDA errors itself
+    std::vector<unsigned char> h(2 * PGM_GUARD_BYTES);
+    if (c->guard_selftest && c->cal.p && c->cal.guarded) CU(c, cudaMemset((char *)c->cal.p + c->cal.cap + 3, 0x00, 1));
+    for (DBuf *b : c->guard_list) {
+        if (!b->p || !b->guarded) continue;
+        CU(c, cudaMemcpy(h.data(), (char *)b->p - PGM_GUARD_BYTES, PGM_GUARD_BYTES, cudaMemcpyDeviceToHost));
+        CU(c, cudaMemcpy(h.data() + PGM_GUARD_BYTES, (char *)b->p + b->cap, PGM_GUARD_BYTES, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < h.size(); i++)
+            if (h[i] != 0xA5) {
+                const bool front = i < PGM_GUARD_BYTES;
+                return fail(c, PGM_ERR_STATE, "PGM_GUARD: %s: buffer %s (%zu bytes): byte %zu %s the buffer was overwritten (0x%02x)", where, b->name ? b->name : "?",
+                            b->cap, front ? PGM_GUARD_BYTES - i : i - PGM_GUARD_BYTES, front ? "in front of" : "behind", h[i]);
+            }
+    }
     return PGM_OK;
 }
 
@@ -187,7 +251,7 @@ int arena_reserve(pgm_ctx *c, DBuf &b, size_t used, size_t more, size_t elem) {
     return PGM_OK;
 }
 
-void release(DBuf &b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+void release(DBuf &b) { free_dev(b); }
 void release_host(DBuf &b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
 
 template <typename T> T *P(DBuf &b) { return reinterpret_cast<T *>(b.p); }
@@ -254,7 +318,7 @@ void pgm_destroy(pgm_ctx *c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->ev_join) cudaEventDestroy(c->ev_join);
     c->model_log.clear();
-    for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows, &c->model_vals, &c->model_lens, &c->model_tab}) if (mbuf->p) { cudaFree(mbuf->p); mbuf->p = nullptr; }
+    for (DBuf *mbuf : {&c->model_bad, &c->model_grouped, &c->model_off, &c->model_dst, &c->model_rows, &c->model_vals, &c->model_lens, &c->model_tab}) release(*mbuf);
     DBuf *dev[] = {&c->lut, &c->consumed, &c->counts, &c->keep, &c->bucket_base, &c->sel_base, &c->totals_snap,
                    &c->gscratch, &c->raw, &c->align, &c->bases, &c->reads, &c->cal, &c->rflags, &c->n_pass,
                    &c->ev_base, &c->rows_tmp, &c->rows_a, &c->sel, &c->rec_src0, &c->sc_start, &c->sc_end, &c->sc_code,
@@ -327,6 +391,7 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
     d.pa_min = opts->pa_min; d.pa_max = opts->pa_max;
     d.fourth = opts->flag_rna ? 'U' : 'T';
     if (const char *dbg = getenv("PGM_DEBUG_SLOW_STATS")) d.debug |= (dbg[0] && dbg[0] != '0') ? 1u : 0u;
+    if (const char *gd = getenv("PGM_GUARD")) { c->guard = gd[0] && gd[0] != '0'; c->guard_selftest = gd[0] == '2'; }
     int rc = PGM_OK;
     auto bail = [&](int code) { std::string m = c->err; pgm_destroy(c); g_create_error = m; return code; };
     if (opts->kmer_list) {
@@ -484,12 +549,14 @@ static int upload_common(pgm_ctx *c, const pgm_batch *b, bool with_raw) {
 }
 
 int pgm_upload(pgm_ctx *c, const pgm_batch *b) {
+    PHASE("pgm_upload");
     if (!c || !b) return PGM_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
     return upload_common(c, b, true);
 }
 
 int pgm_upload_svb(pgm_ctx *c, const pgm_batch *b, const pgm_svb *svb) {
+    PHASE("pgm_upload_svb");
     if (!c || !b || !svb) return PGM_ERR_ARG;
     if (b->raw) return fail(c, PGM_ERR_ARG, "pgm_upload_svb: batch.raw must be NULL (the samples are decoded on the device)");
     if (b->n_reads && (!svb->off || (svb->n_bytes && !svb->bytes))) return fail(c, PGM_ERR_ARG, "null array in pgm_svb");
@@ -555,6 +622,7 @@ static EvSource ev_source(pgm_ctx *c) {
 }
 
 int pgm_count(pgm_ctx *c) {
+    PHASE("pgm_count");
     if (!c) return PGM_ERR_ARG;
     if (c->state != ST_LOADED) return fail(c, PGM_ERR_STATE, "pgm_count needs pgm_upload/pgm_attach_device first");
     CU(c, cudaSetDevice(c->device));
@@ -708,6 +776,7 @@ static TextIO make_text_io(pgm_ctx *c) {
 }
 
 int pgm_emit(pgm_ctx *c) {
+    PHASE("pgm_emit");
     if (!c) return PGM_ERR_ARG;
     if (c->state != ST_COUNTED) return fail(c, PGM_ERR_STATE, "pgm_emit needs pgm_count first");
     CU(c, cudaSetDevice(c->device));
@@ -881,6 +950,7 @@ static int model_log_batch(pgm_ctx *c, size_t ne, size_t nsamp) {
 }
 
 int pgm_download(pgm_ctx *c, pgm_result *out) {
+    PHASE("pgm_download");
     if (!c || !out) return PGM_ERR_ARG;
     if (c->state != ST_EMITTED) return fail(c, PGM_ERR_STATE, "pgm_download needs pgm_emit first");
     CU(c, cudaSetDevice(c->device));
@@ -952,7 +1022,7 @@ int pgm_download(pgm_ctx *c, pgm_result *out) {
     out->text = as_text ? P<char>(c->h_text) : nullptr; out->slot_text_off = as_text ? P<uint64_t>(c->h_slot_toff) : nullptr;
     out->ev_text_off = (as_text && with_events) ? P<uint64_t>(c->h_ev_toff) : nullptr;
     c->state = ST_IDLE;
-    return PGM_OK;
+    return guard_check(c, "pgm_download");
 }
 
 int pgm_summary(pgm_ctx *c, pgm_result *out) {
@@ -967,7 +1037,7 @@ int pgm_summary(pgm_ctx *c, pgm_result *out) {
     out->n_events_examined = s.examined; out->n_events_pass = s.n_pass;
     out->n_sel_events = s.n_sel; out->n_sel_samples = s.n_sel_samples;
     if (s.err_flag) return fail(c, PGM_ERR_INPUT, "batch has records whose offsets fall outside the arrays (or ss records with a trim offset)");
-    return PGM_OK;
+    return guard_check(c, "pgm_summary");
 }
 
 static const char *const kStageNames[PGM_N_STAGES] = {"prep", "decode", "scan", "place", "sort", "select", "stats", "gather", "misc", "text", "svb"};
@@ -1013,6 +1083,7 @@ int pgm_model_begin(pgm_ctx *c) {
 }
 
 int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **rows_out) {
+    PHASE("pgm_model_finalize");
     if (!c || !rows_out) return PGM_ERR_ARG;
     if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_finalize needs pgm_model_begin first");
     static_assert(sizeof(ModelRowDev) == sizeof(pgm_model_row), "device and ABI rows must agree");
@@ -1061,10 +1132,11 @@ int pgm_model_finalize(pgm_ctx *c, double stddev_limit, const pgm_model_row **ro
     CU(c, cudaMemcpyAsync(c->h_model_rows.data(), c->model_rows.p, (size_t)NS * sizeof(pgm_model_row), cudaMemcpyDeviceToHost, st));
     CU(c, cudaStreamSynchronize(st));
     *rows_out = c->h_model_rows.data();
-    return PGM_OK;
+    return guard_check(c, "pgm_model_finalize");
 }
 
 int pgm_model_log(pgm_ctx *c) {
+    PHASE("pgm_model_log");
     if (!c) return PGM_ERR_ARG;
     if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_log needs pgm_model_begin first");
     if (c->state != ST_EMITTED) return fail(c, PGM_ERR_STATE, "pgm_model_log needs pgm_emit first");
@@ -1223,6 +1295,7 @@ int pgm_create_sibling(pgm_ctx *parent, void *stream, pgm_ctx **out) {
 
 #define PGM_PIPE_DEPTH 2
 int pgm_submit(pgm_ctx *c, const pgm_batch *host_batch, const pgm_svb *svb, uint64_t *batch_id) {
+    PHASE("pgm_submit");
     if (!c || !host_batch) return PGM_ERR_ARG;
     if (c->root) return fail(c, PGM_ERR_STATE, "pgm_submit works on the root context of a family");
     if (c->model_on) return fail(c, PGM_ERR_STATE, "pgm_submit does not feed the model log: use the split-phase calls after pgm_model_begin");
@@ -1246,6 +1319,7 @@ int pgm_submit(pgm_ctx *c, const pgm_batch *host_batch, const pgm_svb *svb, uint
 }
 
 int pgm_wait(pgm_ctx *c, uint64_t batch_id, pgm_result *out) {
+    PHASE("pgm_wait");
     if (!c || !out) return PGM_ERR_ARG;
     if (batch_id != c->waited || c->waited >= c->submitted) return fail(c, PGM_ERR_STATE, "pgm_wait takes the batches in the order they were submitted (next: %llu)", (unsigned long long)c->waited);
     pgm_ctx *k = c->pipe[batch_id % PGM_PIPE_DEPTH];
