@@ -229,7 +229,11 @@ def _cli_leg(rf, ref_outs, n_samples):
             return {"error": p.stderr.decode()[-300:]}
         if best is None or dt < best:
             best = dt
-            stats = [ln for ln in p.stderr.decode().splitlines() if "pgm" in ln.lower() and ("s" in ln)][-3:]
+            stats = None
+            for ln in p.stderr.decode().splitlines():      # "[gmove] N records, ...; start 0.1s create 0.2s parse ... close 0.0s" (gmove_cli.cpp, PGM_CLI_STATS)
+                if ln.startswith("[gmove]") and "; start " in ln:
+                    import re
+                    stats = {k + "_s": float(v) for k, v in re.findall(r"(start|create|parse|read|device|write|close) ([0-9.]+)s", ln.split(";", 1)[1])}
     # byte comparison: freq.txt of every window concatenated == ours; every non-empty dump file identical
     same = True
     try:
@@ -246,7 +250,10 @@ def _cli_leg(rf, ref_outs, n_samples):
     except OSError:
         same, checked = False, 0
     return {"value": n_samples / best, "unit": UNIT, "seconds": best, "identical_to_reference": same, "dump_files_compared": checked,
-            "phases": stats, "note": "process start to exit, incl. CUDA context creation"}
+            "phases": stats,
+            "phases_note": "start = option parsing + k-mer list + opening 4^k dump files (overlaps CUDA start-up); create = pgm_create; parse = alignment "
+                           "text; read = waiting for SLOW5 records (decoded on host threads); device = pgm_submit/pgm_wait; write = fwrite of dump text; close = fclose + freq.txt",
+            "note": "process start to exit, incl. CUDA context creation"}
 
 
 # ------------------------------------------------------------------------------------------------

@@ -36,10 +36,13 @@ struct DevBatch {
 };
 
 // Per-read derived calibration (k_read_prep) and Med-MAD result (k_stats).
-struct ReadCal {
-    int32_t clo, chi;   // int16 codes c with clo <= c <= chi are inside [pa_min, pa_max]; clo>chi: none
+struct __align__(64) ReadCal {   // 64 bytes: what a conversion without Med-MAD needs sits in ONE 32-byte sector (k_gather reads it per event)
     double scale;       // range / digitisation
+    double offset;      // pgm_read.offset (copied: the record table itself is a second random access away)
+    int32_t clo, chi;   // int16 codes c with clo <= c <= chi are inside [pa_min, pa_max]; clo>chi: none
+    int32_t pad0, pad1;
     double med, mad;    // only meaningful with scaling and when the read has selected events
+    double pad2, pad3;
 };
 
 // ---------------------------------------------------------------- pA and the in-range interval

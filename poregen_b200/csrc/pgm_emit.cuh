@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(PGM_BLOCK) k_read_prep(DevOpts o, DevBatch b, 
         if (rd.trim >= rd.raw_len) f |= PGM_RF_BAD_ALIGN | PGM_RF_SKIPPED;
         if (b.mode != PGM_MODE_SS && rd.fastq_len < 10) f |= PGM_RF_SKIPPED;
         ReadCal c;
-        c.scale = scale; c.med = 0.0; c.mad = 1.0; c.clo = 0; c.chi = -1;
+        c.scale = scale; c.offset = rd.offset; c.med = 0.0; c.mad = 1.0; c.clo = 0; c.chi = -1; c.pad0 = c.pad1 = 0; c.pad2 = c.pad3 = 0.0;
         if (!(f & PGM_RF_BAD_CALIB)) pgm_code_interval(rd.offset, scale, o.pa_min, o.pa_max, &c.clo, &c.chi);
         cal[r] = c;
         rflags[r] = (uint8_t)f;

@@ -460,7 +460,7 @@ __device__ __forceinline__ uint64_t shfl_u64(uint64_t v, int src) { return __shf
 #define GATHER_CAP_CH 160                   // chunks of staging per batch of 32 events, packed end to end (5 per event on average)
 #define GATHER_STAGE_SAMPLES (GATHER_CAP_CH * 8)
 constexpr int kGatherUnroll = GATHER_UNROLL;
-struct __align__(16) GatherEvP {   // 64 bytes, read with four 16-byte shared-memory loads
+struct __align__(16) GatherEvP {   // 64 bytes of payload, read with 16-byte shared-memory loads
     double offset, scale;
     double med, mad;
     double rcp;
@@ -469,6 +469,8 @@ struct __align__(16) GatherEvP {   // 64 bytes, read with four 16-byte shared-me
     uint32_t len;             // samples of the event
     uint32_t rel;             // output position of its first sample, relative to the batch's first
     uint32_t packed;          // bits 0-10 index of sample 0 in the staged copy | 11-18 samples staged | 19 fast division | 20 odd start
+    uint32_t pad[4];          // 80-byte stride: the records of eight consecutive events start in eight different bank groups, so the
+                              // walk's 16-byte loads of DIFFERENT events (and the publish's stores) do not collide (64: every other one did)
 };
 struct GatherStage {
     int16_t raw[2][GATHER_STAGE_SAMPLES];
@@ -518,14 +520,16 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
     const uint64_t raw_lim = b.n_raw & ~(uint64_t)7;      // whole 16-byte chunks of raw[] end here: nothing is fetched beyond
     auto level2 = [&](uint32_t buf) {
         const uint32_t rd = ok1 ? row1.w : 0u;  // level 1 arrived an iteration ago
-        const pgm_read *rp = b.reads + rd;
         const ReadCal *rc = io.cal + rd;
         ln2 = ok1 ? ev_row_len(row1) : 0u;
         off2 = off1;
         src2 = ev_row_src(row1);
         if (off2 + ln2 > io.samples_cap) ln2 = 0;
-        offset2 = rp->offset;
-        clo2 = rc->clo; chi2 = rc->chi; scale2 = rc->scale;
+        {   // scale | offset and clo | chi: two loads from one 32-byte sector
+            const double2 so = *reinterpret_cast<const double2 *>(&rc->scale);
+            const int2 cc = *reinterpret_cast<const int2 *>(&rc->clo);
+            scale2 = so.x; offset2 = so.y; clo2 = cc.x; chi2 = cc.y;
+        }
         if (SCALING) { med2 = rc->med; mad2 = rc->mad; }
         // raw samples: the 16-byte chunks that hold [src, src + ln), at most GATHER_CH of them, packed behind the chunks of
         // the lanes in front (a warp scan places them); what does not fit the batch's staging area, or lies in the last
@@ -570,7 +574,10 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
             ev.gstart = gstart; ev.len = ln; ev.rel = rel;
             const uint32_t fast = ((__double_as_longlong(mad2) & 0x000FFFFFFFFFFFFFll) != 0x000FFFFFFFFFFFFFll) ? 1u : 0u;
             ev.packed = sidx2 | (nst2 << 11) | (fast << 19) | (par << 20);
-            S.ev[lane] = ev;
+            const uint4 *q = reinterpret_cast<const uint4 *>(&ev);      // the 64 bytes of payload (48 without Med-MAD), not the padding
+            uint4 *d = reinterpret_cast<uint4 *>(&S.ev[lane]);
+            d[0] = q[0]; if (SCALING) d[1] = q[1];
+            d[2] = q[2]; d[3] = q[3];
         }
         const bool all_staged = __all_sync(PGM_FULL, nst2 == ln);   // no event of the batch longer than its staged copy
         cp_async_wait_all();      // this batch's raw samples (issued a batch ago) have landed
