@@ -459,7 +459,11 @@ static SortPlan sort_plan(const pgm_ctx *c) {
     p.bits = bit_length(c->opts.n_slots - 1);
     if (p.bits == 0) p.bits = 1;
     if (p.bits <= SORT_MAX_BITS) { p.hi_bits = 0; p.lo_bits = p.bits; p.first_bits = p.bits; p.first_shift = 0; }
-    else { p.hi_bits = (p.bits + 1) / 2; p.lo_bits = p.bits - p.hi_bits; p.first_bits = p.hi_bits; p.first_shift = p.lo_bits; }
+    else {
+        p.hi_bits = (p.bits + 1) / 2;
+        if (const char *e = getenv("PGM_MSD_HI_BITS")) { const int v = atoi(e); if (v >= (int)p.bits - MSD_MAX_LO_BITS && v >= 1 && v <= SORT_MAX_BITS && v < (int)p.bits) p.hi_bits = (uint32_t)v; }
+        p.lo_bits = p.bits - p.hi_bits; p.first_bits = p.hi_bits; p.first_shift = p.lo_bits;
+    }
     return p;
 }
 
