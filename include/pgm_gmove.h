@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define PGM_ABI_VERSION 3
+#define PGM_ABI_VERSION 4   /* v4 (round 2): pgm_submit / pgm_wait, pgm_create_sibling, pgm_summary, pgm_model_log*, pgm_format_noalloc */
 
 /* ---- status codes ---- */
 #define PGM_OK 0
@@ -256,12 +256,12 @@ uint64_t pgm_launch_count(const pgm_ctx *ctx);
  * pgm_profile_enable(ctx, 1) starts bracketing every stage with an event pair;
  * pgm_profile_read synchronises, adds up the elapsed time and launch count of every stage since
  * the last read into ms[PGM_N_STAGES] / launches[PGM_N_STAGES], and clears the record. */
-#define PGM_STAGE_PREP 0         /* k_read_prep, k_oor_check                                       */
-#define PGM_STAGE_DECODE_COUNT 1 /* k_decode: alignment -> events, filters, per-k-mer counts      */
-#define PGM_STAGE_SCAN 2         /* prefix sums outside the sort                                   */
-#define PGM_STAGE_PLACE 3        /* k_scan_records, k_place: events into batch-wide order          */
-#define PGM_STAGE_SORT 4         /* radix sort passes (histogram, scan, scatter)                   */
-#define PGM_STAGE_SELECT 5       /* k_select_prep, k_select                                        */
+#define PGM_STAGE_PREP 0         /* k_read_prep, k_order, k_oor_check                              */
+#define PGM_STAGE_DECODE_COUNT 1 /* k_decode_moves / k_decode: alignment -> event rows, filters, per-k-mer counts */
+#define PGM_STAGE_SCAN 2         /* k_scan_sel (sample offsets of the selected events)             */
+#define PGM_STAGE_PLACE 3        /* k_scan_records, k_tile_hist: dense order of the passing events */
+#define PGM_STAGE_SORT 4         /* k_scan_hist, k_rank | k_msd_scatter + k_msd_rank               */
+#define PGM_STAGE_SELECT 5       /* k_quota (per-k-mer quota, bucket and selection bases)          */
 #define PGM_STAGE_STATS 6        /* k_stats (+ k_stats_wide): exact Med-MAD of every record that owns a selected event */
 #define PGM_STAGE_GATHER 7       /* k_gather: the selected samples as doubles, in output order     */
 #define PGM_STAGE_MISC 8         /* memsets                                                        */

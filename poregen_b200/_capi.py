@@ -17,7 +17,7 @@ PGM_MODE_MOVES_CHAR, PGM_MODE_SS, PGM_MODE_MOVES_I8 = 0, 1, 2
 PGM_READ_RNA, PGM_READ_SKIP = 1, 2
 PGM_RF_SKIPPED, PGM_RF_BAD_ALIGN, PGM_RF_BAD_CALIB = 1, 2, 4
 PGM_OUT_F64, PGM_OUT_TEXT, PGM_OUT_TEXT_ONLY = 0, 1, 2
-PGM_ABI_VERSION = 3
+PGM_ABI_VERSION = 4
 
 
 class PgmOpts(C.Structure):
