@@ -527,16 +527,22 @@ def run_own_arm(args):
                 eng.set_gathered(all_counts.data_ptr(), world, rank)
             eng.emit()
             eng.model_log()
+        mt = {}
+        if world > 1:   # NCCL opens its peer-to-peer channels on the first all-to-all: not part of the aggregation
+            w_in = torch.zeros(world * 1024, dtype=torch.int64, device=dev)
+            w_out = torch.empty_like(w_in)
+            dist.all_to_all_single(w_out, w_in)
+            torch.cuda.synchronize(dev)
         barrier()
         tm0 = time.perf_counter()
-        rows = eng.model_finalize(3.1) if world == 1 else model_exchange(eng, opts, world, rank, 3.1, dev)
+        rows = eng.model_finalize(3.1) if world == 1 else model_exchange(eng, opts, world, rank, 3.1, dev, timings=mt)
         barrier()
         model_s = time.perf_counter() - tm0
         tmx = torch.tensor([model_s], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tmx, op=dist.ReduceOp.MAX)
         model_info = {"ms": float(tmx.item()) * 1e3, "values": int(rows["n"].sum()), "rows": int(rows.size),
-                      "rows_with_stddev": int(np.isfinite(rows["stddev"]).sum()),
+                      "rows_with_stddev": int(np.isfinite(rows["stddev"]).sum()), "rank0_breakdown": mt or None,
                       "how": "pgm_model_finalize (median by int64 radix selection + exact 128-bit variance per k-mer)" if world == 1 else
                              "NCCL all-to-all of the logged values by k-mer range, pgm_model_finalize on the owners, all-gather of the rows"}
     eng.close()

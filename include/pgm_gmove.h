@@ -88,7 +88,10 @@ typedef struct pgm_opts {
     const char *kmer_list;        /* NULL: k-mers are the lexicographic ACGT/ACGU enumeration
                                      (poregen.cpp:248-267) and slot s is id index_lo+s.
                                      else: n_slots*kmer_size chars, the --kmer_file lines of the
-                                     dumped range in order (gmove.cpp:395-419); must be unique.   */
+                                     dumped range in order (gmove.cpp:395-419). A line that repeats
+                                     an earlier one gets a slot that stays empty: the FIRST slot of
+                                     a k-mer string takes its events (the reference keys files and
+                                     counts by the string, so repeats share one of each).           */
 } pgm_opts;
 
 /* One alignment record. 88 bytes, no padding. */

@@ -385,6 +385,7 @@ struct Gpu {
     pgm_ctx *ctx = nullptr;
     pgm_result res;
     uint32_t r0 = 0, r1 = 0;   // records of the batch this GPU owns
+    std::vector<uint32_t> live_prefix;   // -d: non-skipped records among the first i of this GPU's share (write_batch)
 };
 
 struct Run {
@@ -395,6 +396,7 @@ struct Run {
     bool device_signal = false;         // BLOW5 with signal_press svb-zd: the streams are decoded by k_svb_decode
     std::vector<Gpu> gpus;
     std::vector<uint32_t> totals;       // kmer_frequency_map of the dumped range
+    std::vector<uint32_t> first_slot;   // slot -> first slot with the same k-mer string (itself unless a --kmer_file repeats a line)
     uint32_t n_slots = 0;
     uint32_t mode = PGM_MODE_MOVES_CHAR;
     uint64_t n_records = 0, n_samples = 0, n_examined = 0, n_selected = 0;
@@ -585,6 +587,13 @@ void check(pgm_ctx *c, int rc) {
 void write_batch(Run &R, const Batch &b) {
     const Opt &o = R.opt;
     std::string out;
+    if (o.delimit_files)
+        for (Gpu &g : R.gpus) {
+            const pgm_result &r = g.res;
+            g.live_prefix.assign((size_t)r.n_reads + 1, 0);
+            if (g.r1 == g.r0) continue;
+            for (uint32_t rec = 0; rec < r.n_reads; rec++) g.live_prefix[rec + 1] = g.live_prefix[rec] + ((r.read_flags[rec] & PGM_RF_SKIPPED) ? 0u : 1u);
+        }
     for (uint32_t s = 0; s < R.n_slots; s++) {
         out.clear();
         uint32_t count = R.totals[s];            // before this batch
@@ -599,16 +608,23 @@ void write_batch(Run &R, const Batch &b) {
                 const uint64_t *lo = std::lower_bound(r.ev_text_off, r.ev_text_off + r.n_sel_events, t0);
                 e0 = (uint64_t)(lo - r.ev_text_off);
             }
-            uint64_t e = e0;
+            // Walk the slot's events once; between two of them the records without an event of this slot only contribute their
+            // ':' (live = not skipped), counted from the prefix sums made once per batch (not one pass over the records per slot).
             const uint64_t e1 = e0 + r.slot_sel[s];
-            for (uint32_t rec = 0; rec < r.n_reads; rec++) {
+            const std::vector<uint32_t> &live = g.live_prefix;          // live[rec] = non-skipped records among [0, rec)
+            uint32_t done = 0;                                          // records whose ':' decision has been made
+            for (uint64_t e = e0; e < e1;) {
+                const uint32_t rec = r.ev_read[e];
+                if (o.sample_limit == 0 || count < o.sample_limit) out.append((size_t)(live[rec] - live[done]), ':');
                 while (e < e1 && r.ev_read[e] == rec) {
                     out.append(r.text + r.ev_text_off[e], (size_t)(r.ev_text_off[e + 1] - r.ev_text_off[e]));
                     e++; count++;
                 }
                 // a file is closed only by the emission that reaches the limit (gmove.cpp:680-684); with limit 0 never
                 if (!(r.read_flags[rec] & PGM_RF_SKIPPED) && (o.sample_limit == 0 || count < o.sample_limit)) out.push_back(':');
+                done = rec + 1;
             }
+            if (o.sample_limit == 0 || count < o.sample_limit) out.append((size_t)(live[r.n_reads] - live[done]), ':');
         }
         if (out.empty()) continue;
         const std::string path = R.dump_dir + "/" + R.kmers[o.index_start - 1 + s];
@@ -920,6 +936,11 @@ int gmove(int argc, char *argv[]) {
         }
     }
     R.totals.assign(R.n_slots, 0);
+    R.first_slot.resize(R.n_slots);
+    {
+        std::unordered_map<std::string, uint32_t> seen;
+        for (uint32_t s = 0; s < R.n_slots; s++) R.first_slot[s] = seen.emplace(kmers[opt.index_start - 1 + s], s).first->second;
+    }
 
     if (opt.scaling == 0) fprintf(stderr, "scaling: %s\n", "no scale");
     else if (opt.scaling == 1) fprintf(stderr, "scaling: %s\n", "medmad scale");
@@ -1010,7 +1031,7 @@ int gmove(int argc, char *argv[]) {
             process_batch(R, batch);
             est = 0;
             bool all_full = R.n_slots == kmers.size();                         // gmove.cpp:558: every k-mer complete
-            for (uint32_t s = 0; all_full && s < R.n_slots; s++) all_full = opt.sample_limit != 0 && R.totals[s] >= opt.sample_limit;
+            for (uint32_t s = 0; all_full && s < R.n_slots; s++) all_full = opt.sample_limit != 0 && R.totals[R.first_slot[s]] >= opt.sample_limit;
             if (all_full) break;
         }
     }
@@ -1023,7 +1044,8 @@ int gmove(int argc, char *argv[]) {
     const std::string freq = std::string(output_dir) + "/freq.txt";
     FILE *ff = fopen(freq.c_str(), "w");
     if (!ff) { fprintf(stderr, "Error in opening %s\n", freq.c_str()); exit(EXIT_FAILURE); }
-    for (uint32_t s = 0; s < R.n_slots; s++) fprintf(ff, "%s\t%" PRIu64 "\n", kmers[opt.index_start - 1 + s].c_str(), (uint64_t)R.totals[s]);
+    // one line per k-mer LINE (gmove.cpp:525-534 walks the list); repeated lines of a --kmer_file share the string's one count
+    for (uint32_t s = 0; s < R.n_slots; s++) fprintf(ff, "%s\t%" PRIu64 "\n", kmers[opt.index_start - 1 + s].c_str(), (uint64_t)R.totals[R.first_slot[s]]);
     fclose(ff);
     if (opt.model_out) {
         const pgm_model_row *rows = nullptr;

@@ -412,8 +412,8 @@ int pgm_create(const pgm_opts *opts, int device, void *stream, pgm_ctx **out) {
                 id = (id << 2) | code;
             }
             if (!ok) continue;
-            if (lut[id] != PGM_INVALID) { c->err = "duplicate k-mer in kmer_list"; return bail(PGM_ERR_ARG); }
-            lut[id] = s;
+            if (lut[id] != PGM_INVALID) continue;   // a repeated line: the reference's std::map keeps ONE file and ONE count per k-mer string
+            lut[id] = s;                            // (gmove.cpp:460-473): the first slot of the string takes the events, the others stay empty
         }
         if ((rc = ensure(c, c->lut, n_ids * 4)) != PGM_OK) return bail(rc);
         if (cudaMemcpy(c->lut.p, lut.data(), n_ids * 4, cudaMemcpyHostToDevice) != cudaSuccess) { c->err = "LUT upload failed"; return bail(PGM_ERR_CUDA); }

@@ -288,7 +288,7 @@ def model_merge_local(engines, opts: GmoveOptions, stddev_limit: float) -> np.nd
     return rows
 
 
-def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, stddev_limit: float, device) -> np.ndarray:
+def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, stddev_limit: float, device, timings: Optional[dict] = None) -> np.ndarray:
     """One process per GPU: NCCL all-to-all of the logged values by k-mer range (torch.distributed on the log's device
     memory), pgm_model_finalize on the owner, all-gather of the rows. Every rank returns all rows. Collective."""
     import torch
@@ -297,6 +297,14 @@ def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, 
     class _Dev:
         def __init__(self, ptr, n):
             self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (ptr, False), "version": 3}
+
+    import time
+    tm = {"counts_s": 0.0, "values_s": 0.0, "append_s": 0.0, "finalize_s": 0.0, "rows_s": 0.0, "bytes_sent": 0}
+
+    def lap(key, t0):
+        torch.cuda.synchronize(device)
+        tm[key] += time.perf_counter() - t0
+        return time.perf_counter()
 
     NS = eng.n_slots
     ranges = model_owner_ranges(NS, world)
@@ -309,6 +317,7 @@ def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, 
     try:
         agg.model_begin()
         for r in range(n_rounds):
+            t0 = time.perf_counter()
             ptr, so = eng.model_log_entry(r)
             # per-k-mer counts of every owner's range travel first (NS int64 in, my range from every rank out)
             cnt = torch.from_numpy(np.diff(so).astype(np.int64)).to(device)
@@ -318,17 +327,22 @@ def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, 
             got_cnt = got_cnt.view(world, hi - lo)
             recv_n = got_cnt.sum(dim=1).cpu().tolist()
             send_n = [int(so[b] - so[a]) for a, b in ranges]
+            t0 = lap("counts_s", t0)
             n_mine = int(so[-1])
             vals = torch.as_tensor(_Dev(ptr, n_mine), device=device) if n_mine else torch.empty(0, dtype=torch.int64, device=device)
             recv = torch.empty(int(sum(recv_n)), dtype=torch.int64, device=device)
             dist.all_to_all_single(recv, vals, output_split_sizes=[int(x) for x in recv_n], input_split_sizes=send_n)
-            torch.cuda.synchronize(device)
+            tm["bytes_sent"] += 8 * (n_mine - send_n[rank])
+            t0 = lap("values_s", t0)
             cnt_host = got_cnt.cpu().numpy()
             at = 0
             for g in range(world):
                 agg.model_log_append(recv.data_ptr() + 8 * at, _piece_table(cnt_host[g], lo, hi, NS))
                 at += int(recv_n[g])
+            t0 = lap("append_s", t0)
+        t0 = time.perf_counter()
         mine = agg.model_finalize(stddev_limit)[lo:hi]
+        t0 = lap("finalize_s", t0)
     finally:
         agg.close()
     # rows of every range to every rank (byte view: 40 bytes per row)
@@ -342,4 +356,7 @@ def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, 
     rows = np.zeros(NS, np.dtype(capi.MODEL_ROW_DTYPE))
     for g, (a, b) in enumerate(ranges):
         rows[a:b] = allr[g, :b - a]
+    lap("rows_s", t0)
+    if timings is not None:
+        timings.update(tm)
     return rows

@@ -77,7 +77,12 @@ _LIVE = [
     ("ss_rna_delimit", SynthConfig(n_reads=40, median_samples=3000, mode=capi.PGM_MODE_SS, p_del=0.05, p_ins=0.05, rna_orientation=True, seed=33),
      dict(kmer_size=5, sample_limit=10, scaling=1, rna=True, delimit_files=True)),
     ("sam_delimit", SynthConfig(n_reads=40, median_samples=3000, mode=capi.PGM_MODE_MOVES_I8, seed=34), dict(kmer_size=5, sample_limit=25, delimit_files=True)),
-]
+    # a --kmer_file that repeats lines: the reference keys files and counts by the k-mer string (std::map, gmove.cpp:460-473), so the
+    # repeats share one file and one count, and freq.txt prints that count on every one of the lines
+    ("tsv_kmer_file_repeated_lines", SynthConfig(n_reads=30, median_samples=3000, seed=35),
+     dict(kmer_size=3, sample_limit=12, kmer_list=["AAC", "ACG", "AAC", "GGT", "ACG", "TTT", "AAC"], file_limit=7, index_end=7)),
+]   # (with files still open at the end - e.g. --sample_limit 0 - the reference fclose()s the repeated string's FILE* once per line and
+    #  aborts in free(): undefined there; every k-mer of the case above reaches its limit, which closes each file once)
 
 
 @pytest.mark.parametrize("label,cfg,kw", _LIVE, ids=[c[0] for c in _LIVE])
