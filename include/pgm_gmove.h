@@ -311,6 +311,9 @@ int pgm_model_log(pgm_ctx *ctx);
 int pgm_model_log_size(pgm_ctx *ctx, uint32_t *n_batches);
 int pgm_model_log_entry(pgm_ctx *ctx, uint32_t i, const int64_t **vals_dev, const uint64_t **slot_off_host);
 int pgm_model_log_append(pgm_ctx *ctx, const int64_t *vals_dev, uint64_t n_vals, const uint64_t *slot_off_host);
+/* Room for n_vals_total logged values in all (the log grows by reallocation otherwise: an owner that is about to append the
+ * pieces of every rank and round knows the total from the exchanged counts and asks for it once). */
+int pgm_model_log_reserve(pgm_ctx *ctx, uint64_t n_vals_total);
 
 /* Dwell medians (reference scripts/poregen.sh:33-52, calculate_dwell_times_medians): per dump file, `datamash
  * median` over the comma counts of its ';'-separated fields = (event length - 1) of every event, plus one 0 for the empty field

@@ -120,7 +120,7 @@ SYMBOLS = [
     "pgm_counts_host", "pgm_totals_host", "pgm_set_prior_host", "pgm_alloc_pinned", "pgm_free_pinned", "pgm_device_count",
     "pgm_set_gathered", "pgm_model_begin", "pgm_model_finalize", "pgm_warmup", "pgm_upload_svb", "pgm_debug_raw", "pgm_model_dwell", "pgm_summary", "pgm_submit", "pgm_wait", "pgm_create_sibling",
     "pgm_model_log", "pgm_model_log_size", "pgm_model_log_entry", "pgm_model_log_append",
-    "pgm_format_noalloc",
+    "pgm_format_noalloc", "pgm_model_log_reserve",
 ]
 PGM_NOALLOC_MAX_VALUES = 1 << 24
 PGM_N_STAGES = 11
@@ -209,5 +209,7 @@ def load() -> C.CDLL:
     lib.pgm_debug_format.restype = C.c_int
     lib.pgm_format_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p]
     lib.pgm_format_noalloc.restype = C.c_int
+    lib.pgm_model_log_reserve.argtypes = [C.c_void_p, C.c_uint64]
+    lib.pgm_model_log_reserve.restype = C.c_int
     _lib = lib
     return lib

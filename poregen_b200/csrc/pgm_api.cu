@@ -1190,6 +1190,14 @@ int pgm_model_log_append(pgm_ctx *c, const int64_t *vals_dev, uint64_t n_vals, c
     return PGM_OK;
 }
 
+int pgm_model_log_reserve(pgm_ctx *c, uint64_t n_vals_total) {
+    if (!c) return PGM_ERR_ARG;
+    if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_log_reserve needs pgm_model_begin first");
+    CU(c, cudaSetDevice(c->device));
+    if (n_vals_total <= c->model_vals_used) return PGM_OK;
+    return arena_reserve(c, c->model_vals, c->model_vals_used, n_vals_total - c->model_vals_used, 8);
+}
+
 int pgm_model_dwell(pgm_ctx *c, const int64_t **twice_median_out) {
     if (!c || !twice_median_out) return PGM_ERR_ARG;
     if (!c->model_on) return fail(c, PGM_ERR_STATE, "pgm_model_dwell needs pgm_model_begin first");

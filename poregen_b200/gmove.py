@@ -206,6 +206,9 @@ class GmoveEngine:
         assert so.size == self.n_slots + 1
         self._chk(self.lib.pgm_model_log_append(self._ctx, C.c_void_p(vals_ptr), int(so[-1] - so[0]), so.ctypes.data))
 
+    def model_log_reserve(self, n_vals_total: int):
+        self._chk(self.lib.pgm_model_log_reserve(self._ctx, int(n_vals_total)))
+
     def model_dwell(self) -> np.ndarray:
         """Twice the per-k-mer dwell median over everything logged since model_begin (scripts/poregen.sh:33-52); -1: no event."""
         p = C.c_void_p()
@@ -316,25 +319,33 @@ def model_exchange(eng: GmoveEngine, opts: GmoveOptions, world: int, rank: int, 
     agg = GmoveEngine(opts, device=device.index)
     try:
         agg.model_begin()
+        # phase 1: the per-k-mer counts of every owner's range, all rounds (NS int64 in, my range from every rank out per round):
+        # the owner then knows how many values it will hold and reserves the log once
+        t0 = time.perf_counter()
+        in_split = [b - a for a, b in ranges]
+        entries, got_cnts = [], []
         for r in range(n_rounds):
-            t0 = time.perf_counter()
             ptr, so = eng.model_log_entry(r)
-            # per-k-mer counts of every owner's range travel first (NS int64 in, my range from every rank out)
+            entries.append((ptr, so))
             cnt = torch.from_numpy(np.diff(so).astype(np.int64)).to(device)
-            in_split = [b - a for a, b in ranges]
             got_cnt = torch.empty(world * (hi - lo), dtype=torch.int64, device=device)
             dist.all_to_all_single(got_cnt, cnt, output_split_sizes=[hi - lo] * world, input_split_sizes=in_split)
-            got_cnt = got_cnt.view(world, hi - lo)
-            recv_n = got_cnt.sum(dim=1).cpu().tolist()
+            got_cnts.append(got_cnt.view(world, hi - lo))
+        cnt_hosts = [g.cpu().numpy() for g in got_cnts]
+        agg.model_log_reserve(int(sum(int(c.sum()) for c in cnt_hosts)))
+        t0 = lap("counts_s", t0)
+        # phase 2: the values, one all-to-all per round; the received pieces are appended in (round, rank) = job order
+        for r in range(n_rounds):
+            ptr, so = entries[r]
+            cnt_host = cnt_hosts[r]
+            recv_n = [int(x) for x in cnt_host.sum(axis=1)]
             send_n = [int(so[b] - so[a]) for a, b in ranges]
-            t0 = lap("counts_s", t0)
             n_mine = int(so[-1])
             vals = torch.as_tensor(_Dev(ptr, n_mine), device=device) if n_mine else torch.empty(0, dtype=torch.int64, device=device)
             recv = torch.empty(int(sum(recv_n)), dtype=torch.int64, device=device)
-            dist.all_to_all_single(recv, vals, output_split_sizes=[int(x) for x in recv_n], input_split_sizes=send_n)
+            dist.all_to_all_single(recv, vals, output_split_sizes=recv_n, input_split_sizes=send_n)
             tm["bytes_sent"] += 8 * (n_mine - send_n[rank])
             t0 = lap("values_s", t0)
-            cnt_host = got_cnt.cpu().numpy()
             at = 0
             for g in range(world):
                 agg.model_log_append(recv.data_ptr() + 8 * at, _piece_table(cnt_host[g], lo, hi, NS))
