@@ -294,6 +294,28 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
 
 // k_msd_scatter (first pass): stable split of the batch by the HIGH digit of the slot.
 // rows_out[pos], pos = (events of lower high digits) + (events of the same high digit in earlier tiles) + rank in tile.
+// Bulk copies (TMA, cp.async.bulk -> SASS UBLKCP) with an mbarrier (SYNCS) as the completion signal: one thread asks for a whole
+// tile of rows, the copy engine writes it into shared memory, the CTA waits on the barrier's phase.
+__device__ __forceinline__ uint32_t sort_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(sort_smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(sort_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(sort_smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_load(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {   // 16-byte aligned, bytes % 16 == 0
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(sort_smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(sort_smem_u32(bar)) : "memory");
+}
+
 struct MsdScatterIO {
     const uint32_t *n_events;
     EvSource src;
@@ -303,29 +325,65 @@ struct MsdScatterIO {
 };
 
 __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) {
-    extern __shared__ __align__(16) uint32_t sm_rank[];
+    extern __shared__ __align__(128) uint32_t sm_rank[];
     __shared__ EvTile sm_tile;
+    __shared__ __align__(8) uint64_t sm_bar;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.bits;
-    uint32_t *wcount = sm_rank;                          // [RANK_WARPS][bins]
-    uint32_t *goff = sm_rank + RANK_WARPS * bins;         // [bins]
+    uint4 *tile_rows = reinterpret_cast<uint4 *>(sm_rank);               // [SORT_TILE] the tile's rows, written by the copy engine
+    uint32_t *wcount = sm_rank + SORT_TILE * 4;          // [RANK_WARPS][bins]
+    uint32_t *goff = wcount + RANK_WARPS * bins;          // [bins]
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t used_tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    if (blockIdx.x >= used_tiles) return;
+    if (threadIdx.x == 0) mbar_init(&sm_bar, 1);
+    uint32_t phase = 0;
+    // A tile of long records is one to EV_SEGS contiguous stretches of the temporaries (sm_tile's segment table): one thread
+    // asks the copy engine for them (bulk copies, one mbarrier for the lot) and the tile arrives in dense order in shared
+    // memory while the CTA ranks the tile before it. Tiles that touch more records are fetched row by row (ev_fetch).
+    auto bulk_tile = [&]() { return sm_tile.r_hi - sm_tile.r_lo < EV_SEGS; };
+    auto request = [&](uint32_t base, uint32_t end) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the generic-proxy reads of the buffer come first
+        mbar_expect_tx(&sm_bar, (end - base) * 16u);
+#pragma unroll
+        for (int k = 0; k < EV_SEGS; k++) {
+            const uint32_t lo = max(base, sm_tile.seg_start[k]);
+            const uint32_t hi = min(end, (k + 1 < EV_SEGS) ? sm_tile.seg_start[k + 1] : 0xffffffffu);
+            if (lo < hi) bulk_load(tile_rows + (lo - base), io.src.rows_tmp + (size_t)((long long)lo + sm_tile.seg_delta[k]), (hi - lo) * 16u, &sm_bar);
+        }
+    };
+    bool bulk;                                            // this tile arrives by bulk copy (read while sm_tile is stable: behind the set-up's barrier)
+    {   // prologue: the first tile
+        const uint32_t base = blockIdx.x * SORT_TILE, end = min(n, base + SORT_TILE);
+        ev_tile_setup(io.src, base, end, &sm_tile);       // (its barrier also publishes the mbarrier's initialisation)
+        bulk = bulk_tile();
+        if (threadIdx.x == 0 && bulk) request(base, end);
+    }
     for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < RANK_WARPS * bins; i += RANK_BLOCK) wcount[i] = 0;
         for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)tile * bins + i];
         const uint32_t base = tile * SORT_TILE, end = min(n, base + SORT_TILE);
-        ev_tile_setup(io.src, base, end, &sm_tile);
         const uint32_t wbase = base + w * (32 * RANK_ITEMS);
         const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * RANK_ITEMS)) : 0u;
         uint4 row[RANK_ITEMS];
         uint32_t dig[RANK_ITEMS], lrank[RANK_ITEMS];
+        if (bulk) { mbar_wait(&sm_bar, phase); phase ^= 1; }
 #pragma unroll
         for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
-            row[rd] = (idx < end) ? ev_fetch(io.src, sm_tile, idx) : make_uint4(0, 0, 0, 0);
+            row[rd] = (idx >= end) ? make_uint4(0, 0, 0, 0) : bulk ? tile_rows[idx - base] : ev_fetch(io.src, sm_tile, idx);
             dig[rd] = (row[rd].x >> io.shift) & (bins - 1);
+        }
+        {   // the next tile's segment table and copies: its rows stream in under this tile's ranking and scatter
+            const uint32_t next = tile + gridDim.x;
+            if (next < used_tiles) {
+                if (!bulk) __syncthreads();               // row-by-row fetches read sm_tile: all of them first
+                const uint32_t nbase = next * SORT_TILE, nend = min(n, nbase + SORT_TILE);
+                ev_tile_setup(io.src, nbase, nend, &sm_tile);     // its barrier: every thread holds its rows, the buffer is free
+                bulk = bulk_tile();                       // of the NEXT tile (this tile's rows are in registers)
+                if (threadIdx.x == 0 && bulk) request(nbase, nend);
+            }
         }
         tile_rank<RANK_ITEMS>(dig, nvw, bins, wcount, lrank);
         __syncthreads();
@@ -346,7 +404,7 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
         }
     }
 }
-#define MSD_SCATTER_SMEM(bits) ((size_t)(RANK_WARPS + 1) * (1u << (bits)) * 4)
+#define MSD_SCATTER_SMEM(bits) ((size_t)SORT_TILE * 16 + (size_t)(RANK_WARPS + 1) * (1u << (bits)) * 4)
 
 // ------------------------------------------------------------------------------------------------
 // k_msd_rank (second pass): one CTA per high-digit bucket at a time. The bucket is the contiguous range
@@ -365,16 +423,28 @@ struct MsdRankIO {
 };
 
 __global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO io) {
-    extern __shared__ __align__(16) uint32_t sm_rank[];
+    extern __shared__ __align__(128) uint32_t sm_rank[];
     __shared__ uint32_t sm_bucket;
+    __shared__ __align__(8) uint64_t sm_bar;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.lo_bits, mask = bins - 1;
-    uint32_t *wcount = sm_rank;                          // [MSD_WARPS][bins]
-    uint32_t *cnt = sm_rank + MSD_WARPS * bins;          // [bins] events of the slot so far
+    uint4 *tile_rows = reinterpret_cast<uint4 *>(sm_rank);                 // [MSD_TILE] the tile's rows, written by the copy engine
+    uint32_t *wcount = sm_rank + MSD_TILE * 4;           // [MSD_WARPS][bins]
+    uint32_t *cnt = wcount + MSD_WARPS * bins;           // [bins] events of the slot so far
     uint32_t *keep_s = cnt + bins, *selb_s = keep_s + bins;
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t n_buckets = (io.n_slots + bins - 1) >> io.lo_bits;
     if (n == 0) return;                                  // nothing was scanned: the histogram holds no bucket starts
+    if (threadIdx.x == 0) mbar_init(&sm_bar, 1);
+    uint32_t phase = 0;
+    // one thread asks the copy engine for the rows [base, end) of the bucket; the tile buffer must be free (all rows of the
+    // previous tile are in registers: the callers stand behind a block barrier)
+    auto request = [&](uint32_t base, uint32_t end) {
+        const uint32_t bytes = (end - base) * 16u;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the generic-proxy reads of the buffer come first
+        mbar_expect_tx(&sm_bar, bytes);
+        bulk_load(tile_rows, io.rows_in + base, bytes, &sm_bar);
+    };
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) sm_bucket = atomicAdd(io.ticket, 1u);
@@ -384,6 +454,9 @@ __global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO 
         const uint32_t start = io.hist_scanned[h];
         const uint32_t stop = (h + 1 < (1u << io.hi_bits)) ? io.hist_scanned[h + 1] : n;
         if (start >= stop) continue;
+        // the bucket's first tile is asked for while its slot tables load (the barriers above: the previous bucket's last tile
+        // has left the buffer, and the mbarrier's initialisation is visible)
+        if (threadIdx.x == 0) request(start, min(stop, start + MSD_TILE));
         const uint32_t slot0 = h << io.lo_bits;
         for (uint32_t i = threadIdx.x; i < bins; i += MSD_BLOCK) {
             const uint32_t s = slot0 + i;
@@ -399,12 +472,15 @@ __global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO 
             const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * MSD_ITEMS)) : 0u;
             uint4 row[MSD_ITEMS];
             uint32_t dig[MSD_ITEMS], lrank[MSD_ITEMS];
+            mbar_wait(&sm_bar, phase);                    // the tile asked for one tile ago (or at the bucket's start) has landed
+            phase ^= 1;
 #pragma unroll
-            for (int rd = 0; rd < MSD_ITEMS; rd++) {   // the loads are on their way while the counters are cleared
+            for (int rd = 0; rd < MSD_ITEMS; rd++) {
                 const uint32_t idx = wbase + rd * 32 + lane;
-                row[rd] = (idx < end) ? __ldg(io.rows_in + idx) : make_uint4(0, 0, 0, 0);
+                row[rd] = (idx < end) ? tile_rows[idx - base] : make_uint4(0, 0, 0, 0);
             }
             __syncthreads();
+            if (threadIdx.x == 0 && end < stop) request(end, min(stop, end + MSD_TILE));   // the next tile streams in under the ranking
 #pragma unroll
             for (int rd = 0; rd < MSD_ITEMS; rd++) dig[rd] = row[rd].x & mask;
             tile_rank<MSD_ITEMS>(dig, nvw, bins, wcount, lrank);
@@ -435,7 +511,7 @@ __global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO 
         }
     }
 }
-#define MSD_RANK_SMEM(lo_bits) ((size_t)(MSD_WARPS + 3) * (1u << (lo_bits)) * 4)
+#define MSD_RANK_SMEM(lo_bits) ((size_t)MSD_TILE * 16 + (size_t)(MSD_WARPS + 3) * (1u << (lo_bits)) * 4)
 
 // Selected rows -> the structure-of-arrays form of pgm_result (ev_start / ev_len / ev_read), for callers that download them.
 // ev_start is relative to the record's first sample after trim (rec_src0, k_read_prep).
