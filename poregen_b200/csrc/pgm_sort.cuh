@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
                 ev_tile_setup(io.src, nbase, nend, &sm_tile);     // its barrier: every thread holds its rows, the buffer is free
                 bulk = bulk_tile();                       // of the NEXT tile (this tile's rows are in registers)
                 if (threadIdx.x == 0 && bulk) request(nbase, nend);
-            }
+            } else __syncthreads();                       // the counters are cleared (by all threads, across the warps' rows) before any warp counts
         }
         tile_rank<RANK_ITEMS>(dig, nvw, bins, wcount, lrank);
         __syncthreads();
