@@ -143,3 +143,27 @@ def test_medmad_long_records(built, flat):
     with GmoveEngine(opts) as eng:
         res = eng.process(batch)
     assert_same(res, ref, "long")
+
+
+def test_two_digit_sort_many_sizes(built):
+    """The two-digit path (k = 9, 262,144 slots: k_msd_scatter + k_msd_rank with bulk-copied tiles) over batch sizes from a
+    handful of events to a few tiles per CTA, each repeated: partial last tiles, CTAs with one tile and with several,
+    tiles that span many short records (row-by-row path) next to tiles of long ones (bulk path), quota binding or not.
+    Timing-dependent faults (a missing barrier showed up once in three runs) need the repetition."""
+    from cases import _o
+    from poregen_b200.synth import SynthConfig
+    rng = np.random.default_rng(99)
+    for trial in range(14):
+        n_reads = int(rng.choice([1, 2, 5, 17, 60, 200]))
+        med = int(rng.choice([2500, 9000, 40000]))
+        if n_reads * med > 2_500_000:
+            med = 9000
+        cfg = SynthConfig(n_reads=n_reads, median_samples=med, max_samples=max(40000, 2 * med), short_read_frac=float(rng.choice([0.0, 0.3])),
+                          seed=1000 + trial)
+        opts = _o(kmer_size=9, sample_limit=int(rng.choice([1, 3, 1000])))
+        batch = synth.make_batch(cfg)
+        ref = ol.oracle_run(opts, batch)
+        with GmoveEngine(opts) as eng:
+            for rep in range(3):
+                eng.reset()
+                assert_same(eng.process(batch), ref, f"trial {trial} rep {rep} ({n_reads} reads x {med})")
