@@ -31,7 +31,7 @@
 #define SORT_TILE (PGM_BLOCK * SORT_ITEMS)
 #define SORT_MAX_BITS 10
 #define SORT_MAX_BINS (1 << SORT_MAX_BITS)
-#define MSD_MAX_LO_BITS 11      // k_msd_rank: slots per high-digit bucket (shared-memory counters)
+#define MSD_MAX_LO_BITS 10      // slots per high-digit bucket (shared-memory counters beside the 64 KB tile): tables up to 2^20 slots (k = 10)
 
 // ------------------------------------------------------------------------------------------------
 // EvRow, the 16 bytes of an event:  x = slot,  y = src bits 0-31,  z = src bits 32-39 << 24 | len,  w = record.
@@ -332,7 +332,9 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
     const uint32_t bins = 1u << io.bits;
     uint4 *tile_rows = reinterpret_cast<uint4 *>(sm_rank);               // [SORT_TILE] the tile's rows, written by the copy engine
     uint32_t *wcount = sm_rank + SORT_TILE * 4;          // [RANK_WARPS][bins]
-    uint32_t *goff = wcount + RANK_WARPS * bins;          // [bins]
+    uint32_t *goff = wcount + RANK_WARPS * bins;          // [bins] first output position of the tile's rows of the digit
+    uint32_t *tile_off = goff + bins;                     // [bins] first place of the digit in the tile's digit order
+    __shared__ uint32_t sm_wsum[RANK_WARPS];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t used_tiles = (n + SORT_TILE - 1) / SORT_TILE;
     if (blockIdx.x >= used_tiles) return;
@@ -340,7 +342,9 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
     uint32_t phase = 0;
     // A tile of long records is one to EV_SEGS contiguous stretches of the temporaries (sm_tile's segment table): one thread
     // asks the copy engine for them (bulk copies, one mbarrier for the lot) and the tile arrives in dense order in shared
-    // memory while the CTA ranks the tile before it. Tiles that touch more records are fetched row by row (ev_fetch).
+    // memory while the CTA clears its counters and loads the tile's bases. Tiles that touch more records are fetched row by
+    // row (ev_fetch). (The copy of the NEXT tile under this tile's ranking was measured too: 513 -> 485 us per block; the
+    // buffer serves the coalesced write-out instead, which is worth more: 461, and 4xx with both kernels.)
     auto bulk_tile = [&]() { return sm_tile.r_hi - sm_tile.r_lo < EV_SEGS; };
     auto request = [&](uint32_t base, uint32_t end) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the generic-proxy reads of the buffer come first
@@ -352,18 +356,14 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
             if (lo < hi) bulk_load(tile_rows + (lo - base), io.src.rows_tmp + (size_t)((long long)lo + sm_tile.seg_delta[k]), (hi - lo) * 16u, &sm_bar);
         }
     };
-    bool bulk;                                            // this tile arrives by bulk copy (read while sm_tile is stable: behind the set-up's barrier)
-    {   // prologue: the first tile
-        const uint32_t base = blockIdx.x * SORT_TILE, end = min(n, base + SORT_TILE);
-        ev_tile_setup(io.src, base, end, &sm_tile);       // (its barrier also publishes the mbarrier's initialisation)
-        bulk = bulk_tile();
-        if (threadIdx.x == 0 && bulk) request(base, end);
-    }
     for (uint32_t tile = blockIdx.x; tile < used_tiles; tile += gridDim.x) {
-        __syncthreads();
+        __syncthreads();                                  // the previous tile's write-out has left the buffer and the counters
+        const uint32_t base = tile * SORT_TILE, end = min(n, base + SORT_TILE);
+        ev_tile_setup(io.src, base, end, &sm_tile);       // (its barrier also publishes the mbarrier's initialisation)
+        const bool bulk = bulk_tile();
+        if (threadIdx.x == 0 && bulk) request(base, end);
         for (uint32_t i = threadIdx.x; i < RANK_WARPS * bins; i += RANK_BLOCK) wcount[i] = 0;
         for (uint32_t i = threadIdx.x; i < bins; i += RANK_BLOCK) goff[i] = io.hist_scanned[(size_t)tile * bins + i];
-        const uint32_t base = tile * SORT_TILE, end = min(n, base + SORT_TILE);
         const uint32_t wbase = base + w * (32 * RANK_ITEMS);
         const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * RANK_ITEMS)) : 0u;
         uint4 row[RANK_ITEMS];
@@ -375,36 +375,55 @@ __global__ void __launch_bounds__(RANK_BLOCK, 2) k_msd_scatter(MsdScatterIO io) 
             row[rd] = (idx >= end) ? make_uint4(0, 0, 0, 0) : bulk ? tile_rows[idx - base] : ev_fetch(io.src, sm_tile, idx);
             dig[rd] = (row[rd].x >> io.shift) & (bins - 1);
         }
-        {   // the next tile's segment table and copies: its rows stream in under this tile's ranking and scatter
-            const uint32_t next = tile + gridDim.x;
-            if (next < used_tiles) {
-                if (!bulk) __syncthreads();               // row-by-row fetches read sm_tile: all of them first
-                const uint32_t nbase = next * SORT_TILE, nend = min(n, nbase + SORT_TILE);
-                ev_tile_setup(io.src, nbase, nend, &sm_tile);     // its barrier: every thread holds its rows, the buffer is free
-                bulk = bulk_tile();                       // of the NEXT tile (this tile's rows are in registers)
-                if (threadIdx.x == 0 && bulk) request(nbase, nend);
-            } else __syncthreads();                       // the counters are cleared (by all threads, across the warps' rows) before any warp counts
-        }
+        __syncthreads();                                  // counters cleared, every row in registers: the buffer is free for the sorted copy
         tile_rank<RANK_ITEMS>(dig, nvw, bins, wcount, lrank);
         __syncthreads();
-        for (uint32_t b = threadIdx.x; b < bins; b += RANK_BLOCK) {
-            uint32_t run = goff[b];
+        {   // per digit: the tile's first output position (-> exclusive over warps) and its first place in the tile's digit order
+            const uint32_t bpt = (bins + RANK_BLOCK - 1) / RANK_BLOCK;
+            uint32_t tsum = 0;
+            for (uint32_t kk = 0; kk < bpt; kk++) {
+                const uint32_t b = threadIdx.x * bpt + kk;
+                if (b < bins) {
+                    uint32_t run = goff[b];
 #pragma unroll
-            for (int ww = 0; ww < RANK_WARPS; ww++) {
-                const uint32_t t = wcount[ww * bins + b];
-                wcount[ww * bins + b] = run;
-                run += t;
+                    for (int ww = 0; ww < RANK_WARPS; ww++) {
+                        const uint32_t t = wcount[ww * bins + b];
+                        wcount[ww * bins + b] = run;
+                        run += t;
+                    }
+                    tile_off[b] = tsum;
+                    tsum += run - goff[b];
+                }
+            }
+            const uint32_t inc = warp_incl_scan_add(tsum);
+            if (lane == 31) sm_wsum[w] = inc;
+            __syncthreads();
+            uint32_t before = inc - tsum;
+            for (uint32_t ww = 0; ww < w; ww++) before += sm_wsum[ww];
+            for (uint32_t kk = 0; kk < bpt; kk++) {
+                const uint32_t b = threadIdx.x * bpt + kk;
+                if (b < bins) tile_off[b] += before;
             }
         }
         __syncthreads();
+        // the tile in digit order in shared memory, then out: the rows of one digit go to consecutive places of rows_out
 #pragma unroll
         for (int rd = 0; rd < RANK_ITEMS; rd++) {
             const uint32_t idx = wbase + rd * 32 + lane;
-            if (idx < end) io.rows_out[wcount[w * bins + dig[rd]] + lrank[rd]] = row[rd];
+            if (idx < end) {
+                const uint32_t d = dig[rd];
+                tile_rows[tile_off[d] + (wcount[w * bins + d] + lrank[rd] - goff[d])] = row[rd];
+            }
+        }
+        __syncthreads();
+        for (uint32_t p = threadIdx.x; p < end - base; p += RANK_BLOCK) {
+            const uint4 r = tile_rows[p];
+            const uint32_t d = (r.x >> io.shift) & (bins - 1);
+            io.rows_out[goff[d] + (p - tile_off[d])] = r;
         }
     }
 }
-#define MSD_SCATTER_SMEM(bits) ((size_t)SORT_TILE * 16 + (size_t)(RANK_WARPS + 1) * (1u << (bits)) * 4)
+#define MSD_SCATTER_SMEM(bits) ((size_t)SORT_TILE * 16 + (size_t)(RANK_WARPS + 2) * (1u << (bits)) * 4)
 
 // ------------------------------------------------------------------------------------------------
 // k_msd_rank (second pass): one CTA per high-digit bucket at a time. The bucket is the contiguous range
@@ -432,6 +451,8 @@ __global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO 
     uint32_t *wcount = sm_rank + MSD_TILE * 4;           // [MSD_WARPS][bins]
     uint32_t *cnt = wcount + MSD_WARPS * bins;           // [bins] events of the slot so far
     uint32_t *keep_s = cnt + bins, *selb_s = keep_s + bins;
+    uint32_t *cold = selb_s + bins, *tile_off = cold + bins;   // [bins] the slot's count before this tile; its first place in the tile's slot order
+    __shared__ uint32_t sm_wsum[MSD_WARPS];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t n_buckets = (io.n_slots + bins - 1) >> io.lo_bits;
     if (n == 0) return;                                  // nothing was scanned: the histogram holds no bucket starts
@@ -465,53 +486,83 @@ __global__ void __launch_bounds__(MSD_BLOCK, MSD_MIN_CTAS) k_msd_rank(MsdRankIO 
             selb_s[i] = (s < io.n_slots) ? io.sel_base[s] : 0u;
         }
         for (uint32_t base = start; base < stop; base += MSD_TILE) {
-            __syncthreads();
-            for (uint32_t i = threadIdx.x; i < MSD_WARPS * bins; i += MSD_BLOCK) wcount[i] = 0;
+            __syncthreads();                              // the previous tile's write-out has left the buffer and the counters
             const uint32_t end = min(stop, base + MSD_TILE);
+            if (threadIdx.x == 0 && base != start) request(base, end);
+            for (uint32_t i = threadIdx.x; i < MSD_WARPS * bins; i += MSD_BLOCK) wcount[i] = 0;
             const uint32_t wbase = base + w * (32 * MSD_ITEMS);
             const uint32_t nvw = (end > wbase) ? min(end - wbase, (uint32_t)(32 * MSD_ITEMS)) : 0u;
             uint4 row[MSD_ITEMS];
             uint32_t dig[MSD_ITEMS], lrank[MSD_ITEMS];
-            mbar_wait(&sm_bar, phase);                    // the tile asked for one tile ago (or at the bucket's start) has landed
+            mbar_wait(&sm_bar, phase);
             phase ^= 1;
 #pragma unroll
             for (int rd = 0; rd < MSD_ITEMS; rd++) {
                 const uint32_t idx = wbase + rd * 32 + lane;
                 row[rd] = (idx < end) ? tile_rows[idx - base] : make_uint4(0, 0, 0, 0);
+                dig[rd] = row[rd].x & mask;
             }
-            __syncthreads();
-            if (threadIdx.x == 0 && end < stop) request(end, min(stop, end + MSD_TILE));   // the next tile streams in under the ranking
-#pragma unroll
-            for (int rd = 0; rd < MSD_ITEMS; rd++) dig[rd] = row[rd].x & mask;
+            __syncthreads();                              // counters cleared, every row in registers: the buffer is free for the sorted copy
             tile_rank<MSD_ITEMS>(dig, nvw, bins, wcount, lrank);
             __syncthreads();
-            for (uint32_t b = threadIdx.x; b < bins; b += MSD_BLOCK) {   // running count of the slot, then exclusive over warps
-                uint32_t run = cnt[b];
+            // Per slot: running count (-> exclusive over warps), and where the slot's events of THIS tile start in the tile's
+            // slot-sorted order (exclusive scan over the slots; a thread owns bpt consecutive slots).
+            {
+                const uint32_t bpt = (bins + MSD_BLOCK - 1) / MSD_BLOCK;
+                uint32_t tsum = 0;
+                for (uint32_t kk = 0; kk < bpt; kk++) {
+                    const uint32_t b = threadIdx.x * bpt + kk;
+                    if (b < bins) {
+                        uint32_t run = cnt[b];
+                        cold[b] = run;
 #pragma unroll
-                for (int ww = 0; ww < MSD_WARPS; ww++) {
-                    const uint32_t t = wcount[ww * bins + b];
-                    wcount[ww * bins + b] = run;
-                    run += t;
+                        for (int ww = 0; ww < MSD_WARPS; ww++) {
+                            const uint32_t t = wcount[ww * bins + b];
+                            wcount[ww * bins + b] = run;
+                            run += t;
+                        }
+                        tile_off[b] = tsum;
+                        tsum += run - cnt[b];
+                        cnt[b] = run;
+                    }
                 }
-                cnt[b] = run;
+                const uint32_t inc = warp_incl_scan_add(tsum);
+                if (lane == 31) sm_wsum[w] = inc;
+                __syncthreads();
+                uint32_t before = inc - tsum;             // exclusive prefix of this thread's slots inside the tile
+                for (uint32_t ww = 0; ww < w; ww++) before += sm_wsum[ww];
+                for (uint32_t kk = 0; kk < bpt; kk++) {
+                    const uint32_t b = threadIdx.x * bpt + kk;
+                    if (b < bins) tile_off[b] += before;
+                }
             }
             __syncthreads();
+            // The tile in slot order, in shared memory: the rows of a slot stand together, and a slot's rows go to CONSECUTIVE
+            // places of sel[]; written out by consecutive threads they leave as whole 32/64/128-byte pieces instead of one
+            // 16-byte store per event scattered over 512 places (the scattered form cost as much as everything else in the kernel).
 #pragma unroll
             for (int rd = 0; rd < MSD_ITEMS; rd++) {
                 const uint32_t idx = wbase + rd * 32 + lane;
                 if (idx < end) {
                     const uint32_t d = dig[rd];
                     const uint32_t rank = wcount[w * bins + d] + lrank[rd];
-                    if (rank < keep_s[d]) {
-                        io.sel[selb_s[d] + rank] = row[rd];
-                        if (io.read_has_sel) io.read_has_sel[row[rd].w] = 1;
-                    }
+                    tile_rows[tile_off[d] + (rank - cold[d])] = row[rd];
+                }
+            }
+            __syncthreads();
+            for (uint32_t p = threadIdx.x; p < end - base; p += MSD_BLOCK) {
+                const uint4 r = tile_rows[p];
+                const uint32_t d = r.x & mask;
+                const uint32_t rank = cold[d] + (p - tile_off[d]);
+                if (rank < keep_s[d]) {
+                    io.sel[selb_s[d] + rank] = r;
+                    if (io.read_has_sel) io.read_has_sel[r.w] = 1;
                 }
             }
         }
     }
 }
-#define MSD_RANK_SMEM(lo_bits) ((size_t)MSD_TILE * 16 + (size_t)(MSD_WARPS + 3) * (1u << (lo_bits)) * 4)
+#define MSD_RANK_SMEM(lo_bits) ((size_t)MSD_TILE * 16 + (size_t)(MSD_WARPS + 5) * (1u << (lo_bits)) * 4)
 
 // Selected rows -> the structure-of-arrays form of pgm_result (ev_start / ev_len / ev_read), for callers that download them.
 // ev_start is relative to the record's first sample after trim (rec_src0, k_read_prep).
