@@ -482,7 +482,7 @@ struct GatherStage {
 #define GATHER_SMEM (sizeof(GatherStage) * GATHER_WARPS)
 
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+    asm volatile("cp.async.cg.shared.global.L2::64B [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
@@ -525,10 +525,11 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
         off2 = off1;
         src2 = ev_row_src(row1);
         if (off2 + ln2 > io.samples_cap) ln2 = 0;
-        {   // scale | offset and clo | chi: two loads from one 32-byte sector
-            const double2 so = *reinterpret_cast<const double2 *>(&rc->scale);
-            const int2 cc = *reinterpret_cast<const int2 *>(&rc->clo);
-            scale2 = so.x; offset2 = so.y; clo2 = cc.x; chi2 = cc.y;
+        {   // scale | offset | clo | chi: the record's first 32-byte sector in ONE load (LDG.256: one request per event)
+            unsigned long long a, bq, cq, dq;
+            asm volatile("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(a), "=l"(bq), "=l"(cq), "=l"(dq) : "l"(rc));
+            scale2 = __longlong_as_double((long long)a); offset2 = __longlong_as_double((long long)bq);
+            clo2 = (int)(uint32_t)cq; chi2 = (int)(uint32_t)(cq >> 32);
         }
         if (SCALING) { med2 = rc->med; mad2 = rc->mad; }
         // raw samples: the 16-byte chunks that hold [src, src + ln), at most GATHER_CH of them, packed behind the chunks of
@@ -542,10 +543,21 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, GATHER_MIN_CTAS) k_gather(D
         uint32_t cfirst = cinc - need;
         if (cfirst >= (uint32_t)GATHER_CAP_CH) { cfirst = 0; need = 0; }
         else if (cfirst + need > (uint32_t)GATHER_CAP_CH) need = GATHER_CAP_CH - cfirst;
-        const uint32_t dst = smem_u32(&S.raw[buf][cfirst * 8]);
+        // Issue: FOUR lanes per event, one 16-byte chunk each, so the two or three chunks of an event leave the SM as one
+        // request (one or two 128-byte lines) instead of one request per chunk; eight events per step, the events' chunk
+        // base / count / place fetched from their owner lanes by shuffle. Chunks 4.. (events above ~25 samples) take more rounds.
+        const uint32_t sbase = smem_u32(&S.raw[buf][0]);
+        const uint32_t maxneed = __reduce_max_sync(PGM_FULL, need);
+        for (uint32_t cr = 0; cr < maxneed; cr += 4) {
 #pragma unroll
-        for (int c = 0; c < GATHER_CH; c++)
-            if ((uint32_t)c < need) cp_async16(dst + 16u * c, b.raw + c0 + 8u * c);
+            for (int k = 0; k < 4; k++) {
+                const int e = (int)(lane >> 2) + 8 * k;
+                const uint64_t c0e = shfl_u64(c0, e);
+                const uint32_t ne = __shfl_sync(PGM_FULL, need, e), cfe = __shfl_sync(PGM_FULL, cfirst, e);
+                const uint32_t c = cr + (lane & 3);
+                if (c < ne) cp_async16(sbase + 16u * (cfe + c), b.raw + c0e + 8u * c);
+            }
+        }
         cp_async_commit();
         sidx2 = cfirst * 8 + mis;
         nst2 = (need * 8 > mis) ? min(ln2, need * 8 - mis) : 0u;

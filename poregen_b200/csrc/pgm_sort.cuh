@@ -226,7 +226,7 @@ struct RankIO {
 
 #define RANK_SMEM ((RANK_WARPS + 1) * SORT_MAX_BINS * 4)
 __global__ void __launch_bounds__(RANK_BLOCK, 2) k_rank(RankIO io) {
-    extern __shared__ __align__(16) uint32_t sm_rank[];
+    extern __shared__ __align__(128) uint32_t sm_rank[];
     __shared__ EvTile sm_tile;
     const uint32_t n = *io.n_events;
     const uint32_t bins = 1u << io.bits, mask = bins - 1;
