@@ -172,7 +172,7 @@ def run_reference_arm(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT,
             "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic", "config": workload_desc(C3_READS, args.block_reads, args.gpus),
+            "dtype": "f64", "data": "synthetic", "config": workload_desc(C3_READS, args.block_reads or min(12500, max(256, -(-C3_READS // (4 * args.gpus)))), args.gpus),
             "events_per_sec": examined / t,
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": 1, "kind": kind,
                              "sample": f"first {n_reads} of the 100,000 C3 reads ({n_samples} samples) per step, --sample_limit "
@@ -414,7 +414,11 @@ def run_own_arm(args):
     dev = torch.device("cuda", local)
 
     cfg, opts = workloads.c3(n_reads=args.reads)
-    B = args.block_reads
+    # resident block: 12,500 records on one GPU (larger blocks amortise the per-block table scans); with several GPUs at least four
+    # rounds per rank: the job's first blocks select every event and its last ones few, and a rank's share evens out over the rounds
+    # (one round per rank at N=8 left rank 0 with the heaviest block: 5.4 ms against 4.8 with four rounds). Two rounds in flight per
+    # rank (sibling contexts) were measured too: N=2 16.99 against 16.56 ms, and every kernel's bracket then holds the other lane's kernels.
+    B = args.block_reads or min(12500, max(256, -(-args.reads // (4 * world))))
     n_blocks = (args.reads + B - 1) // B
     rounds = (n_blocks + world - 1) // world
     my_blocks = [j * world + rank for j in range(rounds)]            # may run past n_blocks in the last round: an empty block
@@ -774,7 +778,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--reads", type=int, default=C3_READS, help="records of the whole job (C3 = 100000)")
-    ap.add_argument("--block-reads", type=int, default=12500, help="consecutive records handed over per call (per rank and round), resident job")
+    ap.add_argument("--block-reads", type=int, default=0, help="consecutive records handed over per call (per rank and round), resident job (0: 12500, at least 4 rounds per rank)")
     ap.add_argument("--e2e-block-reads", type=int, default=0, help="the same for the end-to-end job (0: at most 3125, at least 8 rounds per rank)")
     ap.add_argument("--ref-reads", type=int, default=1000, help="--impl reference: records per step (prefix of the same reads)")
     ap.add_argument("--cpu-reads", type=int, default=2000, help="cpu_baseline leg: records in the sample")
