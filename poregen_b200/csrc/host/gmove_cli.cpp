@@ -55,12 +55,12 @@ double realtime() {
     gettimeofday(&tp, nullptr);
     return tp.tv_sec + tp.tv_usec * 1e-6;
 }
-double cputime() {
+[[maybe_unused]] double cputime() {
     struct rusage r;
     getrusage(RUSAGE_SELF, &r);
     return r.ru_utime.tv_sec + r.ru_stime.tv_sec + 1e-6 * (r.ru_utime.tv_usec + r.ru_stime.tv_usec);
 }
-long peakrss() {
+[[maybe_unused]] long peakrss() {
     struct rusage r;
     getrusage(RUSAGE_SELF, &r);
     return r.ru_maxrss * 1024;

@@ -424,7 +424,6 @@ __global__ void __launch_bounds__(DM_THREADS, DM_MIN_CTAS) k_decode_moves(DevOpt
                 }
                 *reinterpret_cast<uint4 *>(sm_codes + 16 * tid) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
             }
-            const int p0 = (int)off - (int)head;                                       // string position of the thread's byte 0
             const uint32_t lo = (off < head) ? min((uint32_t)DM_PER, head - off) : 0u;
             const uint32_t hi = (off >= span) ? 0u : min((uint32_t)DM_PER, span - off);
             uint32_t bits = byte_nibble(byte_is_zero(x.x ^ one8)) | (byte_nibble(byte_is_zero(x.y ^ one8)) << 4);
