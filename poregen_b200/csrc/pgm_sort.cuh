@@ -21,7 +21,8 @@
 // bucket then holds a CONTIGUOUS range of slots, and k_msd_rank gives a bucket to one CTA, which walks it in order
 // with one running counter per slot in shared memory - no second histogram, no second scan, the quota data of the
 // bucket's slots (keep, sel_base) loaded once, coalesced, and all writes of a CTA inside one bucket's output range.
-// Inside a tile, stability comes from processing items in (warp, round, lane) order with __match_any_sync peer ranks
+// Inside a tile, stability comes from processing items in (warp, round, lane) order with peer masks (the lanes of a round that hold
+// the same digit: ballots over the digit's bits - MATCH.ANY, -DSORT_MATCH_ANY, is 25 % slower for the whole sort stage)
 // and per-warp digit counters.
 #pragma once
 #include "pgm_device.cuh"
@@ -187,7 +188,19 @@ __device__ __forceinline__ void tile_rank(const uint32_t (&dig)[ITEMS], uint32_t
 #pragma unroll
     for (int rd = 0; rd < ITEMS; rd++) {
         const bool valid = (uint32_t)(rd * 32) + lane < nvalid_warp;
+#ifdef SORT_MATCH_ANY
         peers[rd] = __match_any_sync(0xffffffffu, valid ? dig[rd] : 0xffffffffu);   // invalid lanes form their own group
+#else
+        // the lanes with my digit, bit by bit with ballots (one VOTE and two logic operations per bit: MATCH.ANY stood for a third
+        // of the sort kernels' stall samples, profiles/ncu_r02_c3block.md)
+        uint32_t m = __ballot_sync(0xffffffffu, valid);
+        if (!valid) m = ~m;
+        for (uint32_t bit = 1; bit < bins; bit <<= 1) {
+            const uint32_t v = __ballot_sync(0xffffffffu, (dig[rd] & bit) != 0);
+            m &= (dig[rd] & bit) ? v : ~v;
+        }
+        peers[rd] = m;
+#endif
     }
 #pragma unroll
     for (int rd = 0; rd < ITEMS; rd++) {
