@@ -611,10 +611,13 @@ def run_own_arm(args):
                 r = capi.PgmResult()
                 e._chk(e.lib.pgm_download(e._ctx, C.byref(r)))
                 return text_len(r)
+            trace = [] if (rank == 0 and os.environ.get("PGM_BENCH_TRACE")) else None
             for j in range(rounds):
                 e, st_ = lanes[j % 2]
+                t_a = time.perf_counter()
                 if len(pending) == 2:
                     tb += collect(pending.pop(0))
+                t_b = time.perf_counter()
                 hb = host_blocks[j]
                 with torch.cuda.stream(st_):
                     if hb is not None:
@@ -626,8 +629,13 @@ def run_own_arm(args):
                     e.set_gathered(lane_all[j % 2].data_ptr(), world, rank)
                     e.emit()
                 pending.append(e)
+                if trace is not None:
+                    trace.append((round((t_b - t_a) * 1e3, 1), round((time.perf_counter() - t_b) * 1e3, 1)))
+            t_a = time.perf_counter()
             while pending:
                 tb += collect(pending.pop(0))
+            if trace is not None:
+                print(f"[e2e trace rank 0] per round (collect ms, launch ms): {trace}; drain {round((time.perf_counter() - t_a) * 1e3, 1)} ms", file=sys.stderr)
             text_bytes[0] = tb
 
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
