@@ -438,7 +438,7 @@ def run_own_arm(args):
     e2e_nb = (args.reads + e2e_B - 1) // e2e_B
     e2e_rounds = (e2e_nb + world - 1) // world
     e2e_host_blocks = []
-    for j in range(e2e_rounds):
+    for j in range(0 if args.no_e2e else e2e_rounds):
         lo, hi = (j * world + rank) * e2e_B, min(args.reads, (j * world + rank + 1) * e2e_B)
         if lo >= hi:
             e2e_host_blocks.append(None)
@@ -639,13 +639,15 @@ def run_own_arm(args):
             text_bytes[0] = tb
 
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    if args.no_e2e:             # (a run that only wants the resident job and K7, e.g. the 1 M-read C5 shape)
+        rounds, host_blocks, e2e_steps = 0, [], 0
     job_e2e()
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         job_e2e()
     barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    e2e_s = (time.perf_counter() - t0) / max(1, e2e_steps)
     t_e2e = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
@@ -685,7 +687,7 @@ def run_own_arm(args):
                 "events_per_sec": tot_events / (ms_step * 1e-3),
                 "events_examined_per_step": tot_events, "events_pass_per_step": tot_pass,
                 "events_selected_per_step": tot_sel_ev, "samples_selected_per_step": tot_sel_samp,
-                "e2e": {"value": tot_samples / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "events_per_sec": tot_events / e2e_s,
+                "e2e": None if args.no_e2e else {"value": tot_samples / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "events_per_sec": tot_events / e2e_s,
                         "h2d_bytes_per_step": int(tot_h2d), "d2h_bytes_per_step": int(tot_d2h), "steps": e2e_steps,
                         "output": "dump text (%.8f, formatted on the device), per-k-mer text offsets and counts, per-record flags",
                         "batches_in_flight": 2, "how": "pgm_submit / pgm_wait" if world == 1 else "two sibling contexts per rank, split-phase calls",
@@ -790,6 +792,7 @@ def main():
     ap.add_argument("--e2e-block-reads", type=int, default=0, help="the same for the end-to-end job (0: at most 3125, at least 8 rounds per rank)")
     ap.add_argument("--ref-reads", type=int, default=1000, help="--impl reference: records per step (prefix of the same reads)")
     ap.add_argument("--cpu-reads", type=int, default=2000, help="cpu_baseline leg: records in the sample")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (the line then has e2e: null)")
     ap.add_argument("--e2e-steps", type=int, default=3, help="steps of the end-to-end leg (each moves ~55 GB over PCIe)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-c2", action="store_true", help="skip the C2 comparison leg")
