@@ -80,7 +80,8 @@ typedef struct pgm_opts {
     uint32_t flag_rna;            /* --rna: generated alphabet is ACGU (gmove.cpp:421-425)        */
     uint32_t scaling;             /* --scaling: 0 none (the real default, gmove.cpp:229), 1 medmad*/
     uint32_t output;              /* PGM_OUT_*                                                    */
-    uint32_t n_slots;             /* number of dumped k-mers = index_end - index_start + 1        */
+    uint32_t n_slots;             /* number of dumped k-mers = index_end - index_start + 1; at
+                                     most 2^20 (all 10-mers): two sort digits of 10 bits           */
     uint32_t index_lo;            /* generated list: id of the first dumped k-mer = index_start-1 */
     uint32_t reserved0;
     double pa_min;                /* --pa_min [40.0]                                              */
